@@ -1,0 +1,40 @@
+import os
+import sys
+import zlib
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def golden_stage2():
+    return np.load(os.path.join(GOLDEN, "stage2.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_net():
+    return np.load(os.path.join(GOLDEN, "net.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_frames(golden_stage2):
+    """Frames behind tests/golden/stage2.npz, regenerated from unet_b200.synth and pinned
+    by the crc32 recorded when the real reference produced the fixture."""
+    import unet_b200.synth as S
+    g = golden_stage2
+    speckle = S.frames_speckle(1, 448, 800, seed=5, n_blobs=400)[0]
+    frames = {"cable": S.frames_cable(1, 448, 800, seed=0)[0], "noise": g["noise_frame"],
+              "speckle": speckle, "dots": speckle}
+    for k, fr in frames.items():
+        assert zlib.crc32(fr.tobytes()) == int(g[f"{k}_crc"]), \
+            f"synthetic frame '{k}' no longer matches the golden fixture; rerun tests/golden/make_golden.py"
+    return frames

@@ -1,0 +1,126 @@
+"""Generate tests/golden/*.npz by running the REAL reference (imported from
+/root/reference) on seeded synthetic inputs.  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+The reference ships no tests, fixtures or golden vectors of its own,
+so these files are what pins oracle/ to the reference.  Library versions are recorded
+inside each file.
+"""
+import os
+import sys
+
+import cv2
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference")
+
+import infer_two_stage_burr as T          # noqa: E402  (the reference)
+import infer_enhanced_burr as E           # noqa: E402
+from src.models.unetpp import NestedUNet  # noqa: E402
+
+import unet_b200.synth as S               # noqa: E402
+
+cv2.setNumThreads(1)
+torch.set_num_threads(4)
+VERS = np.array([cv2.__version__, torch.__version__, np.__version__])
+
+
+def ref_model(sd):
+    m = NestedUNet(num_classes=3, deep_supervision=True, pretrained_encoder=False)
+    m.load_state_dict(sd, strict=True)
+    return m.eval()
+
+
+def stage2():
+    out = {"versions": VERS}
+    cable = S.frames_cable(1, 448, 800, seed=0)[0]
+    noise = S.frames_noise(1, 160, 256, seed=1)[0]
+    speckle = S.frames_speckle(1, 448, 800, seed=5, n_blobs=400)[0]
+    for tag, fr in (("cable", cable), ("noise", noise), ("speckle", speckle), ("dots", speckle)):
+        h, w = fr.shape[:2]
+        gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+        roi = T.map_roi_to_original((w, h), (512, 512))
+        mask = S.mask_cable_synth(h, w, None)
+        if tag == "dots":
+            mask = S.mask_blobs(h, w, seed=3, fill=0.002)
+        # large frames are regenerated from unet_b200.synth in the tests; crc32 pins them
+        import zlib
+        out[f"{tag}_crc"] = np.array(zlib.crc32(fr.tobytes()), np.uint32)
+        if tag == "noise":
+            out[f"{tag}_frame"] = fr
+        if tag in ("cable", "noise"):
+            out[f"{tag}_gray"] = gray
+        out[f"{tag}_roi"] = np.array(roi, np.int32)
+        out[f"{tag}_mask"] = mask
+        pre = T.preprocess_image(fr).numpy()               # [3,512,512] f32 = u8/255 exactly
+        pre_u8 = np.rint(pre * 255.0).astype(np.uint8)
+        assert np.array_equal(pre_u8.astype(np.float32) / 255.0, pre)
+        if tag in ("cable", "noise"):
+            out[f"{tag}_pre_u8"] = pre_u8                  # stored as u8 (4x smaller)
+        for sens, cfg in (("medium", {"min_area": 30, "max_area": 800}),
+                          ("high", {"min_area": 20, "max_area": 1000})):
+            out[f"{tag}_burr_{sens}"] = T.detect_burrs_on_cable(gray, mask, cfg)
+        out[f"{tag}_burr_enh"] = E.detect_burrs_enhanced(gray, mask, {"min_area": 50, "max_area": 500})
+        out[f"{tag}_burr_empty"] = T.detect_burrs_on_cable(gray, np.zeros_like(mask), None)
+    # enhance_image on a small crop-sized frame (NLM is slow) -- size divisible by the 8x8 CLAHE grid
+    small = S.frames_cable(1, 128, 256, seed=2)[0]
+    out["enh_in"] = small
+    out["enh_out"] = E.enhance_image(small)
+    big = S.frames_cable(1, 270, 480, seed=3)[0]
+    out["norm_in"] = big
+    out["norm_out"] = cv2.resize(cv2.rotate(big, cv2.ROTATE_90_COUNTERCLOCKWISE), (800, 448),
+                                 interpolation=cv2.INTER_LINEAR)
+    np.savez_compressed(os.path.join(HERE, "stage2.npz"), **out)
+
+
+def net():
+    out = {"versions": VERS}
+    sd = S.make_state_dict(seed=0)
+    m = ref_model(sd)
+    keys = list(m.state_dict().keys())
+    out["state_dict_keys"] = np.array(keys)
+    g = torch.Generator().manual_seed(7)
+    for tag, shape in (("a", (1, 3, 64, 64)), ("b", (2, 3, 48, 80))):
+        x = torch.rand(*shape, generator=g)
+        with torch.no_grad():
+            y = m(x)
+        out[f"x_{tag}"] = x.numpy()
+        out[f"y_{tag}"] = y.numpy()
+    # whole frame step through the reference's own statements (infer_two_stage_burr.py:286-323)
+    fr = S.frames_cable(1, 448, 800, seed=4)[0]
+    roi = T.map_roi_to_original((800, 448), (512, 512))
+    x1, y1, x2, y2 = roi
+    img = T.preprocess_image(fr).unsqueeze(0)
+    with torch.no_grad():
+        o = m(img)
+    probs = torch.softmax(o, dim=1)[0].cpu().numpy()
+    pred = np.argmax(probs, axis=0).astype(np.uint8)
+    res = {}
+    for name, cls in (("cable", 1), ("tape", 2)):
+        full = cv2.resize((pred == cls).astype(np.uint8), (800, 448), interpolation=cv2.INTER_NEAREST)
+        mk = np.zeros_like(full)
+        mk[y1:y2, x1:x2] = full[y1:y2, x1:x2]
+        res[name] = mk
+    gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+    burr = T.detect_burrs_on_cable(gray, res["cable"], {"min_area": 30, "max_area": 800})
+    out["step_seed"] = np.array(4)
+    out["step_logits_sub"] = o[0, :, ::8, ::8].numpy()
+    out["step_logits_sum"] = np.array([float(o.double().sum()), float(o.double().abs().sum())])
+    out["step_pred"] = pred
+    out["step_mask_cable"] = res["cable"]
+    out["step_mask_tape"] = res["tape"]
+    out["step_mask_burr"] = burr
+    out["step_counts"] = np.array([res["cable"].sum(), res["tape"].sum(), burr.sum()], np.int64)
+    np.savez_compressed(os.path.join(HERE, "net.npz"), **out)
+
+
+if __name__ == "__main__":
+    stage2()
+    net()
+    for f in ("stage2.npz", "net.npz"):
+        print(f, os.path.getsize(os.path.join(HERE, f)))

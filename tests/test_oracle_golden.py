@@ -1,0 +1,78 @@
+"""Pins oracle/ (the CPU restatement) to outputs of the REAL reference captured in
+tests/golden/*.npz by tests/golden/make_golden.py."""
+import cv2
+import numpy as np
+import pytest
+import torch
+
+import unet_b200.synth as S
+from oracle import cvnp
+from oracle import ref_pipeline as R
+
+TAGS = ["cable", "noise", "speckle", "dots"]
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_burr_functions_match_reference(tag, golden_stage2, golden_frames):
+    g = golden_stage2
+    fr = golden_frames[tag]
+    gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+    mask = g[f"{tag}_mask"]
+    for sens in ("medium", "high"):
+        got = R.burrs_standard(gray, mask, R.BURR_CONFIGS[sens])
+        assert np.array_equal(got, g[f"{tag}_burr_{sens}"])
+    assert np.array_equal(R.burrs_enhanced(gray, mask), g[f"{tag}_burr_enh"])
+    assert np.array_equal(R.burrs_standard(gray, np.zeros_like(mask)), g[f"{tag}_burr_empty"])
+    h, w = fr.shape[:2]
+    assert tuple(g[f"{tag}_roi"]) == R.map_roi((w, h))
+
+
+@pytest.mark.parametrize("tag", ["cable", "noise"])
+def test_preprocess_and_gray_match_reference(tag, golden_stage2, golden_frames):
+    g = golden_stage2
+    fr = golden_frames[tag]
+    want = g[f"{tag}_pre_u8"].astype(np.float32) / 255.0
+    assert np.array_equal(R.preprocess(fr).numpy(), want)
+    assert np.array_equal(cvnp.bgr2gray(fr), g[f"{tag}_gray"])
+    rs = cvnp.resize_linear(fr[..., ::-1], (512, 512))
+    assert np.array_equal(np.transpose(rs, (2, 0, 1)), g[f"{tag}_pre_u8"])
+
+
+def test_enhance_and_normalize_match_reference(golden_stage2):
+    g = golden_stage2
+    assert np.array_equal(R.enhance(g["enh_in"]), g["enh_out"])
+    assert np.array_equal(R.normalize_frame(g["norm_in"], rotate=True), g["norm_out"])
+    rot = np.ascontiguousarray(np.transpose(g["norm_in"], (1, 0, 2))[::-1])
+    assert np.array_equal(cvnp.resize_linear(rot, (800, 448)), g["norm_out"])
+
+
+def test_state_dict_layout(golden_net):
+    sd = S.make_state_dict(0)
+    assert list(sd.keys()) == list(golden_net["state_dict_keys"])
+    assert len(sd) == 134
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_unet_forward_matches_reference(tag, golden_net):
+    sd = S.make_state_dict(0)
+    y = R.unet_forward(torch.from_numpy(golden_net[f"x_{tag}"]), sd).numpy()
+    want = golden_net[f"y_{tag}"]
+    assert y.shape == want.shape
+    assert np.abs(y - want).max() <= 1e-5 * np.abs(want).max()
+
+
+def test_frame_step_matches_reference(golden_net):
+    torch.set_num_threads(4)
+    g = golden_net
+    sd = S.make_state_dict(0)
+    fr = S.frames_cable(1, 448, 800, seed=int(g["step_seed"]))[0]
+    st = {}
+    res = R.frame_step(fr, sd, "medium", stages=st)
+    assert np.abs(st["logits"][:, ::8, ::8] - g["step_logits_sub"]).max() <= 1e-4 * np.abs(g["step_logits_sub"]).max()
+    agree = (res["pred"] == g["step_pred"]).mean()
+    assert agree >= 0.9999          # thread-count dependent fp32 summation order in MKLDNN
+    if agree == 1.0:
+        assert np.array_equal(res["mask_cable"], g["step_mask_cable"])
+        assert np.array_equal(res["mask_tape"], g["step_mask_tape"])
+        assert np.array_equal(res["mask_burr"], g["step_mask_burr"])
+        assert [res["cable_px"], res["tape_px"], res["burr_px"]] == list(g["step_counts"])

@@ -1,0 +1,122 @@
+"""Seeded synthetic inputs for the inspection hot path.
+
+The reference ships no video, no checkpoint and no test data
+(/root/reference/.gitignore:30-37), so every test and benchmark input is generated
+here.  Pure numpy / torch-CPU; no device work.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def frames_noise(b: int, h: int = 448, w: int = 800, seed: int = 0) -> np.ndarray:
+    """iid uniform uint8 BGR frames [b,h,w,3]: worst case for Canny / CCL."""
+    rng = np.random.default_rng(seed)
+    return rng.integers(0, 256, size=(b, h, w, 3), dtype=np.uint8)
+
+
+def frames_cable(b: int, h: int = 448, w: int = 800, seed: int = 0) -> np.ndarray:
+    """Structured frames: dark noisy background, a bright vertical "cable" band at
+    x in [0.40w, 0.55w) with a sinusoidal edge wobble, and 20 bright blobs ("burrs")
+    touching the band's outer edges."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((b, h, w, 3), np.uint8)
+    ys = np.arange(h, dtype=np.float64)[:, None]
+    xs = np.arange(w, dtype=np.float64)[None, :]
+    for i in range(b):
+        img = rng.normal(30.0, 10.0, size=(h, w))
+        phase = rng.uniform(0, 2 * np.pi)
+        wob = 6.0 * np.sin(2 * np.pi * ys / 64.0 + phase)
+        left = 0.40 * w + wob
+        right = 0.55 * w + wob
+        band = (xs >= left) & (xs < right)
+        img = img + 150.0 * band
+        for _ in range(20):
+            sz = int(rng.integers(6, 13))
+            y0 = int(rng.integers(0, max(1, h - sz)))
+            side = int(rng.integers(0, 2))
+            edge = (right if side else left)[y0, 0]
+            x0 = int(edge) if side else int(edge) - sz
+            x0 = min(max(x0, 0), w - sz)
+            img[y0:y0 + sz, x0:x0 + sz] += 80.0
+        img = img + rng.normal(0.0, 8.0, size=(h, w))
+        for c, gain in enumerate((1.0, 0.95, 0.9)):
+            out[i, :, :, c] = np.clip(img * gain, 0, 255).astype(np.uint8)
+    return out
+
+
+def mask_cable_synth(h: int = 448, w: int = 800, roi=None) -> np.ndarray:
+    """Cable mask decoupled from the net: 1 inside the un-wobbled band (and ROI)."""
+    m = np.zeros((h, w), np.uint8)
+    m[:, int(0.40 * w):int(0.55 * w)] = 1
+    if roi is not None:
+        x1, y1, x2, y2 = roi
+        keep = np.zeros_like(m)
+        keep[y1:y2, x1:x2] = 1
+        m &= keep
+    return m
+
+
+def mask_blobs(h: int, w: int, seed: int = 0, fill: float = 0.3) -> np.ndarray:
+    """Random binary image {0,1}; dense, many small components."""
+    rng = np.random.default_rng(seed)
+    return (rng.random((h, w)) < fill).astype(np.uint8)
+
+
+def make_state_dict(seed: int = 0, num_classes: int = 3, input_channels: int = 3,
+                    head_gain: float = 1.0):
+    """Random-init checkpoint "W0" with the reference's 134-key layout
+    (src/models/unetpp.py:40-91): default-init-like conv weights, randomised BN
+    statistics so BN folding is exercised.  ``head_gain`` scales final.weight ("W1")."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    nb = [32, 64, 128, 256, 512]
+    blocks = [("conv0_0", input_channels, nb[0]), ("conv1_0", nb[0], nb[1]),
+              ("conv2_0", nb[1], nb[2]), ("conv3_0", nb[2], nb[3]),
+              ("conv4_0", nb[3], nb[4]), ("conv3_1", nb[3] + nb[4], nb[3]),
+              ("conv2_2", nb[2] + nb[3], nb[2]), ("conv1_3", nb[1] + nb[2], nb[1]),
+              ("conv0_4", nb[0] + nb[1], nb[0])]
+    sd = {}
+
+    def conv(name, cin, cout, k):
+        # ReLU-preserving scale (He-uniform) so activations neither vanish nor explode.
+        bound = (6.0 / (cin * k * k)) ** 0.5
+        sd[name + ".weight"] = (torch.rand(cout, cin, k, k, generator=g) * 2 - 1) * bound
+        sd[name + ".bias"] = (torch.rand(cout, generator=g) * 2 - 1) * 0.1
+
+    def bn(name, c):
+        sd[name + ".weight"] = torch.rand(c, generator=g) + 0.5
+        sd[name + ".bias"] = torch.randn(c, generator=g) * 0.1
+        sd[name + ".running_mean"] = torch.randn(c, generator=g) * 0.1
+        sd[name + ".running_var"] = torch.rand(c, generator=g) + 0.5
+        sd[name + ".num_batches_tracked"] = torch.tensor(1, dtype=torch.int64)
+
+    for blk, cin, cout in blocks:
+        conv(f"{blk}.conv1", cin, cout, 3)
+        bn(f"{blk}.bn1", cout)
+        conv(f"{blk}.conv2", cout, cout, 3)
+        bn(f"{blk}.bn2", cout)
+    conv("final", nb[0], num_classes, 1)
+    sd["final.weight"] = sd["final.weight"] * head_gain
+    conv("ds3_1", nb[3], num_classes, 1)
+    conv("ds2_2", nb[2], num_classes, 1)
+    conv("ds1_3", nb[1], num_classes, 1)
+    return sd
+
+
+def frames_speckle(b: int, h: int = 448, w: int = 800, seed: int = 0, n_blobs: int = 400) -> np.ndarray:
+    """Smooth dark background with sparse bright rectangles (3..14 px sides): yields
+    many mid-sized edge components, so the component filter keeps a non-trivial subset."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((b, h, w, 3), np.uint8)
+    for i in range(b):
+        img = np.full((h, w), 40.0) + rng.normal(0, 1.5, size=(h, w))
+        for _ in range(n_blobs):
+            bh = int(rng.integers(3, 15))
+            bw = int(rng.integers(3, 15))
+            y0 = int(rng.integers(0, h - bh))
+            x0 = int(rng.integers(0, w - bw))
+            img[y0:y0 + bh, x0:x0 + bw] += float(rng.integers(40, 200))
+        for c, gain in enumerate((1.0, 0.97, 0.93)):
+            out[i, :, :, c] = np.clip(img * gain, 0, 255).astype(np.uint8)
+    return out
