@@ -1,0 +1,164 @@
+/* unetb200.h -- C ABI of libunetb200.so: the B200 (sm_100a) implementation of the
+ * per-frame inspection hot path of Chenxu1103/UNET-.
+ *
+ * The reference has no FFI / plugin layer of its own (it is pure Python calling
+ * torch and OpenCV), so each entry point below names the reference statements it
+ * replaces (file:line under /root/reference).  The Python host layer in unet-_b200/
+ * binds these with ctypes and re-creates the reference's own contracts on top
+ * (NestedUNet module, preprocess_image, detect_burrs_on_cable, ...).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative ub_status; no C++ exception
+ *     crosses the ABI; ub_last_error() gives the message of the last failure.
+ *   - pointers suffixed _dev are device pointers borrowed for the duration of the
+ *     enqueued work; pointers suffixed _host are host pointers.
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued asynchronously on
+ *     it unless a function says otherwise.  One ctx per (thread, GPU); not thread-safe.
+ *   - there is no CPU fallback: ub_create fails on anything that is not sm_100.
+ */
+#ifndef UNETB200_H
+#define UNETB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ub_ctx ub_ctx;
+
+typedef enum ub_status {
+  UB_OK = 0,
+  UB_ERR_ARG = -1,       /* bad argument / shape */
+  UB_ERR_CUDA = -2,      /* CUDA runtime error (message in ub_last_error) */
+  UB_ERR_ARCH = -3,      /* device is not sm_100 */
+  UB_ERR_STATE = -4,     /* e.g. weights not set */
+  UB_ERR_NOMEM = -5
+} ub_status;
+
+/* One entry of a state_dict (src/models/unetpp.py:40-91; 134 entries for the 3-class
+ * model).  `data_host` is fp32 (int64 for *.num_batches_tracked, which is ignored). */
+typedef struct ub_named_tensor {
+  const char* name;
+  const void* data_host;
+  int64_t numel;
+} ub_named_tensor;
+
+typedef struct ub_roi { int32_t x1, y1, x2, y2; } ub_roi;   /* infer_two_stage_burr.py:37-47 */
+
+/* Component filter of infer_two_stage_burr.py:103-117 / infer_enhanced_burr.py:121-136. */
+typedef struct ub_burr_params {
+  int32_t min_area, max_area;   /* keep iff min_area <= area <= max_area            */
+  int32_t max_aspect;           /* and max(w,h) <= max_aspect*min(w,h)  (5 or 6)     */
+  int32_t min_side;             /* and w >= min_side and h >= min_side  (4 or 5)     */
+  int32_t canny_low, canny_high;/* 50/150 standard, 30/100 enhanced                  */
+  int32_t band_k, close_k, open_k; /* ellipse sizes: 8/3/2 standard, 25/5/3 enhanced */
+} ub_burr_params;
+
+enum { UB_VARIANT_STANDARD = 0,   /* detect_burrs_on_cable, infer_two_stage_burr.py:50-119 */
+       UB_VARIANT_ENHANCED = 1 }; /* detect_burrs_enhanced, infer_enhanced_burr.py:69-138  */
+
+/* ---- lifetime ------------------------------------------------------------------- */
+/* Allocates all scratch for batches of up to max_batch frames of frame_h x frame_w and
+ * a net input of net_h x net_w (multiples of 16).  num_classes <= 8. */
+int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
+              int net_h, int net_w, int num_classes);
+void ub_destroy(ub_ctx* ctx);
+const char* ub_last_error(ub_ctx* ctx);          /* ctx may be NULL */
+int ub_version(void);
+
+/* ---- stage 1: the network -------------------------------------------------------- */
+/* Replaces model.load_state_dict(...) + .eval() (infer_two_stage_burr.py:214-217):
+ * folds eval-mode BatchNorm (eps 1e-5) into each conv, repacks to bf16 K-blocked
+ * layout, uploads.  Synchronous. */
+int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* tensors, int n);
+
+/* Replaces NestedUNet.forward in eval mode (src/models/unetpp.py:93-135):
+ * x fp32 NCHW [B,3,H,W] -> logits fp32 NCHW [B,num_classes,H,W]; H,W multiples of 16,
+ * H*W <= net_h*net_w, B <= max_batch. */
+int ub_forward(ub_ctx* ctx, const float* x_nchw_dev, int B, int H, int W,
+               float* logits_nchw_dev, void* stream);
+
+/* Select the conv implementation: 0 = tcgen05 tensor-core kernel (default, the product
+ * path), 1 = plain CUDA-core kernel kept for kernel-vs-kernel debugging. */
+int ub_set_conv_impl(ub_ctx* ctx, int impl);
+
+/* ---- pre / post processing around the net ---------------------------------------- */
+/* Replaces preprocess_image (infer_two_stage_burr.py:122-127) and the BGR2GRAY of :317
+ * for a batch: frames u8 BGR [B,H,W,3] -> x fp32 NCHW [B,3,net_h,net_w] (RGB, /255;
+ * nullable) and gray u8 [B,H,W] (nullable). */
+int ub_preprocess(ub_ctx* ctx, const uint8_t* frames_bgr_dev, int B, int H, int W,
+                  float* x_nchw_dev, uint8_t* gray_dev, void* stream);
+
+/* Replaces cv2.rotate(ROTATE_90_COUNTERCLOCKWISE) + cv2.resize(INTER_LINEAR)
+ * (infer_two_stage_burr.py:275-280): src u8 [B,sh,sw,3] -> dst u8 [B,dh,dw,3]. */
+int ub_normalize_frames(ub_ctx* ctx, const uint8_t* src_dev, int B, int sh, int sw,
+                        int rotate_ccw, uint8_t* dst_dev, int dh, int dw, void* stream);
+
+/* Replaces softmax/argmax/class masks/NEAREST resize/ROI (infer_two_stage_burr.py:299-314):
+ * logits fp32 NCHW [B,C,nh,nw] -> pred u8 [B,nh,nw] (nullable), mask_cable / mask_tape
+ * u8 [B,H,W] in {0,1}. */
+int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, int nw,
+                         int H, int W, const ub_roi* roi, uint8_t* pred_dev,
+                         uint8_t* mask_cable_dev, uint8_t* mask_tape_dev, void* stream);
+
+/* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
+int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
+int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */
+/* op: 0 dilate, 1 erode, 2 close, 3 open with cv2 MORPH_ELLIPSE(k,k), k <= 25, on binary images:
+ * any non-zero input is foreground, the output is {0, value}. */
+int ub_morph(ub_ctx* ctx, int op, int k, const uint8_t* src_dev, int B, int H, int W, int value, uint8_t* dst_dev, void* stream); /* :78-80,:92-97 */
+/* cv2.connectedComponentsWithStats(conn 8) (:100): labels i32 [B,H,W] in OpenCV order,
+ * stats i32 [B,max_labels,5] (left,top,width,height,area; row 0 = background),
+ * n_labels i32 [B] (includes background).  Components beyond max_labels are labelled
+ * but their stats rows are dropped. */
+int ub_ccl(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int32_t* labels_dev,
+           int32_t* stats_dev, int max_labels, int32_t* n_labels_dev, void* stream);
+/* Sobel-magnitude / Laplacian edge maps of infer_enhanced_burr.py:93-102 -> {0,255}. */
+int ub_sobel_edges(ub_ctx* ctx, const uint8_t* gray_dev, int B, int H, int W, int thresh, uint8_t* dst_dev, void* stream);
+int ub_laplacian_edges(ub_ctx* ctx, const uint8_t* gray_dev, int B, int H, int W, int thresh, uint8_t* dst_dev, void* stream);
+
+/* Whole detect_burrs_on_cable / detect_burrs_enhanced for a batch:
+ * gray u8 [B,H,W], mask_cable u8 [B,H,W] in {0,1} -> burr_mask u8 [B,H,W] in {0,1},
+ * burr_px i32 [B] (nullable). */
+int ub_burr(ub_ctx* ctx, int variant, const uint8_t* gray_dev, const uint8_t* mask_cable_dev,
+            int B, int H, int W, const ub_burr_params* params, uint8_t* burr_mask_dev,
+            int32_t* burr_px_dev, void* stream);
+
+/* ---- the whole per-frame step (body of the loop, infer_two_stage_burr.py:286-343) -- */
+/* frames u8 BGR [B,frame_h,frame_w,3] -> frame_stats i32 [B,4] = (index in batch,
+ * cable_px, tape_px, burr_px); masks (nullable) u8 [B,3,frame_h,frame_w] = cable, tape,
+ * burr.  roi == NULL -> map_roi_to_original of the frame size. */
+int ub_pipeline(ub_ctx* ctx, const uint8_t* frames_bgr_dev, int B, int variant,
+                const ub_roi* roi, const ub_burr_params* params,
+                int32_t* frame_stats_dev, uint8_t* masks_dev, void* stream);
+
+/* Same, from HOST buffers (pinned for full speed): copies frames host->device, runs the
+ * step, copies the stats (and masks if non-NULL) back, and waits for completion. */
+int ub_pipeline_host(ub_ctx* ctx, const uint8_t* frames_bgr_host, int B, int variant,
+                     const ub_roi* roi, const ub_burr_params* params,
+                     int32_t* frame_stats_host, uint8_t* masks_host);
+
+/* ---- test hooks (layer-level parity checks; not used by the product path) ------------ */
+/* Runs conv layer `layer` (0..17 in network order; BN folded, ReLU) on NCHW fp32 inputs:
+ * x0 [B,cin0,H,W] (layer 0: 3 channels), x1 [B,cin1,H,W] or NULL -> out [B,cout,H,W]. */
+int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0_dev, const float* x1_dev, int B, int H, int W,
+                  float* out_dev, void* stream);
+/* Copies activation buffer `index` of the last forward (order: x_in,t0,x0_0,p0,t1,x1_0,p1,t2,
+ * x2_0,p2,t3,x3_0,p3,t4,x4_0,up4,x3_1,up3,x2_2,up2,x1_3,up1) to NCHW fp32 [B,C,H,W]. */
+int ub_debug_activation(ub_ctx* ctx, int index, int B, int C, int H, int W, float* out_dev, void* stream);
+
+/* ---- instrumentation -------------------------------------------------------------- */
+/* When enabled, every kernel class is bracketed by CUDA events on the launch stream;
+ * ub_timing_read sums them (synchronises).  classes: 0 conv3x3, 1 net glue (pool,
+ * upsample, layout), 2 pre/post, 3 stage-2 stencil/morphology, 4 CCL/hysteresis. */
+enum { UB_T_CONV = 0, UB_T_GLUE = 1, UB_T_PREPOST = 2, UB_T_STENCIL = 3, UB_T_CCL = 4, UB_T_NCLASS = 5 };
+int ub_timing_enable(ub_ctx* ctx, int on);
+int ub_timing_read(ub_ctx* ctx, float* ms_per_class, int64_t* scopes_per_class, int reset);
+/* Number of kernels this context has launched so far. */
+int64_t ub_launch_count(ub_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UNETB200_H */

@@ -1,0 +1,152 @@
+"""GPU parity of the network path: every conv layer (tcgen05 kernel) against a torch fp32
+reference of the same op on the same bf16-rounded operands, the whole forward against the
+fp32 oracle (tolerances from BASELINE.json: logits within 1e-2 relative of fp32, argmax
+agreement >= 99.9 %), the NestedUNet module contract, and the full pipeline."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import unet_b200.synth as S
+from oracle import ref_pipeline as R
+
+pytestmark = pytest.mark.gpu
+
+LAYERS = [("conv0_0", 1, 3, 0, 32), ("conv0_0", 2, 32, 0, 32), ("conv1_0", 1, 32, 0, 64), ("conv1_0", 2, 64, 0, 64),
+          ("conv2_0", 1, 64, 0, 128), ("conv2_0", 2, 128, 0, 128), ("conv3_0", 1, 128, 0, 256), ("conv3_0", 2, 256, 0, 256),
+          ("conv4_0", 1, 256, 0, 512), ("conv4_0", 2, 512, 0, 512), ("conv3_1", 1, 256, 512, 256), ("conv3_1", 2, 256, 0, 256),
+          ("conv2_2", 1, 128, 256, 128), ("conv2_2", 2, 128, 0, 128), ("conv1_3", 1, 64, 128, 64), ("conv1_3", 2, 64, 0, 64),
+          ("conv0_4", 1, 32, 64, 32), ("conv0_4", 2, 32, 0, 32)]
+LOGIT_REL_TOL = 1e-2       # BASELINE.json north_star: "logits within 1e-2 relative of fp32"
+ARGMAX_MIN_AGREE = 0.999   # "argmax mask agreeing on >= 99.9 % of pixels"
+
+
+def bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def folded(sd, blk, idx):
+    w, b = sd[f"{blk}.conv{idx}.weight"].double(), sd[f"{blk}.conv{idx}.bias"].double()
+    g, be = sd[f"{blk}.bn{idx}.weight"].double(), sd[f"{blk}.bn{idx}.bias"].double()
+    mu, var = sd[f"{blk}.bn{idx}.running_mean"].double(), sd[f"{blk}.bn{idx}.running_var"].double()
+    s = g / torch.sqrt(var + 1e-5)
+    return bf((w * s[:, None, None, None]).float()), ((b - mu) * s + be).float()
+
+
+@pytest.fixture(scope="module")
+def sd():
+    return S.make_state_dict(0)
+
+
+@pytest.fixture(scope="module")
+def ctx(sd):
+    from unet_b200 import _lib
+    c = _lib.Context(0, max_batch=2, frame_hw=(448, 800), net_hw=(128, 160))
+    c.set_weights(sd)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("impl", [0, 2, 1], ids=["tcgen05", "tcgen05_alignedA", "simt"])
+@pytest.mark.parametrize("li", range(18))
+def test_conv_layer(ctx, sd, li, impl):
+    blk, idx, c0, c1, cout = LAYERS[li]
+    lvl = li // 2 if li < 10 else (3, 3, 2, 2, 1, 1, 0, 0)[li - 10]
+    h, w = 128 >> lvl, 160 >> lvl
+    g = torch.Generator().manual_seed(li)
+    x0 = torch.rand(2, c0, h, w, generator=g) * 2 - 0.5
+    x1 = (torch.rand(2, c1, h, w, generator=g) * 2 - 0.5) if c1 else None
+    wf, bfold = folded(sd, blk, idx)
+    xin = bf(x0) if x1 is None else torch.cat([bf(x0), bf(x1)], 1)
+    want = F.relu(F.conv2d(xin.double(), wf.double(), bfold.double(), padding=1)).float()
+    ctx.set_conv_impl(impl)
+    try:
+        got = ctx.debug_conv(li, x0.cuda(), x1.cuda() if c1 else None, cout).cpu()
+    finally:
+        ctx.set_conv_impl(0)
+    torch.cuda.synchronize()
+    err = (got - want).abs()
+    tol = 2.0 ** -8 * want.abs() + 1e-3          # one bf16 rounding of the output + fp32 accumulation noise
+    bad = (err > tol)
+    assert not bad.any(), (f"layer {li} ({blk}.conv{idx}) impl {impl}: {int(bad.sum())}/{bad.numel()} outside tolerance, "
+                           f"max err {float(err.max()):.4g} at {np.unravel_index(int(err.argmax()), err.shape)}, "
+                           f"ref there {float(want.flatten()[err.argmax()]):.4g}, max |ref| {float(want.abs().max()):.4g}")
+
+
+@pytest.mark.parametrize("hw", [(64, 64), (128, 160), (48, 80)])
+def test_forward_vs_fp32_oracle(ctx, sd, hw, golden_net):
+    g = torch.Generator().manual_seed(7)
+    x = torch.rand(2, 3, hw[0], hw[1], generator=g)
+    want = R.unet_forward(x, sd)
+    got = ctx.forward(x.cuda()).cpu()
+    rel = float((got - want).abs().max() / want.abs().max())
+    rms = float(((got - want) ** 2).mean().sqrt() / (want ** 2).mean().sqrt())
+    agree = float((got.argmax(1) == want.argmax(1)).float().mean())
+    print(f"forward {hw}: max-rel {rel:.4g} rms-rel {rms:.4g} argmax agreement {agree:.5f}")
+    assert rel <= LOGIT_REL_TOL, f"logits differ by {rel} relative to max |fp32 logit|"
+    assert agree >= ARGMAX_MIN_AGREE
+
+
+def test_forward_golden_reference_outputs(ctx, sd, golden_net):
+    """Against logits produced by the REAL reference module (tests/golden/net.npz)."""
+    for tag in ("a", "b"):
+        x = torch.from_numpy(golden_net[f"x_{tag}"])
+        want = torch.from_numpy(golden_net[f"y_{tag}"])
+        got = ctx.forward(x.cuda()).cpu()
+        rel = float((got - want).abs().max() / want.abs().max())
+        agree = float((got.argmax(1) == want.argmax(1)).float().mean())
+        print(f"golden {tag}: max-rel {rel:.4g} argmax agreement {agree:.5f}")
+        assert rel <= LOGIT_REL_TOL and agree >= ARGMAX_MIN_AGREE
+
+
+def test_module_contract(sd, golden_net):
+    from unet_b200 import NestedUNet
+    m = NestedUNet(num_classes=3, deep_supervision=True, pretrained_encoder=False).to("cuda")
+    assert list(m.state_dict().keys()) == list(golden_net["state_dict_keys"])
+    m.load_state_dict(sd, strict=True)
+    with pytest.raises(RuntimeError):
+        bad = dict(sd)
+        bad.pop("final.bias")
+        m.load_state_dict(bad, strict=True)
+    m.eval()
+    x = torch.from_numpy(golden_net["x_a"]).cuda()
+    with torch.no_grad():
+        y = m(x)
+    assert isinstance(y, torch.Tensor) and y.shape == (1, 3, 64, 64) and y.dtype == torch.float32 and y.is_cuda
+    want = torch.from_numpy(golden_net["y_a"])
+    assert float((y.cpu() - want).abs().max() / want.abs().max()) <= LOGIT_REL_TOL
+    # weights are re-prepared after load_state_dict
+    sd2 = {k: (v * 0 if k == "final.weight" else v) for k, v in sd.items()}
+    m.load_state_dict(sd2, strict=True)
+    with torch.no_grad():
+        y2 = m(x)
+    assert torch.allclose(y2.cpu(), sd["final.bias"].view(1, 3, 1, 1).expand_as(y2), atol=1e-6)
+    m.train()
+    with pytest.raises(NotImplementedError):
+        m(x)
+    with pytest.raises(NotImplementedError):
+        NestedUNet(3, pretrained_encoder=True)
+
+
+def test_pipeline_vs_oracle(sd):
+    """Whole step (infer_two_stage_burr.py:286-343) for a batch: the integer stage must be
+    bit-exact given the GPU's own cable mask; the masks themselves within the argmax tolerance."""
+    import cv2
+    from unet_b200.pipeline import InspectionPipeline
+    frames = np.concatenate([S.frames_cable(2, 448, 800, seed=4), S.frames_noise(1, 448, 800, seed=5)])
+    pipe = InspectionPipeline(sd, batch=3)
+    stats, masks = pipe.run(torch.from_numpy(frames).cuda(), want_masks=True)
+    stats, masks = stats.cpu().numpy(), masks.cpu().numpy()
+    host_stats = pipe.run_host(torch.from_numpy(frames).pin_memory()).numpy()
+    assert np.array_equal(stats, host_stats)
+    for i in range(3):
+        ref = R.frame_step(frames[i], sd, "medium")
+        agree_c = (masks[i, 0] == ref["mask_cable"]).mean()
+        agree_t = (masks[i, 1] == ref["mask_tape"]).mean()
+        print(f"pipeline frame {i}: stats {stats[i].tolist()} oracle {[ref['cable_px'], ref['tape_px'], ref['burr_px']]} "
+              f"mask agreement cable {agree_c:.5f} tape {agree_t:.5f}")
+        assert agree_c >= ARGMAX_MIN_AGREE and agree_t >= ARGMAX_MIN_AGREE
+        gray = cv2.cvtColor(frames[i], cv2.COLOR_BGR2GRAY)
+        same_mask_burr = R.burrs_standard(gray, masks[i, 0], R.BURR_CONFIGS["medium"])
+        assert np.array_equal(masks[i, 2], same_mask_burr)
+        assert stats[i].tolist() == [i, int(masks[i, 0].sum()), int(masks[i, 1].sum()), int(same_mask_burr.sum())]

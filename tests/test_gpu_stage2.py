@@ -1,0 +1,175 @@
+"""GPU parity: integer path (pre/post-processing and the burr stage) must be bit-exact against
+the oracle (cv2-backed restatement in oracle/ref_pipeline.py + numpy spec in oracle/cvnp.py).
+All calls go through the C ABI (unet_b200._lib -> libunetb200.so)."""
+import cv2
+import numpy as np
+import pytest
+import torch
+
+import unet_b200.synth as S
+from oracle import cvnp
+from oracle import ref_pipeline as R
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from unet_b200 import _lib
+    c = _lib.Context(0, max_batch=4, frame_hw=(448, 800), net_hw=(512, 512))
+    yield c
+    c.close()
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def same(name, got, want):
+    got = got.cpu().numpy() if isinstance(got, torch.Tensor) else got
+    assert got.shape == want.shape, (name, got.shape, want.shape)
+    bad = np.argwhere(got != want)
+    assert len(bad) == 0, f"{name}: {len(bad)} of {want.size} differ; first at {bad[0].tolist()} got {got[tuple(bad[0])]} want {want[tuple(bad[0])]}"
+
+
+def frames4():
+    return np.concatenate([S.frames_cable(2, 448, 800, seed=1), S.frames_noise(1, 448, 800, seed=2),
+                           S.frames_speckle(1, 448, 800, seed=5)])
+
+
+def test_preprocess_and_gray(ctx):
+    fr = frames4()
+    x, g = ctx.preprocess(dev(fr))
+    for i in range(4):
+        same(f"gray[{i}]", g[i], cv2.cvtColor(fr[i], cv2.COLOR_BGR2GRAY))
+        same(f"x[{i}]", x[i], R.preprocess(fr[i]).numpy())
+
+
+def test_preprocess_golden(ctx, golden_stage2, golden_frames):
+    for tag in ("cable", "noise"):
+        fr = golden_frames[tag]
+        c = ctx
+        if fr.shape[:2] != (448, 800):
+            from unet_b200 import _lib
+            c = _lib.Context(0, 1, fr.shape[:2], (512, 512))
+        x, g = c.preprocess(dev(fr[None]))
+        same(tag + " gray", g[0], golden_stage2[f"{tag}_gray"])
+        same(tag + " pre", x[0], golden_stage2[f"{tag}_pre_u8"].astype(np.float32) / 255.0)
+
+
+def test_normalize_frames(ctx, golden_stage2):
+    big = S.frames_noise(2, 1080, 1920, seed=3)
+    out = ctx.normalize_frames(dev(big), (800, 448), rotate=False)
+    for i in range(2):
+        same("resize", out[i], cv2.resize(big[i], (800, 448), interpolation=cv2.INTER_LINEAR))
+    out = ctx.normalize_frames(dev(big), (800, 448), rotate=True)
+    for i in range(2):
+        same("rot+resize", out[i], R.normalize_frame(big[i], rotate=True))
+    g = golden_stage2
+    out = ctx.normalize_frames(dev(g["norm_in"][None]), (800, 448), rotate=True)
+    same("golden normalize", out[0], g["norm_out"])
+
+
+def test_masks_from_logits(ctx):
+    rng = np.random.default_rng(0)
+    logits = rng.normal(size=(2, 3, 512, 512)).astype(np.float32)
+    logits[0, :, :40] = 0.25                      # exact ties -> lowest index
+    roi = R.map_roi((800, 448))
+    pred, cable, tape = ctx.masks_from_logits(dev(logits), (448, 800), roi)
+    for i in range(2):
+        p, c, t = R.masks_from_logits(torch.from_numpy(logits[i]), (800, 448), roi)
+        same("pred", pred[i], p)
+        same("cable", cable[i], c)
+        same("tape", tape[i], t)
+
+
+@pytest.mark.parametrize("hw", [(448, 800), (37, 53), (64, 96)])
+def test_gauss_canny_edges(ctx, hw):
+    h, w = hw
+    fr = np.concatenate([S.frames_cable(1, h, w, seed=1), S.frames_noise(1, h, w, seed=2)])
+    gray = np.stack([cv2.cvtColor(f, cv2.COLOR_BGR2GRAY) for f in fr])
+    blur = ctx.gaussian5(dev(gray))
+    ref_blur = np.stack([cv2.GaussianBlur(g, (5, 5), 1.0) for g in gray])
+    same("gauss", blur, ref_blur)
+    for lo, hi in ((50, 150), (30, 100)):
+        e = ctx.canny(dev(ref_blur), lo, hi)
+        same(f"canny{lo}", e, np.stack([cv2.Canny(b, lo, hi) for b in ref_blur]))
+    same("sobel", ctx.sobel_edges(dev(gray)), np.stack([cvnp.sobel_edges(g) for g in gray]))
+    same("lap", ctx.laplacian_edges(dev(gray)), np.stack([cvnp.laplacian_edges(g) for g in gray]))
+
+
+@pytest.mark.parametrize("k", [2, 3, 5, 8, 25])
+def test_morphology(ctx, k):
+    se = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (k, k))
+    for h, w, fill in ((448, 800, 0.3), (50, 70, 0.05), (31, 33, 0.6), (448, 800, 0.002)):
+        b = np.stack([S.mask_blobs(h, w, seed=k + i, fill=fill) for i in range(2)])
+        d = dev(b)
+        same(f"dilate{k}", ctx.morph("dilate", k, d), np.stack([cv2.dilate(x, se) for x in b]))
+        same(f"erode{k}", ctx.morph("erode", k, d), np.stack([cv2.erode(x, se) for x in b]))
+        same(f"close{k}", ctx.morph("close", k, d), np.stack([cv2.morphologyEx(x, cv2.MORPH_CLOSE, se) for x in b]))
+        same(f"open{k}", ctx.morph("open", k, d), np.stack([cv2.morphologyEx(x, cv2.MORPH_OPEN, se) for x in b]))
+
+
+@pytest.mark.parametrize("hw,fill", [((448, 800), 0.3), ((447, 799), 0.45), ((33, 65), 0.6), ((448, 800), 0.02)])
+def test_ccl_labels_and_stats(ctx, hw, fill):
+    b = np.stack([S.mask_blobs(hw[0], hw[1], seed=9 + i, fill=fill) for i in range(2)])
+    n, lab, st = ctx.ccl(dev(b), max_labels=32768)
+    n, lab, st = n.cpu().numpy(), lab.cpu().numpy(), st.cpu().numpy()
+    for i in range(2):
+        rn, rl, rs, _ = cv2.connectedComponentsWithStats(b[i], connectivity=8)
+        assert n[i] == rn
+        same("labels", lab[i], rl)
+        same("stats", st[i, :rn], rs)
+
+
+@pytest.mark.parametrize("variant", ["standard", "enhanced"])
+def test_burr_stage_golden(ctx, variant, golden_stage2, golden_frames):
+    from unet_b200 import _lib
+    g = golden_stage2
+    for tag in ("cable", "speckle", "dots", "noise"):
+        fr = golden_frames[tag]
+        gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+        mask = g[f"{tag}_mask"]
+        c = ctx if gray.shape == (448, 800) else _lib.Context(0, 1, gray.shape, (512, 512))
+        if variant == "standard":
+            for sens in ("medium", "high"):
+                cfg = R.BURR_CONFIGS[sens]
+                out, px = c.burr(dev(gray[None]), dev(mask[None]), 0, _lib.standard_params(cfg["min_area"], cfg["max_area"]))
+                same(f"{tag} burr {sens}", out[0], g[f"{tag}_burr_{sens}"])
+                assert int(px[0]) == int(g[f"{tag}_burr_{sens}"].sum())
+            out, px = c.burr(dev(gray[None]), dev(np.zeros_like(mask)[None]), 0)
+            same(f"{tag} empty", out[0], g[f"{tag}_burr_empty"])
+        else:
+            out, px = c.burr(dev(gray[None]), dev(mask[None]), 1)
+            same(f"{tag} burr enh", out[0], g[f"{tag}_burr_enh"])
+            assert int(px[0]) == int(g[f"{tag}_burr_enh"].sum())
+
+
+def test_burr_stage_batched_vs_oracle(ctx):
+    fr = frames4()
+    gray = np.stack([cv2.cvtColor(f, cv2.COLOR_BGR2GRAY) for f in fr])
+    masks = np.stack([S.mask_cable_synth(448, 800), S.mask_blobs(448, 800, 3, 0.002),
+                      S.mask_cable_synth(448, 800, R.map_roi((800, 448))), S.mask_blobs(448, 800, 4, 0.01)])
+    out, px = ctx.burr(dev(gray), dev(masks), 0)
+    oute, pxe = ctx.burr(dev(gray), dev(masks), 1)
+    for i in range(4):
+        same(f"std[{i}]", out[i], R.burrs_standard(gray[i], masks[i]))
+        same(f"enh[{i}]", oute[i], R.burrs_enhanced(gray[i], masks[i]))
+    assert px.cpu().tolist() == [int(out[i].sum()) for i in range(4)]
+
+
+def test_function_contract():
+    """The reference-named functions accept numpy like the reference and return numpy."""
+    import unet_b200 as U
+    fr = S.frames_speckle(1, 448, 800, seed=5)[0]
+    gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+    mask = S.mask_blobs(448, 800, seed=3, fill=0.002)
+    same("detect_burrs_on_cable", U.detect_burrs_on_cable(gray, mask, {"min_area": 20, "max_area": 1000}),
+         R.burrs_standard(gray, mask, {"min_area": 20, "max_area": 1000}))
+    same("detect_burrs_enhanced", U.detect_burrs_enhanced(gray, mask, {"min_area": 50, "max_area": 500}),
+         R.burrs_enhanced(gray, mask))
+    x = U.preprocess_image(fr)
+    assert isinstance(x, torch.Tensor) and not x.is_cuda and x.dtype == torch.float32
+    same("preprocess_image", x.numpy(), R.preprocess(fr).numpy())
+    assert U.map_roi_to_original((800, 448)) == (218, 0, 421, 448)
+    same("bgr2gray", U.bgr2gray(fr), gray)

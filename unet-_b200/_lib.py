@@ -1,0 +1,301 @@
+"""ctypes binding of libunetb200.so (the C ABI declared in include/unetb200.h).
+
+The shared library is built in-tree by ``make -C unet-_b200/csrc`` (see
+__graft_entry__.build).  There is no fallback: if the library is missing, or the device
+is not sm_100, every entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libunetb200.so")
+_lib = None
+
+VARIANT_STANDARD, VARIANT_ENHANCED = 0, 1
+T_CLASSES = ("conv3x3", "net_glue", "prepost", "stencil_morph", "ccl")
+
+
+class UbError(RuntimeError):
+    pass
+
+
+class NamedTensor(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("data_host", C.c_void_p), ("numel", C.c_int64)]
+
+
+class Roi(C.Structure):
+    _fields_ = [("x1", C.c_int32), ("y1", C.c_int32), ("x2", C.c_int32), ("y2", C.c_int32)]
+
+
+class BurrParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("min_area", "max_area", "max_aspect", "min_side", "canny_low",
+                                         "canny_high", "band_k", "close_k", "open_k")]
+
+
+# name -> (restype, argtypes); must list every symbol include/unetb200.h declares
+_P = C.c_void_p
+_I = C.c_int
+SIGNATURES = {
+    "ub_create": (_I, [C.POINTER(_P), _I, _I, _I, _I, _I, _I, _I]),
+    "ub_destroy": (None, [_P]),
+    "ub_last_error": (C.c_char_p, [_P]),
+    "ub_version": (_I, []),
+    "ub_set_weights": (_I, [_P, C.POINTER(NamedTensor), _I]),
+    "ub_forward": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "ub_set_conv_impl": (_I, [_P, _I]),
+    "ub_preprocess": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
+    "ub_normalize_frames": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P]),
+    "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
+    "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_morph": (_I, [_P, _I, _I, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_ccl": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _P, _P]),
+    "ub_sobel_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_laplacian_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_burr": (_I, [_P, _I, _P, _P, _I, _I, _I, C.POINTER(BurrParams), _P, _P, _P]),
+    "ub_pipeline": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P, _P]),
+    "ub_pipeline_host": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P]),
+    "ub_debug_conv": (_I, [_P, _I, _P, _P, _I, _I, _I, _P, _P]),
+    "ub_debug_activation": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_timing_enable": (_I, [_P, _I]),
+    "ub_timing_read": (_I, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int64), _I]),
+    "ub_launch_count": (C.c_int64, [_P]),
+}
+
+
+def build(verbose: bool = False) -> str:
+    """Compile libunetb200.so for sm_100a with nvcc (cross-compiles without a GPU)."""
+    res = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "-j8"], capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout[-4000:])
+        print(res.stderr[-4000:])
+    if res.returncode != 0:
+        raise UbError("building libunetb200.so failed")
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise UbError(f"{LIB_PATH} is missing: build it with `make -C unet-_b200/csrc` "
+                          "(python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    if isinstance(t, torch.Tensor):
+        assert t.is_contiguous(), "tensor must be contiguous"
+        return t.data_ptr()
+    if isinstance(t, np.ndarray):
+        assert t.flags["C_CONTIGUOUS"]
+        return t.ctypes.data
+    return int(t)
+
+
+def _stream(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def standard_params(min_area=30, max_area=800) -> BurrParams:
+    """detect_burrs_on_cable constants (infer_two_stage_burr.py:78-117)."""
+    return BurrParams(min_area, max_area, 5, 4, 50, 150, 8, 3, 2)
+
+
+def enhanced_params(min_area=50, max_area=500) -> BurrParams:
+    """detect_burrs_enhanced constants (infer_enhanced_burr.py:82-136)."""
+    return BurrParams(min_area, max_area, 6, 5, 30, 100, 25, 5, 3)
+
+
+class Context:
+    """Owns one ub_ctx (device scratch for up to max_batch frames)."""
+
+    def __init__(self, device=0, max_batch=1, frame_hw=(448, 800), net_hw=(512, 512), num_classes=3):
+        if not torch.cuda.is_available():
+            raise UbError("no CUDA device: libunetb200 has no CPU fallback")
+        self.device = torch.device("cuda", device if isinstance(device, int) else (device.index or 0))
+        self.max_batch, self.frame_hw, self.net_hw, self.num_classes = max_batch, tuple(frame_hw), tuple(net_hw), num_classes
+        self._h = C.c_void_p()
+        self._check(lib().ub_create(C.byref(self._h), self.device.index, max_batch, frame_hw[0], frame_hw[1],
+                                    net_hw[0], net_hw[1], num_classes), None)
+        self._keep = None
+
+    # -- plumbing
+    def _check(self, code, h="self"):
+        if code != 0:
+            msg = lib().ub_last_error(self._h if h == "self" else None)
+            raise UbError(f"libunetb200 error {code}: {msg.decode() if msg else '?'}")
+
+    def close(self):
+        if self._h:
+            lib().ub_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dev(self, t, dtype):
+        assert t.is_cuda and t.dtype == dtype and t.is_contiguous(), (t.device, t.dtype)
+        return t.data_ptr()
+
+    @property
+    def stream(self):
+        return _stream(self.device)
+
+    # -- stage 1
+    def set_weights(self, state_dict):
+        items, keep = [], []
+        for k, v in state_dict.items():
+            if k.endswith("num_batches_tracked"):
+                continue
+            a = v.detach().to("cpu", torch.float32).contiguous()
+            keep.append(a)
+            items.append((k.encode(), a))
+        arr = (NamedTensor * len(items))()
+        for i, (k, a) in enumerate(items):
+            arr[i] = NamedTensor(k, a.data_ptr(), a.numel())
+        self._check(lib().ub_set_weights(self._h, arr, len(items)))
+
+    def set_conv_impl(self, impl: int):
+        self._check(lib().ub_set_conv_impl(self._h, impl))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        b, c, h, w = x.shape
+        assert c == 3
+        out = torch.empty((b, self.num_classes, h, w), dtype=torch.float32, device=x.device)
+        self._check(lib().ub_forward(self._h, self._dev(x, torch.float32), b, h, w, out.data_ptr(), self.stream))
+        return out
+
+    # -- pre / post
+    def preprocess(self, frames: torch.Tensor, want_x=True, want_gray=True):
+        b, h, w, _ = frames.shape
+        x = torch.empty((b, 3) + self.net_hw, dtype=torch.float32, device=frames.device) if want_x else None
+        g = torch.empty((b, h, w), dtype=torch.uint8, device=frames.device) if want_gray else None
+        self._check(lib().ub_preprocess(self._h, self._dev(frames, torch.uint8), b, h, w, _ptr(x), _ptr(g), self.stream))
+        return x, g
+
+    def normalize_frames(self, src: torch.Tensor, size_wh=(800, 448), rotate=False) -> torch.Tensor:
+        b, sh, sw, _ = src.shape
+        dst = torch.empty((b, size_wh[1], size_wh[0], 3), dtype=torch.uint8, device=src.device)
+        self._check(lib().ub_normalize_frames(self._h, self._dev(src, torch.uint8), b, sh, sw, int(rotate),
+                                              dst.data_ptr(), size_wh[1], size_wh[0], self.stream))
+        return dst
+
+    def masks_from_logits(self, logits: torch.Tensor, frame_hw, roi):
+        b, c, nh, nw = logits.shape
+        H, W = frame_hw
+        pred = torch.empty((b, nh, nw), dtype=torch.uint8, device=logits.device)
+        cable = torch.empty((b, H, W), dtype=torch.uint8, device=logits.device)
+        tape = torch.empty_like(cable)
+        r = Roi(*roi)
+        self._check(lib().ub_masks_from_logits(self._h, self._dev(logits, torch.float32), b, nh, nw, H, W, C.byref(r),
+                                               pred.data_ptr(), cable.data_ptr(), tape.data_ptr(), self.stream))
+        return pred, cable, tape
+
+    # -- stage 2 operators
+    def _u8op(self, fn, src, *args):
+        b, h, w = src.shape
+        dst = torch.empty_like(src)
+        self._check(fn(self._h, self._dev(src, torch.uint8), b, h, w, *args, dst.data_ptr(), self.stream))
+        return dst
+
+    def gaussian5(self, src):
+        return self._u8op(lib().ub_gaussian5, src)
+
+    def canny(self, src, low, high):
+        return self._u8op(lib().ub_canny, src, low, high)
+
+    def sobel_edges(self, gray, thresh=50):
+        return self._u8op(lib().ub_sobel_edges, gray, thresh)
+
+    def laplacian_edges(self, gray, thresh=15):
+        return self._u8op(lib().ub_laplacian_edges, gray, thresh)
+
+    def morph(self, op, k, src, value=1):
+        b, h, w = src.shape
+        dst = torch.empty_like(src)
+        code = {"dilate": 0, "erode": 1, "close": 2, "open": 3}[op]
+        self._check(lib().ub_morph(self._h, code, k, self._dev(src, torch.uint8), b, h, w, value, dst.data_ptr(), self.stream))
+        return dst
+
+    def ccl(self, src, max_labels=4096):
+        b, h, w = src.shape
+        labels = torch.empty((b, h, w), dtype=torch.int32, device=src.device)
+        stats = torch.empty((b, max_labels, 5), dtype=torch.int32, device=src.device)
+        n = torch.empty((b,), dtype=torch.int32, device=src.device)
+        self._check(lib().ub_ccl(self._h, self._dev(src, torch.uint8), b, h, w, labels.data_ptr(), stats.data_ptr(),
+                                 max_labels, n.data_ptr(), self.stream))
+        return n, labels, stats
+
+    def burr(self, gray, mask, variant=VARIANT_STANDARD, params=None):
+        b, h, w = gray.shape
+        out = torch.empty_like(gray)
+        px = torch.empty((b,), dtype=torch.int32, device=gray.device)
+        p = params if params is not None else (enhanced_params() if variant else standard_params())
+        self._check(lib().ub_burr(self._h, variant, self._dev(gray, torch.uint8), self._dev(mask, torch.uint8), b, h, w,
+                                  C.byref(p), out.data_ptr(), px.data_ptr(), self.stream))
+        return out, px
+
+    # -- whole step
+    def pipeline(self, frames: torch.Tensor, variant=VARIANT_STANDARD, roi=None, params=None, want_masks=False):
+        b = frames.shape[0]
+        assert tuple(frames.shape[1:3]) == self.frame_hw
+        stats = torch.empty((b, 4), dtype=torch.int32, device=frames.device)
+        masks = torch.empty((b, 3) + self.frame_hw, dtype=torch.uint8, device=frames.device) if want_masks else None
+        r = C.byref(Roi(*roi)) if roi is not None else None
+        p = C.byref(params) if params is not None else None
+        self._check(lib().ub_pipeline(self._h, self._dev(frames, torch.uint8), b, variant, r, p, stats.data_ptr(),
+                                      _ptr(masks), self.stream))
+        return stats, masks
+
+    def pipeline_host(self, frames, stats_out, variant=VARIANT_STANDARD, roi=None, params=None, masks_out=None):
+        """frames / stats_out: pinned host tensors or numpy arrays.  Synchronous."""
+        b = frames.shape[0]
+        r = C.byref(Roi(*roi)) if roi is not None else None
+        p = C.byref(params) if params is not None else None
+        self._check(lib().ub_pipeline_host(self._h, _ptr(frames), b, variant, r, p, _ptr(stats_out), _ptr(masks_out)))
+        return stats_out
+
+    # -- test hooks
+    def debug_conv(self, layer, x0, x1, cout):
+        b, _, h, w = x0.shape
+        out = torch.empty((b, cout, h, w), dtype=torch.float32, device=x0.device)
+        self._check(lib().ub_debug_conv(self._h, layer, self._dev(x0, torch.float32),
+                                        self._dev(x1, torch.float32) if x1 is not None else None, b, h, w,
+                                        out.data_ptr(), self.stream))
+        return out
+
+    def debug_activation(self, index, b, c, h, w):
+        out = torch.empty((b, c, h, w), dtype=torch.float32, device=self.device)
+        self._check(lib().ub_debug_activation(self._h, index, b, c, h, w, out.data_ptr(), self.stream))
+        return out
+
+    # -- instrumentation
+    def timing_enable(self, on=True):
+        self._check(lib().ub_timing_enable(self._h, int(on)))
+
+    def timing_read(self, reset=True):
+        ms = (C.c_float * 5)()
+        n = (C.c_int64 * 5)()
+        self._check(lib().ub_timing_read(self._h, ms, n, int(reset)))
+        return {k: (ms[i], n[i]) for i, k in enumerate(T_CLASSES)}
+
+    def launch_count(self) -> int:
+        return int(lib().ub_launch_count(self._h))

@@ -1,0 +1,426 @@
+// api.cu -- the C ABI of libunetb200.so (include/unetb200.h): context, weight folding /
+// repacking, and thin wrappers that validate arguments and enqueue the kernels.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+#include <map>
+#include "common.cuh"
+
+thread_local std::string g_last_error;
+
+int ub_fail(ub_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+// ---------------------------------------------------------------- timing
+TimeScope::TimeScope(ub_ctx* ctx, int cls, cudaStream_t st) : c(ctx), s(st) {
+  if (!c->tm.on) return;
+  auto get = [&]() {
+    cudaEvent_t e;
+    if (!c->tm.pool.empty()) { e = c->tm.pool.back(); c->tm.pool.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+  };
+  Timing::Rec r{get(), get(), cls};
+  cudaEventRecord(r.a, s);
+  c->tm.recs.push_back(r);
+  idx = (int)c->tm.recs.size() - 1;
+}
+TimeScope::~TimeScope() {
+  if (idx >= 0) cudaEventRecord(c->tm.recs[idx].b, s);
+}
+
+// forward declarations of functions defined in other translation units
+void resize_cache_free(ub_ctx* ctx);
+int normalize_frames_impl(ub_ctx*, const uint8_t*, int, int, int, int, uint8_t*, int, int, cudaStream_t);
+int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t);
+int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
+int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
+int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
+int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
+
+// ---------------------------------------------------------------- layer tables
+namespace {
+struct LayerDef { const char* block; int idx; int cin0, cin1, cout, kc, bn; int real_cin0; };
+// cin0 of the first layer is the 3 input channels zero-padded to 16 (one UMMA K step)
+const LayerDef kLayers[18] = {
+    {"conv0_0", 1, 16, 0, 32, 16, 32, 3},     {"conv0_0", 2, 32, 0, 32, 32, 32, 32},
+    {"conv1_0", 1, 32, 0, 64, 32, 64, 32},    {"conv1_0", 2, 64, 0, 64, 32, 64, 64},
+    {"conv2_0", 1, 64, 0, 128, 16, 128, 64},  {"conv2_0", 2, 128, 0, 128, 16, 128, 128},
+    {"conv3_0", 1, 128, 0, 256, 16, 256, 128}, {"conv3_0", 2, 256, 0, 256, 16, 256, 256},
+    {"conv4_0", 1, 256, 0, 512, 16, 256, 256}, {"conv4_0", 2, 512, 0, 512, 16, 256, 512},
+    {"conv3_1", 1, 256, 512, 256, 16, 256, 256}, {"conv3_1", 2, 256, 0, 256, 16, 256, 256},
+    {"conv2_2", 1, 128, 256, 128, 16, 128, 128}, {"conv2_2", 2, 128, 0, 128, 16, 128, 128},
+    {"conv1_3", 1, 64, 128, 64, 32, 64, 64},  {"conv1_3", 2, 64, 0, 64, 32, 64, 64},
+    {"conv0_4", 1, 32, 64, 32, 32, 32, 32},   {"conv0_4", 2, 32, 0, 32, 32, 32, 32},
+};
+// activation buffers: channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu
+const int kActC[23] = {16, 32, 32, 32, 64, 64, 64, 128, 128, 128, 256, 256, 256, 512, 512, 512, 256, 256, 128, 128, 64, 64, 0};
+const int kActL[23] = {0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
+
+cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
+
+template <class T>
+int dmalloc(ub_ctx* ctx, T** p, size_t n) {
+  cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+  if (e != cudaSuccess) return ub_fail(ctx, UB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", n * sizeof(T), cudaGetErrorString(e));
+  e = cudaMemset(*p, 0, n * sizeof(T));
+  if (e != cudaSuccess) return ub_fail(ctx, UB_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e));
+  return UB_OK;
+}
+}  // namespace
+
+#define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
+#define NEED_CTX(ctx) if (!(ctx)) return ub_fail(nullptr, UB_ERR_ARG, "null context")
+
+extern "C" {
+
+int ub_version(void) { return 100; }
+
+const char* ub_last_error(ub_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w, int net_h, int net_w, int num_classes) {
+  if (!out) return ub_fail(nullptr, UB_ERR_ARG, "out is null");
+  *out = nullptr;
+  if (max_batch < 1 || frame_h < 1 || frame_w < 1 || net_h < 16 || net_w < 16 || (net_h & 15) || (net_w & 15) ||
+      num_classes < 1 || num_classes > 8)
+    return ub_fail(nullptr, UB_ERR_ARG, "bad sizes: batch %d frame %dx%d net %dx%d classes %d (net dims must be multiples of 16)",
+                   max_batch, frame_h, frame_w, net_h, net_w, num_classes);
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) return ub_fail(nullptr, UB_ERR_CUDA, "cudaGetDeviceProperties(%d): %s", device, cudaGetErrorString(e));
+  if (prop.major != 10)
+    return ub_fail(nullptr, UB_ERR_ARCH, "device %d is sm_%d%d; libunetb200 is built for sm_100a only (no fallback path)",
+                   device, prop.major, prop.minor);
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return ub_fail(nullptr, UB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+  ub_ctx* c = new ub_ctx();
+  c->device = device; c->sm_count = prop.multiProcessorCount;
+  c->max_batch = max_batch; c->frame_h = frame_h; c->frame_w = frame_w; c->net_h = net_h; c->net_w = net_w;
+  c->num_classes = num_classes;
+  const char* impl = getenv("UB_CONV_IMPL");
+  if (impl) c->conv_impl = atoi(impl);
+  int r = UB_OK;
+  auto fail = [&](int code) { ub_destroy(c); return code; };
+  for (int i = 0; i < 22 && r == UB_OK; ++i) {
+    size_t bytes = pp_bytes(max_batch, kActC[i], net_h >> kActL[i], net_w >> kActL[i]);
+    r = dmalloc(c, &c->act[i], bytes / sizeof(__nv_bfloat16));
+  }
+  if (r) return fail(r);
+  const size_t fpix = (size_t)max_batch * frame_h * frame_w, npix = (size_t)max_batch * net_h * net_w;
+  const size_t ipl = (size_t)max_batch * (frame_h + 1) * (frame_w + 1);
+  if ((r = dmalloc(c, &c->d_frames, fpix * 3)) || (r = dmalloc(c, &c->d_gray, fpix)) || (r = dmalloc(c, &c->d_pred, npix)) ||
+      (r = dmalloc(c, &c->d_lab[0], ipl)) || (r = dmalloc(c, &c->d_lab[1], ipl)) || (r = dmalloc(c, &c->d_comp, fpix * 6)) ||
+      (r = dmalloc(c, &c->d_counts, (size_t)max_batch * 16)) || (r = dmalloc(c, &c->d_stats, (size_t)max_batch * 4)) ||
+      (r = dmalloc(c, &c->d_logits, npix * num_classes)))
+    return fail(r);
+  for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
+  for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
+  if (r) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK) return fail(r);
+  e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
+  *out = c;
+  return UB_OK;
+}
+
+void ub_destroy(ub_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (auto& p : c->act) cudaFree(p);
+  for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.bias); }
+  cudaFree(c->head_w); cudaFree(c->head_b);
+  cudaFree(c->d_frames); cudaFree(c->d_gray); cudaFree(c->d_pred);
+  for (auto& p : c->d_mask) cudaFree(p);
+  for (auto& p : c->d_tmp) cudaFree(p);
+  for (auto& p : c->d_lab) cudaFree(p);
+  cudaFree(c->d_comp); cudaFree(c->d_counts); cudaFree(c->d_stats); cudaFree(c->d_logits);
+  resize_cache_free(c);
+  for (auto& r : c->tm.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (auto& e : c->tm.pool) cudaEventDestroy(e);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+int ub_set_conv_impl(ub_ctx* ctx, int impl) {
+  NEED_CTX(ctx);
+  if (impl < 0 || impl > 2) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A)", impl);
+  ctx->conv_impl = impl;
+  return UB_OK;
+}
+
+// Fold eval-mode BN into the conv, repack to bf16 [cout/bn][kblock][tap][kc/8][bn][8].
+int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
+  NEED_CTX(ctx);
+  if (!t || n <= 0) return ub_fail(ctx, UB_ERR_ARG, "no tensors");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::map<std::string, const ub_named_tensor*> m;
+  for (int i = 0; i < n; ++i) if (t[i].name) m[t[i].name] = &t[i];
+  auto get = [&](const std::string& name, int64_t numel, const float** out) -> int {
+    auto it = m.find(name);
+    if (it == m.end()) return ub_fail(ctx, UB_ERR_ARG, "missing key \"%s\" in state_dict", name.c_str());
+    if (it->second->numel != numel)
+      return ub_fail(ctx, UB_ERR_ARG, "size mismatch for %s: got %lld elements, expected %lld", name.c_str(),
+                     (long long)it->second->numel, (long long)numel);
+    *out = static_cast<const float*>(it->second->data_host);
+    return UB_OK;
+  };
+  for (int li = 0; li < 18; ++li) {
+    const LayerDef& d = kLayers[li];
+    const std::string cv = std::string(d.block) + ".conv" + std::to_string(d.idx);
+    const std::string bn = std::string(d.block) + ".bn" + std::to_string(d.idx);
+    const int cin_real = d.real_cin0 + d.cin1, cin_pad = d.cin0 + d.cin1;
+    const float *w, *b, *g, *be, *mu, *var;
+    RUN(get(cv + ".weight", (int64_t)d.cout * cin_real * 9, &w));
+    RUN(get(cv + ".bias", d.cout, &b));
+    RUN(get(bn + ".weight", d.cout, &g));
+    RUN(get(bn + ".bias", d.cout, &be));
+    RUN(get(bn + ".running_mean", d.cout, &mu));
+    RUN(get(bn + ".running_var", d.cout, &var));
+    const int kbn = cin_pad / d.kc, cpk = d.kc / 8, nnt = d.cout / d.bn;
+    std::vector<__nv_bfloat16> wp((size_t)d.cout * cin_pad * 9);
+    std::vector<float> bias(d.cout);
+    for (int co = 0; co < d.cout; ++co) {
+      const double scale = (double)g[co] / sqrt((double)var[co] + 1e-5);
+      bias[co] = (float)(((double)b[co] - (double)mu[co]) * scale + (double)be[co]);
+      const int nt = co / d.bn, r = co % d.bn;
+      for (int ci = 0; ci < cin_pad; ++ci) {
+        // padded channel -> real channel of the torch weight (only layer 0 has padding)
+        int cr = -1;
+        if (ci < d.cin0) { if (ci < d.real_cin0) cr = ci; }
+        else cr = d.real_cin0 + (ci - d.cin0);
+        const int kb = ci / d.kc, cc = (ci % d.kc) / 8, j = ci % 8;
+        for (int tap = 0; tap < 9; ++tap) {
+          const float v = cr < 0 ? 0.f : (float)((double)w[((size_t)co * cin_real + cr) * 9 + tap] * scale);
+          const size_t o = ((((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * d.bn + r) * 8) + j;
+          wp[o] = __float2bfloat16_rn(v);
+        }
+      }
+    }
+    (void)nnt;
+    ConvLayer& L = ctx->conv[li];
+    L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn;
+    if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
+    if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
+    UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  const float *hw, *hb;
+  RUN(get("final.weight", (int64_t)ctx->num_classes * 32, &hw));
+  RUN(get("final.bias", ctx->num_classes, &hb));
+  if (!ctx->head_w) RUN(dmalloc(ctx, &ctx->head_w, (size_t)ctx->num_classes * 32));
+  if (!ctx->head_b) RUN(dmalloc(ctx, &ctx->head_b, (size_t)ctx->num_classes));
+  UB_CUDA(ctx, cudaMemcpy(ctx->head_w, hw, sizeof(float) * ctx->num_classes * 32, cudaMemcpyHostToDevice));
+  UB_CUDA(ctx, cudaMemcpy(ctx->head_b, hb, sizeof(float) * ctx->num_classes, cudaMemcpyHostToDevice));
+  ctx->weights_set = true;
+  return UB_OK;
+}
+
+static int check_net_shape(ub_ctx* ctx, int B, int H, int W) {
+  if (B < 1 || B > ctx->max_batch) return ub_fail(ctx, UB_ERR_ARG, "batch %d outside [1,%d]", B, ctx->max_batch);
+  if (H < 16 || W < 16 || (H & 15) || (W & 15)) return ub_fail(ctx, UB_ERR_ARG, "net input %dx%d must be multiples of 16", H, W);
+  // buffers are sized for net_h x net_w; any shape whose padded planes are not larger fits
+  for (int l = 0; l < 5; ++l)
+    if (pp_layout(H >> l, W >> l).Ppl > pp_layout(ctx->net_h >> l, ctx->net_w >> l).Ppl)
+      return ub_fail(ctx, UB_ERR_ARG, "net input %dx%d exceeds the context's %dx%d", H, W, ctx->net_h, ctx->net_w);
+  if (!ctx->weights_set) return ub_fail(ctx, UB_ERR_STATE, "ub_set_weights has not been called");
+  return UB_OK;
+}
+
+int ub_forward(ub_ctx* ctx, const float* x, int B, int H, int W, float* logits, void* stream) {
+  NEED_CTX(ctx);
+  if (!x || !logits) return ub_fail(ctx, UB_ERR_ARG, "null tensor");
+  RUN(check_net_shape(ctx, B, H, W));
+  cudaStream_t st = as_stream(stream);
+  RUN(nchw_to_pp(ctx, x, B, 3, H, W, ctx->act[0], 16, st));
+  return net_forward_pp(ctx, B, H, W, logits, nullptr, st);
+}
+
+int ub_preprocess(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, float* x_nchw, uint8_t* gray, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || B < 1 || H < 2 || W < 2) return ub_fail(ctx, UB_ERR_ARG, "bad frames argument");
+  return preprocess_frames(ctx, frames, B, H, W, ctx->net_h, ctx->net_w, nullptr, x_nchw, gray, as_stream(stream));
+}
+
+int ub_normalize_frames(ub_ctx* ctx, const uint8_t* src, int B, int sh, int sw, int rot, uint8_t* dst, int dh, int dw, void* stream) {
+  NEED_CTX(ctx);
+  if (!src || !dst || B < 1 || sh < 2 || sw < 2 || dh < 1 || dw < 1) return ub_fail(ctx, UB_ERR_ARG, "bad argument");
+  return normalize_frames_impl(ctx, src, B, sh, sw, rot, dst, dh, dw, as_stream(stream));
+}
+
+int ub_masks_from_logits(ub_ctx* ctx, const float* logits, int B, int nh, int nw, int H, int W, const ub_roi* roi,
+                         uint8_t* pred, uint8_t* cable, uint8_t* tape, void* stream) {
+  NEED_CTX(ctx);
+  if (!logits || !roi || !cable || !tape) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (B > ctx->max_batch || (size_t)nh * nw > (size_t)ctx->net_h * ctx->net_w) return ub_fail(ctx, UB_ERR_ARG, "shape exceeds context");
+  cudaStream_t st = as_stream(stream);
+  uint8_t* p = pred ? pred : ctx->d_pred;
+  RUN(argmax_logits(ctx, logits, B, ctx->num_classes, nh, nw, p, st));
+  return masks_from_pred(ctx, p, B, nh, nw, H, W, *roi, cable, tape, nullptr, st);
+}
+
+static int check_frame_shape(ub_ctx* ctx, int B, int H, int W) {
+  if (B < 1 || B > ctx->max_batch || H < 1 || W < 1 || (size_t)H * W > (size_t)ctx->frame_h * ctx->frame_w)
+    return ub_fail(ctx, UB_ERR_ARG, "frames %dx%dx%d exceed the context (%d x %dx%d)", B, H, W, ctx->max_batch, ctx->frame_h, ctx->frame_w);
+  return UB_OK;
+}
+
+int ub_gaussian5(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return gaussian5(ctx, src, dst, B, H, W, as_stream(stream));
+}
+
+int ub_canny(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int low, int high, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return canny(ctx, src, dst, ctx->d_tmp[3], ctx->d_lab[0], B, H, W, low, high, as_stream(stream));
+}
+
+int ub_morph(ub_ctx* ctx, int op, int k, const uint8_t* src, int B, int H, int W, int value, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return morph_op(ctx, op, k, src, dst, ctx->d_tmp[3], B, H, W, value, as_stream(stream));
+}
+
+int ub_ccl(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int32_t* labels, int32_t* stats, int max_labels,
+           int32_t* n_labels, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return ccl_export(ctx, src, B, H, W, labels, stats, max_labels, n_labels, as_stream(stream));
+}
+
+int ub_sobel_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int thresh, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return enh_edges(ctx, gray, B, H, W, 1, thresh, 0, nullptr, dst, as_stream(stream));
+}
+int ub_laplacian_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int thresh, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return enh_edges(ctx, gray, B, H, W, 2, 0, thresh, nullptr, dst, as_stream(stream));
+}
+
+static ub_burr_params default_params(int variant) {
+  ub_burr_params p;
+  if (variant == UB_VARIANT_ENHANCED) p = {50, 500, 6, 5, 30, 100, 25, 5, 3};
+  else p = {30, 800, 5, 4, 50, 150, 8, 3, 2};
+  return p;
+}
+
+int ub_burr(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
+            const ub_burr_params* params, uint8_t* burr, int32_t* burr_px, void* stream) {
+  NEED_CTX(ctx);
+  if (!gray || !mask || !burr) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  cudaStream_t st = as_stream(stream);
+  ub_burr_params p = params ? *params : default_params(variant);
+  if (burr_px) UB_CUDA(ctx, cudaMemsetAsync(burr_px, 0, sizeof(int32_t) * B, st));
+  return burr_stage(ctx, variant, gray, mask, B, H, W, p, burr, burr_px, 1, st);
+}
+
+int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub_roi* roi, const ub_burr_params* params,
+                int32_t* frame_stats, uint8_t* masks, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || !frame_stats) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  const int H = ctx->frame_h, W = ctx->frame_w, nh = ctx->net_h, nw = ctx->net_w;
+  RUN(check_net_shape(ctx, B, nh, nw));
+  cudaStream_t st = as_stream(stream);
+  ub_roi r;
+  if (roi) r = *roi;
+  else if (variant == UB_VARIANT_ENHANCED) r = {200, 0, 600, 448};                     // VERTICAL_ROI, infer_enhanced_burr.py:23-28
+  else r = {(int)(140 * ((double)W / 512)), 0, (int)(270 * ((double)W / 512)), (int)(512 * ((double)H / 512))};   // :37-47
+  ub_burr_params p = params ? *params : default_params(variant);
+  const size_t fpix = (size_t)H * W;
+  uint8_t *cable = ctx->d_mask[0], *tape = ctx->d_mask[1], *burr = ctx->d_mask[2];
+  RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, ctx->act[0], nullptr, ctx->d_gray, st));
+  RUN(net_forward_pp(ctx, B, nh, nw, nullptr, ctx->d_pred, st));
+  RUN(masks_from_pred(ctx, ctx->d_pred, B, nh, nw, H, W, r, cable, tape, frame_stats, st));
+  RUN(burr_stage(ctx, variant, ctx->d_gray, cable, B, H, W, p, burr, frame_stats + 3, 4, st));
+  if (masks) {
+    for (int k = 0; k < 3; ++k)
+      UB_CUDA(ctx, cudaMemcpy2DAsync(masks + k * fpix, 3 * fpix, ctx->d_mask[k], fpix, fpix, B, cudaMemcpyDeviceToDevice, st));
+  }
+  return UB_OK;
+}
+
+int ub_pipeline_host(ub_ctx* ctx, const uint8_t* frames_host, int B, int variant, const ub_roi* roi,
+                     const ub_burr_params* params, int32_t* stats_host, uint8_t* masks_host) {
+  NEED_CTX(ctx);
+  if (!frames_host || !stats_host) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (B < 1 || B > ctx->max_batch) return ub_fail(ctx, UB_ERR_ARG, "batch %d outside [1,%d]", B, ctx->max_batch);
+  cudaStream_t st = ctx->own_stream;
+  const size_t fbytes = (size_t)ctx->frame_h * ctx->frame_w * 3;
+  UB_CUDA(ctx, cudaMemcpyAsync(ctx->d_frames, frames_host, fbytes * B, cudaMemcpyHostToDevice, st));
+  RUN(ub_pipeline(ctx, ctx->d_frames, B, variant, roi, params, ctx->d_stats, nullptr, st));
+  UB_CUDA(ctx, cudaMemcpyAsync(stats_host, ctx->d_stats, sizeof(int32_t) * 4 * B, cudaMemcpyDeviceToHost, st));
+  if (masks_host) {
+    const size_t fpix = (size_t)ctx->frame_h * ctx->frame_w;
+    for (int k = 0; k < 3; ++k)
+      UB_CUDA(ctx, cudaMemcpy2DAsync(masks_host + k * fpix, 3 * fpix, ctx->d_mask[k], fpix, fpix, B, cudaMemcpyDeviceToHost, st));
+  }
+  UB_CUDA(ctx, cudaStreamSynchronize(st));
+  return UB_OK;
+}
+
+int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0, const float* x1, int B, int H, int W, float* out, void* stream) {
+  NEED_CTX(ctx);
+  if (layer < 0 || layer > 17 || !x0 || !out) return ub_fail(ctx, UB_ERR_ARG, "bad argument");
+  if (!ctx->weights_set) return ub_fail(ctx, UB_ERR_STATE, "ub_set_weights has not been called");
+  const LayerDef& d = kLayers[layer];
+  const int lvl = layer < 10 ? layer / 2 : (layer < 12 ? 3 : layer < 14 ? 2 : layer < 16 ? 1 : 0);
+  if (B > ctx->max_batch || pp_layout(H, W).Ppl > pp_layout(ctx->net_h >> lvl, ctx->net_w >> lvl).Ppl)
+    return ub_fail(ctx, UB_ERR_ARG, "shape exceeds the context at pyramid level %d", lvl);
+  if ((d.cin1 != 0) != (x1 != nullptr)) return ub_fail(ctx, UB_ERR_ARG, "layer %d takes %d sources", layer, d.cin1 ? 2 : 1);
+  cudaStream_t st = as_stream(stream);
+  // scratch: buffers of the same level that are large enough: in0 -> x/skip slot, in1 -> up slot, out -> t slot
+  static const int in0[5] = {2, 5, 8, 11, 14}, in1[5] = {21, 19, 17, 15, 15}, outb[5] = {1, 4, 7, 10, 13};
+  __nv_bfloat16* s0 = layer == 0 ? ctx->act[0] : ctx->act[in0[lvl]];
+  RUN(nchw_to_pp(ctx, x0, B, d.real_cin0, H, W, s0, d.cin0, st));
+  if (x1) RUN(nchw_to_pp(ctx, x1, B, d.cin1, H, W, ctx->act[in1[lvl]], d.cin1, st));
+  ConvArgs a{};
+  a.src0 = s0; a.src1 = x1 ? ctx->act[in1[lvl]] : nullptr; a.out = ctx->act[outb[lvl]]; a.B = B; a.H = H; a.W = W;
+  RUN(ctx->conv_impl == 1 ? conv3x3_simt(ctx, ctx->conv[layer], a, st) : conv3x3_tc(ctx, ctx->conv[layer], a, st));
+  return pp_to_nchw(ctx, ctx->act[outb[lvl]], B, d.cout, H, W, out, st);
+}
+
+int ub_debug_activation(ub_ctx* ctx, int index, int B, int C, int H, int W, float* out, void* stream) {
+  NEED_CTX(ctx);
+  if (index < 0 || index > 21 || !out || C > kActC[index]) return ub_fail(ctx, UB_ERR_ARG, "bad argument");
+  return pp_to_nchw(ctx, ctx->act[index], B, C, H, W, out, as_stream(stream));
+}
+
+int64_t ub_launch_count(ub_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int ub_timing_enable(ub_ctx* ctx, int on) {
+  NEED_CTX(ctx);
+  ctx->tm.on = on != 0;
+  return UB_OK;
+}
+
+int ub_timing_read(ub_ctx* ctx, float* ms, int64_t* launches, int reset) {
+  NEED_CTX(ctx);
+  UB_CUDA(ctx, cudaDeviceSynchronize());
+  for (auto& r : ctx->tm.recs) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ctx->tm.ms[r.cls] += t; ctx->tm.launches[r.cls] += 1; }
+    ctx->tm.pool.push_back(r.a); ctx->tm.pool.push_back(r.b);
+  }
+  ctx->tm.recs.clear();
+  for (int i = 0; i < UB_T_NCLASS; ++i) {
+    if (ms) ms[i] = ctx->tm.ms[i];
+    if (launches) launches[i] = ctx->tm.launches[i];
+    if (reset) { ctx->tm.ms[i] = 0; ctx->tm.launches[i] = 0; }
+  }
+  return UB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,159 @@
+// common.cuh -- shared declarations of libunetb200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/unetb200.h"
+
+// ---------------------------------------------------------------------------------
+// Activation layout ("pixel-planar, zero-padded", PP)
+//
+// A feature map [B, C, H, W] is stored in bf16 as  [B][C/8][Ppl][8]:
+// for every image and every group of 8 channels ("chunk") one plane of Ppl positions,
+// 16 bytes per position.  Position of pixel (y,x):  p = G + (y+1)*(W+2) + (x+1), i.e.
+// the plane is the image with a one-pixel zero border, flattened row-major, preceded by
+// a guard of G >= W+3 positions and followed by a guard of >= 128 + W+3 positions.
+//
+// Why: a 3x3 tap (ky,kx) of ANY output position p is the input position
+// p + (ky-1)*(W+2) + (kx-1) -- a constant offset, borders included.  A conv is then nine
+// shifted GEMMs over a flat position axis: a tile of 128 consecutive positions is a
+// UMMA M=128 operand whose rows are 16 B apart (no-swizzle K-major core matrices), the
+// tap shift is a plain address offset, and every global->shared move is a contiguous
+// 1-D bulk copy (no tensor map, no im2col).  Outputs computed at border positions are
+// garbage and are overwritten with zeros by the epilogue, which keeps the zero border.
+// ---------------------------------------------------------------------------------
+struct PPLayout {
+  int H, W;        // image size
+  int pitch;       // W + 2
+  int G;           // leading guard (positions), multiple of 8
+  int npos;        // (H+2)*(W+2)
+  int ntiles;      // ceil(npos / 128)
+  int Ppl;         // positions per plane, multiple of 8
+};
+
+static inline PPLayout pp_layout(int H, int W) {
+  PPLayout L;
+  L.H = H; L.W = W; L.pitch = W + 2;
+  L.G = ((W + 3) + 7) & ~7;
+  L.npos = (H + 2) * (W + 2);
+  L.ntiles = (L.npos + 127) / 128;
+  L.Ppl = ((L.G + L.ntiles * 128 + (W + 3) + 8) + 7) & ~7;
+  return L;
+}
+static inline size_t pp_bytes(int B, int C, int H, int W) {
+  PPLayout L = pp_layout(H, W);
+  return (size_t)B * (C / 8) * L.Ppl * 16;
+}
+
+// ---------------------------------------------------------------------------------
+// Conv layer description (weights already folded / repacked on the device)
+// ---------------------------------------------------------------------------------
+struct ConvLayer {
+  int cin0, cin1;      // channels of source 0 (skip) and source 1 (upsampled); cin1 may be 0
+  int cout;
+  int kc;              // channels per k-block (16 / 32 / 64); divides cin0 and cin1
+  int bn;              // N tile (<= 256); divides cout
+  // weights bf16 [cout/bn][kblocks][9 taps][kc/8][bn][8], bias fp32 [cout]
+  __nv_bfloat16* w = nullptr;
+  float* bias = nullptr;
+};
+
+// ---------------------------------------------------------------------------------
+// Context
+// ---------------------------------------------------------------------------------
+struct Timing {
+  bool on = false;
+  struct Rec { cudaEvent_t a, b; int cls; };
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool;
+  float ms[UB_T_NCLASS] = {0};
+  int64_t launches[UB_T_NCLASS] = {0};
+};
+
+struct ub_ctx {
+  int device = 0, sm_count = 148;
+  int max_batch = 0, frame_h = 0, frame_w = 0, net_h = 0, net_w = 0, num_classes = 3;
+  int conv_impl = 0;                 // 0 tcgen05, 1 simt, 2 tcgen05 with aligned A segments
+  int64_t launches = 0;              // kernels launched so far
+  std::string err;
+  bool weights_set = false;
+  ConvLayer conv[18];
+  float* head_w = nullptr;           // [num_classes][32] fp32
+  float* head_b = nullptr;           // [num_classes]
+  // activation arena (PP layout, sized for max_batch at net_h x net_w)
+  __nv_bfloat16* act[24] = {nullptr};
+  // pre/post + stage-2 scratch
+  uint8_t* d_frames = nullptr;       // [B,fh,fw,3]   (ub_pipeline_host staging)
+  uint8_t* d_gray = nullptr;         // [B,fh,fw]
+  uint8_t* d_pred = nullptr;         // [B,nh,nw]
+  uint8_t* d_mask[3] = {nullptr};    // cable, tape, burr [B,fh,fw]
+  uint8_t* d_tmp[4] = {nullptr};     // u8 planes [B,fh,fw]
+  int32_t* d_lab[2] = {nullptr};     // i32 planes [B,fh,fw]
+  int32_t* d_comp = nullptr;         // per-pixel component accumulators
+  int32_t* d_counts = nullptr;       // small per-frame counters
+  int32_t* d_stats = nullptr;        // [B,4]
+  float* d_logits = nullptr;         // [B,C,nh,nw] fp32 (module path / debug)
+  int* d_rs_tab = nullptr;           // resize coefficient tables
+  void* cache = nullptr;             // host-side cache of resize tables (ResizeCache*)
+  cudaStream_t own_stream = nullptr;
+  Timing tm;
+};
+
+extern thread_local std::string g_last_error;
+int ub_fail(ub_ctx* ctx, int code, const char* fmt, ...);
+
+#define UB_CUDA(ctx, call)                                                              \
+  do {                                                                                  \
+    cudaError_t e__ = (call);                                                           \
+    if (e__ != cudaSuccess)                                                             \
+      return ub_fail(ctx, UB_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call,     \
+                     cudaGetErrorString(e__));                                          \
+  } while (0)
+
+// after a group of n kernel launches: count them and surface launch errors
+#define UB_CHECK_LAUNCH_N(ctx, n) do { (ctx)->launches += (n); UB_CUDA(ctx, cudaGetLastError()); } while (0)
+#define UB_CHECK_LAUNCH(ctx) UB_CHECK_LAUNCH_N(ctx, 1)
+
+// RAII bracket that times one kernel class with CUDA events when timing is enabled.
+struct TimeScope {
+  ub_ctx* c; cudaStream_t s; int idx = -1;
+  TimeScope(ub_ctx* ctx, int cls, cudaStream_t st);
+  ~TimeScope();
+};
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// ---- entry points implemented across translation units ---------------------------
+// conv_simt.cu / conv_tc.cu : out = relu(conv3x3(cat(src0,src1)) + bias), PP layout in/out.
+// If head_w != nullptr (cout must be 32) the 1x1 head is fused: logits fp32 NCHW and/or
+// pred u8 are written instead of `out`.
+struct ConvArgs {
+  const __nv_bfloat16* src0; const __nv_bfloat16* src1; __nv_bfloat16* out;
+  int B, H, W;
+  const float* head_w; const float* head_b; int num_classes;
+  float* logits; uint8_t* pred;
+};
+int conv3x3_simt(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
+int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
+int conv_tc_init(ub_ctx* ctx);
+
+// net_glue.cu
+int nchw_to_pp(ub_ctx*, const float* x, int B, int C, int H, int W, __nv_bfloat16* out, int Cpad, cudaStream_t);
+int pp_to_nchw(ub_ctx*, const __nv_bfloat16* in, int B, int C, int H, int W, float* out, cudaStream_t);
+int maxpool2_pp(ub_ctx*, const __nv_bfloat16* in, int B, int C, int H, int W, __nv_bfloat16* out, cudaStream_t);
+int upsample2_pp(ub_ctx*, const __nv_bfloat16* in, int B, int C, int H, int W, __nv_bfloat16* out, cudaStream_t);
+int net_forward_pp(ub_ctx*, int B, int H, int W, float* logits, uint8_t* pred, cudaStream_t);
+
+// preprocess.cu
+int preprocess_frames(ub_ctx*, const uint8_t* frames, int B, int H, int W, int nh, int nw,
+                      __nv_bfloat16* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t);
+int masks_from_pred(ub_ctx*, const uint8_t* pred, int B, int nh, int nw, int H, int W, ub_roi roi,
+                    uint8_t* cable, uint8_t* tape, int32_t* stats, cudaStream_t);
+int argmax_logits(ub_ctx*, const float* logits, int B, int C, int nh, int nw, uint8_t* pred, cudaStream_t);
+
+// stage2.cu
+int burr_stage(ub_ctx*, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
+               const ub_burr_params& p, uint8_t* burr, int32_t* burr_px, int px_stride, cudaStream_t);

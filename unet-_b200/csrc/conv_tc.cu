@@ -1,0 +1,357 @@
+// conv_tc.cu -- 3x3 conv (+folded BN bias, ReLU, optional fused 1x1 head + argmax) as an
+// implicit GEMM on the 5th-gen tensor cores (tcgen05.mma, fp32 accumulators in TMEM),
+// fed by 1-D bulk async copies (cp.async.bulk -> UBLKCP) with an mbarrier pipeline.
+//
+// Replaces ConvBlock.forward's conv+bn+relu (src/models/unetpp.py:23-26) and, for the
+// last layer, `final` (unetpp.py:119) + softmax/argmax (infer_two_stage_burr.py:299-300).
+//
+// GEMM view (see common.cuh for the PP layout):
+//   D[p, co] = sum_{tap, ci} X[p + off(tap), ci] * Wt[tap, ci, co]
+//   M = 128 consecutive flat positions of one image, N = BN output channels,
+//   K = 9 taps x Cin, walked in k-blocks of KC channels x 9 taps.
+//   A operand = activations, K-major, no-swizzle core matrices (8 positions x 16 B):
+//               rows 16 B apart inside a chunk plane, K chunks LBO apart.  With SHIFT_A the
+//               three taps of a kernel row share ONE staged segment of 130(+6) positions
+//               and differ only by +16 B in the descriptor start address.
+//   B operand = weights, K-major, [tap][chunk][BN][8] in shared memory.
+// Warp roles (192 threads): warps 0-3 epilogue (TMEM lane quarter = warp id),
+// warp 4 bulk-copy producer (+TMEM alloc), warp 5 MMA issuer (one elected lane).
+// Persistent CTAs, one per SM; TMEM accumulators double-buffered so the epilogue of item i
+// overlaps the MMAs of item i+1.
+#include "common.cuh"
+
+namespace {
+
+constexpr int SEG_POS = 136;                 // staged positions per shifted segment (130 used)
+constexpr int SEG_BYTES = SEG_POS * 16;      // 2176
+constexpr int TILE_M = 128;
+
+struct TcParams {
+  const __nv_bfloat16* src0; const __nv_bfloat16* src1; __nv_bfloat16* out;
+  const __nv_bfloat16* w; const float* bias;
+  int B, kb0, kbn, nch0, nch1, cout, n_ntiles, num_stages, b_resident;
+  long long total_items;
+  PPLayout L;
+  const float* head_w; const float* head_b; int ncls; float* logits; uint8_t* pred;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                       uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
+// [0,14) addr>>4, [16,30) LBO>>4 (K-direction core-matrix stride), [32,46) SBO>>4
+// (M/N-direction 8-row group stride), [46,48) version=1, [61,64) layout 0 = no swizzle.
+__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+
+#define TMEM_LD32(taddr, v)                                                                        \
+  asm volatile(                                                                                    \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                    \
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"    \
+      "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"                                                   \
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),        \
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),    \
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), \
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), \
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                                         \
+      : "r"(taddr))
+
+template <int BN, int KC, bool SHIFT_A>
+struct Cfg {
+  static constexpr int CPK = KC / 8;                                   // chunks per k-block
+  static constexpr int A_SEGS = SHIFT_A ? 3 : 9;
+  static constexpr int A_SEG_BYTES = SHIFT_A ? SEG_BYTES : TILE_M * 16;  // per chunk
+  static constexpr int A_STAGE = A_SEGS * CPK * A_SEG_BYTES;
+  static constexpr int B_TAP = KC * BN * 2;
+  static constexpr int B_STAGE = 9 * B_TAP;
+  static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;        // power of two for BN in {32..256}
+  static constexpr int HDR = 2048;                                     // barriers + head weights
+};
+
+template <int BN, int KC, bool SHIFT_A>
+__global__ void __launch_bounds__(192, 1) k_conv_tc(TcParams P) {
+  using C = Cfg<BN, KC, SHIFT_A>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = P.num_stages;
+  // header: full[S] | empty[S] | tfull[2] | tempty[2] | tmem ptr | head weights (fp32)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * S;
+  const uint32_t bar_tfull = bar_empty + 8 * S, bar_tempty = bar_tfull + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 4));
+  float* s_head = reinterpret_cast<float*>(smem + 512);               // [ncls*32 + ncls] <= 8*33
+  const uint32_t a_base = smem_u32(smem) + C::HDR;
+  const uint32_t b_base = a_base + S * C::A_STAGE;
+  const PPLayout& L = P.L;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (P.head_w != nullptr) {
+    const int n = P.ncls * 32;
+    for (int i = threadIdx.x; i < P.ncls * 33; i += blockDim.x)
+      s_head[i] = i < n ? P.head_w[i] : P.head_b[i - n];
+  }
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "n"(C::TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ===================== producer: bulk copies global -> shared =====================
+    int s = 0; uint32_t ph = 0; bool first = true;
+    for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x) {
+      const int nt = (int)(item % P.n_ntiles);
+      const long long r = item / P.n_ntiles;
+      const int mt = (int)(r % L.ntiles), b = (int)(r / L.ntiles);
+      const int p0 = L.G + mt * TILE_M;
+      const bool load_b = !P.b_resident || first;
+      for (int kb = 0; kb < P.kbn; ++kb) {
+        const uint32_t full = bar_full + 8 * s;
+        if (lane == 0) {
+          mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
+        }
+        __syncwarp();
+        const __nv_bfloat16* plane0 =
+            kb < P.kb0 ? P.src0 + ((size_t)b * P.nch0 + (size_t)kb * C::CPK) * L.Ppl * 8
+                       : P.src1 + ((size_t)b * P.nch1 + (size_t)(kb - P.kb0) * C::CPK) * L.Ppl * 8;
+        const uint32_t a_st = a_base + s * C::A_STAGE;
+        const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+        constexpr int NA = C::A_SEGS * C::CPK;
+        const int ncopy = NA + (load_b ? 9 : 0);
+        for (int c = lane; c < ncopy; c += 32) {
+          if (c < NA) {
+            const int seg = c / C::CPK, cc = c - seg * C::CPK;
+            const int off = SHIFT_A ? (seg - 1) * L.pitch - 1 : (seg / 3 - 1) * L.pitch + (seg % 3 - 1);
+            bulk_g2s(a_st + c * C::A_SEG_BYTES, plane0 + ((size_t)cc * L.Ppl + p0 + off) * 8,
+                     C::A_SEG_BYTES, full);
+          } else {
+            const int tap = c - NA;
+            bulk_g2s(b_st + tap * C::B_TAP,
+                     P.w + (((size_t)nt * P.kbn + kb) * 9 + tap) * (size_t)(KC * BN), C::B_TAP, full);
+          }
+        }
+        if (++s == S) { s = 0; ph ^= 1; }
+      }
+      first = false;
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                                 ((uint32_t)(TILE_M >> 4) << 24);
+      int s = 0; uint32_t ph = 0; int it = 0;
+      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(bar_tempty + 8 * buf, ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = 0; kb < P.kbn; ++kb) {
+          mbar_wait(bar_full + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_st = a_base + s * C::A_STAGE;
+          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const uint32_t a_tap = SHIFT_A ? a_st + (tap / 3) * C::CPK * C::A_SEG_BYTES + (tap % 3) * 16
+                                           : a_st + tap * C::CPK * C::A_SEG_BYTES;
+#pragma unroll
+            for (int k16 = 0; k16 < KC / 16; ++k16) {
+              const uint64_t ad = make_desc(a_tap + 2 * k16 * C::A_SEG_BYTES, C::A_SEG_BYTES, 128);
+              const uint64_t bd = make_desc(b_st + tap * C::B_TAP + 2 * k16 * BN * 16, BN * 16, 128);
+              tc_mma(d_tmem, ad, bd, IDESC, (kb | tap | k16) != 0);
+            }
+          }
+          tc_commit(bar_empty + 8 * s);          // frees the smem stage when these MMAs retire
+          if (++s == S) { s = 0; ph ^= 1; }
+        }
+        tc_commit(bar_tfull + 8 * buf);          // accumulator ready for the epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    int it = 0;
+    const int row = warp * 32 + lane;
+    const int nco_chunks = P.cout / 8;
+    for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+      const int nt = (int)(item % P.n_ntiles);
+      const long long r = item / P.n_ntiles;
+      const int mt = (int)(r % L.ntiles), b = (int)(r / L.ntiles);
+      const int buf = it & 1;
+      const int q = mt * TILE_M + row;
+      const int yy = q / L.pitch, xx = q - yy * L.pitch;
+      const bool interior = (q < L.npos) && yy >= 1 && yy <= L.H && xx >= 1 && xx <= L.W;
+      mbar_wait(bar_tfull + 8 * buf, (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        TMEM_LD32(taddr + c0, v);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int co0 = nt * BN + c0;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          f[j] = interior ? fmaxf(__uint_as_float(v[j]) + __ldg(P.bias + co0 + j), 0.f) : 0.f;
+        if (P.head_w != nullptr) {
+          if (interior) {
+            float lg[8];
+            int best = 0;
+            const size_t hw = (size_t)L.H * L.W, pix = (size_t)(yy - 1) * L.W + (xx - 1);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              if (c < P.ncls) {
+                float acc = s_head[P.ncls * 32 + c];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc = fmaf(s_head[c * 32 + j], f[j], acc);
+                lg[c] = acc;
+                if (P.logits) P.logits[((size_t)b * P.ncls + c) * hw + pix] = acc;
+                if (c > 0 && acc > lg[best]) best = c;
+              }
+            }
+            if (P.pred) P.pred[(size_t)b * hw + pix] = (uint8_t)best;
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            __nv_bfloat162 h[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[g * 8 + 2 * j], f[g * 8 + 2 * j + 1]);
+            *reinterpret_cast<uint4*>(P.out + (((size_t)b * nco_chunks + (co0 >> 3) + g) * L.Ppl + L.G + q) * 8) =
+                *reinterpret_cast<uint4*>(h);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS));
+  }
+}
+
+constexpr int SMEM_BUDGET = 227 * 1024;
+
+template <int BN, int KC, bool SHIFT_A>
+int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
+  using C = Cfg<BN, KC, SHIFT_A>;
+  auto kern = k_conv_tc<BN, KC, SHIFT_A>;
+  if (init_only) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+    return UB_OK;
+  }
+  // weights resident in shared memory when they fit beside >= 3 activation stages
+  const int resident_bytes = P.kbn * C::B_STAGE;
+  int stages;
+  if (P.n_ntiles == 1 && C::HDR + resident_bytes + 3 * C::A_STAGE <= SMEM_BUDGET) {
+    P.b_resident = 1;
+    stages = (SMEM_BUDGET - C::HDR - resident_bytes) / C::A_STAGE;
+  } else {
+    P.b_resident = 0;
+    stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + C::B_STAGE);
+  }
+  if (stages > 8) stages = 8;
+  if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_tc: BN=%d KC=%d does not fit 2 stages", BN, KC);
+  P.num_stages = stages;
+  const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
+  kern<<<(unsigned)grid, 192, smem, st>>>(P);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+template <bool SHIFT_A>
+int dispatch(ub_ctx* ctx, int bn, int kc, TcParams& P, cudaStream_t st, bool init_only) {
+#define UB_CASE(BN_, KC_) \
+  if (bn == BN_ && kc == KC_) return launch_cfg<BN_, KC_, SHIFT_A>(ctx, P, st, init_only);
+  UB_CASE(32, 16) UB_CASE(32, 32) UB_CASE(64, 16) UB_CASE(64, 32) UB_CASE(128, 16) UB_CASE(128, 32)
+  UB_CASE(256, 16)
+#undef UB_CASE
+  return ub_fail(ctx, UB_ERR_ARG, "conv_tc: unsupported tile BN=%d KC=%d", bn, kc);
+}
+
+}  // namespace
+
+static const int kTileTable[][2] = {{32, 16}, {32, 32}, {64, 16}, {64, 32}, {128, 16}, {128, 32}, {256, 16}};
+
+int conv_tc_init(ub_ctx* ctx) {
+  TcParams P{};
+  for (auto& t : kTileTable) {
+    int r = dispatch<true>(ctx, t[0], t[1], P, nullptr, true);
+    if (r != UB_OK) return r;
+    r = dispatch<false>(ctx, t[0], t[1], P, nullptr, true);
+    if (r != UB_OK) return r;
+  }
+  return UB_OK;
+}
+
+int conv3x3_tc(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t st) {
+  TcParams P{};
+  P.src0 = a.src0; P.src1 = a.src1; P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
+  P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
+  P.nch0 = Lr.cin0 / 8; P.nch1 = Lr.cin1 / 8; P.cout = Lr.cout; P.n_ntiles = Lr.cout / Lr.bn;
+  P.L = pp_layout(a.H, a.W);
+  P.total_items = (long long)a.B * P.L.ntiles * P.n_ntiles;
+  P.head_w = a.head_w; P.head_b = a.head_b; P.ncls = a.num_classes; P.logits = a.logits; P.pred = a.pred;
+  if (a.head_w && (Lr.cout != 32 || Lr.bn != 32)) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == bn == 32");
+  TimeScope ts(ctx, UB_T_CONV, st);
+  // conv_impl 0: shifted-descriptor A operand (3 staged segments); 2: nine aligned segments
+  return ctx->conv_impl == 2 ? dispatch<false>(ctx, Lr.bn, Lr.kc, P, st, false)
+                             : dispatch<true>(ctx, Lr.bn, Lr.kc, P, st, false);
+}

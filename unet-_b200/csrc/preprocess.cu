@@ -1,0 +1,243 @@
+// preprocess.cu -- uint8 frame -> net input / gray, frame normalisation, and
+// logits -> class masks.  All integer arithmetic follows OpenCV 4.13 bit-exactly
+// (restated and pinned in oracle/cvnp.py).
+#include <map>
+#include <math.h>
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------
+// cv2.resize(INTER_LINEAR) coefficient tables (oracle/cvnp.py: linear_coeffs).
+// Table layout per axis: int4 {i0, i1, c0, c1} per destination index.
+// ---------------------------------------------------------------------------------
+struct ResizeCache {
+  std::map<uint64_t, int4*> dev;
+  std::vector<std::vector<int4>*> host;
+};
+
+static void build_axis(int src, int dst, bool is_x, std::vector<int4>& t) {
+  t.resize(dst);
+  const double scale = 1.0 / ((double)dst / (double)src);     // cv::resize: scale = 1./inv_scale
+  for (int d = 0; d < dst; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    int i0, i1;
+    if (is_x) {
+      if (s < 0) { s = 0; f = 0.f; }
+      if (s >= src - 1) { s = src - 1; f = 0.f; }
+      i0 = s; i1 = s + 1 < src ? s + 1 : src - 1;
+    } else {
+      i0 = s < 0 ? 0 : (s > src - 1 ? src - 1 : s);
+      int s1 = s + 1;
+      i1 = s1 < 0 ? 0 : (s1 > src - 1 ? src - 1 : s1);
+    }
+    int c0 = (int)lrintf((1.f - f) * 2048.f);
+    int c1 = (int)lrintf(f * 2048.f);
+    t[d] = make_int4(i0, i1, c0, c1);
+  }
+}
+
+static int get_table(ub_ctx* ctx, int src, int dst, bool is_x, const int4** out, cudaStream_t st) {
+  if (!ctx->cache) ctx->cache = new ResizeCache();
+  ResizeCache* rc = static_cast<ResizeCache*>(ctx->cache);
+  uint64_t key = ((uint64_t)src << 33) | ((uint64_t)dst << 1) | (is_x ? 1 : 0);
+  auto it = rc->dev.find(key);
+  if (it == rc->dev.end()) {
+    auto* h = new std::vector<int4>();
+    build_axis(src, dst, is_x, *h);
+    rc->host.push_back(h);
+    int4* d = nullptr;
+    UB_CUDA(ctx, cudaMalloc(&d, sizeof(int4) * dst));
+    UB_CUDA(ctx, cudaMemcpyAsync(d, h->data(), sizeof(int4) * dst, cudaMemcpyHostToDevice, st));
+    it = rc->dev.emplace(key, d).first;
+  }
+  *out = it->second;
+  return UB_OK;
+}
+
+void resize_cache_free(ub_ctx* ctx) {
+  if (!ctx->cache) return;
+  ResizeCache* rc = static_cast<ResizeCache*>(ctx->cache);
+  for (auto& kv : rc->dev) cudaFree(kv.second);
+  for (auto* h : rc->host) delete h;
+  delete rc;
+  ctx->cache = nullptr;
+}
+
+namespace {
+
+// One bilinear sample of channel c, cv2's 11-bit fixed point (two-pass, >>4, >>16, +2 >>2).
+template <class Src>
+__device__ __forceinline__ int bilerp(const Src& S, int4 ty, int4 tx, int c) {
+  int h0 = S(ty.x, tx.x, c) * tx.z + S(ty.x, tx.y, c) * tx.w;
+  int h1 = S(ty.y, tx.x, c) * tx.z + S(ty.y, tx.y, c) * tx.w;
+  return (((ty.z * (h0 >> 4)) >> 16) + ((ty.w * (h1 >> 4)) >> 16) + 2) >> 2;
+}
+
+struct SrcPlain {
+  const uint8_t* p; int w;
+  __device__ __forceinline__ int operator()(int y, int x, int c) const { return p[((size_t)y * w + x) * 3 + c]; }
+};
+// view of cv2.rotate(src, ROTATE_90_COUNTERCLOCKWISE): R[y][x] = src[x][sw-1-y]
+struct SrcRot {
+  const uint8_t* p; int w;
+  __device__ __forceinline__ int operator()(int y, int x, int c) const { return p[((size_t)x * w + (w - 1 - y)) * 3 + c]; }
+};
+
+// preprocess_image (infer_two_stage_burr.py:122-127): BGR->RGB, resize, /255.
+__global__ void k_preprocess(const uint8_t* __restrict__ frames, int H, int W, int nh, int nw,
+                             const int4* __restrict__ ty, const int4* __restrict__ tx,
+                             __nv_bfloat16* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L) {
+  int q = blockIdx.x * blockDim.x + threadIdx.x;
+  int b = blockIdx.y;
+  if (q >= L.ntiles * 128) return;
+  int yy = q / L.pitch, xx = q - yy * L.pitch;
+  bool interior = (q < L.npos) && yy >= 1 && yy <= nh && xx >= 1 && xx <= nw;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (interior) {
+    SrcPlain S{frames + (size_t)b * H * W * 3, W};
+    int4 cy = ty[yy - 1], cx = tx[xx - 1];
+    __nv_bfloat16 h[8];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      int u = bilerp(S, cy, cx, 2 - c);                       // RGB order: channel c reads B,G,R[2-c]
+      float f = __fdiv_rn((float)u, 255.0f);
+      h[c] = __float2bfloat16_rn(f);
+      if (x_nchw) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = f;
+    }
+#pragma unroll
+    for (int c = 3; c < 8; ++c) h[c] = __float2bfloat16_rn(0.f);
+    v = *reinterpret_cast<uint4*>(h);
+  }
+  if (x_pp) *reinterpret_cast<uint4*>(x_pp + (((size_t)b * 2) * L.Ppl + L.G + q) * 8) = v;
+}
+
+// cv2.cvtColor(BGR2GRAY) (infer_two_stage_burr.py:317): (3735 B + 19235 G + 9798 R + 2^14) >> 15
+__global__ void k_gray(const uint8_t* __restrict__ frames, uint8_t* __restrict__ gray, size_t npix) {
+  size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= npix) return;
+  if (i + 4 <= npix) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(frames + i * 3);   // 12 B, 4-aligned
+    uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+    uint8_t px[12];
+    *reinterpret_cast<uint32_t*>(px) = w0; *reinterpret_cast<uint32_t*>(px + 4) = w1;
+    *reinterpret_cast<uint32_t*>(px + 8) = w2;
+    uint32_t o = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      uint32_t g = (3735u * px[3 * k] + 19235u * px[3 * k + 1] + 9798u * px[3 * k + 2] + (1u << 14)) >> 15;
+      o |= g << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(gray + i) = o;
+  } else {
+    for (; i < npix; ++i)
+      gray[i] = (uint8_t)((3735u * frames[i * 3] + 19235u * frames[i * 3 + 1] + 9798u * frames[i * 3 + 2] + (1u << 14)) >> 15);
+  }
+}
+
+// rotate + resize (infer_two_stage_burr.py:275-280)
+template <class Src>
+__global__ void k_resize3(Src S0, size_t src_stride, uint8_t* __restrict__ dst, int dh, int dw,
+                          const int4* __restrict__ ty, const int4* __restrict__ tx) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+  if (x >= dw) return;
+  Src S = S0; S.p += (size_t)b * src_stride;
+  int4 cy = ty[y], cx = tx[x];
+  uint8_t* o = dst + (((size_t)b * dh + y) * dw + x) * 3;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) o[c] = (uint8_t)bilerp(S, cy, cx, c);
+}
+
+// argmax over classes (softmax is monotone; ties -> lowest index like np.argmax)
+__global__ void k_argmax(const float* __restrict__ logits, int C, size_t hw, uint8_t* __restrict__ pred) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int b = blockIdx.y;
+  if (i >= hw) return;
+  const float* p = logits + (size_t)b * C * hw + i;
+  float bv = p[0]; int best = 0;
+  for (int c = 1; c < C; ++c) { float v = p[c * hw]; if (v > bv) { bv = v; best = c; } }
+  pred[(size_t)b * hw + i] = (uint8_t)best;
+}
+
+// (pred==1),(pred==2) -> NEAREST upscale -> ROI (infer_two_stage_burr.py:303-314) + pixel counts
+__global__ void k_masks(const uint8_t* __restrict__ pred, int nh, int nw, int H, int W, double sy, double sx,
+                        ub_roi roi, uint8_t* __restrict__ cable, uint8_t* __restrict__ tape,
+                        int32_t* __restrict__ stats) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+  int c = 0, t = 0;
+  if (x < W) {
+    if (x >= roi.x1 && x < roi.x2 && y >= roi.y1 && y < roi.y2) {
+      int py = min((int)floor(y * sy), nh - 1), pxx = min((int)floor(x * sx), nw - 1);
+      int cls = pred[((size_t)b * nh + py) * nw + pxx];
+      c = cls == 1; t = cls == 2;
+    }
+    size_t o = ((size_t)b * H + y) * W + x;
+    cable[o] = (uint8_t)c; tape[o] = (uint8_t)t;
+  }
+  unsigned mc = __ballot_sync(0xffffffffu, c), mt = __ballot_sync(0xffffffffu, t);
+  if ((threadIdx.x & 31) == 0 && stats) {
+    if (mc) atomicAdd(stats + b * 4 + 1, __popc(mc));
+    if (mt) atomicAdd(stats + b * 4 + 2, __popc(mt));
+  }
+}
+
+__global__ void k_stats_init(int32_t* stats, int B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B * 4) stats[i] = (i & 3) == 0 ? (i >> 2) : 0;
+}
+
+}  // namespace
+
+int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, int nh, int nw,
+                      __nv_bfloat16* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t st) {
+  if (x_pp || x_nchw) {
+    const int4 *ty, *tx;
+    int r = get_table(ctx, H, nh, false, &ty, st); if (r) return r;
+    r = get_table(ctx, W, nw, true, &tx, st); if (r) return r;
+    PPLayout L = pp_layout(nh, nw);
+    TimeScope ts(ctx, UB_T_PREPOST, st);
+    dim3 grid(cdiv(L.ntiles * 128, 256), B);
+    k_preprocess<<<grid, 256, 0, st>>>(frames, H, W, nh, nw, ty, tx, x_pp, x_nchw, L);
+    UB_CHECK_LAUNCH(ctx);
+  }
+  if (gray) {
+    size_t npix = (size_t)B * H * W;
+    TimeScope ts(ctx, UB_T_PREPOST, st);
+    k_gray<<<(unsigned)((npix / 4 + 255) / 256 + 1), 256, 0, st>>>(frames, gray, npix);
+    UB_CHECK_LAUNCH(ctx);
+  }
+  return UB_OK;
+}
+
+int normalize_frames_impl(ub_ctx* ctx, const uint8_t* src, int B, int sh, int sw, int rot,
+                          uint8_t* dst, int dh, int dw, cudaStream_t st) {
+  int rh = rot ? sw : sh, rw = rot ? sh : sw;
+  const int4 *ty, *tx;
+  int r = get_table(ctx, rh, dh, false, &ty, st); if (r) return r;
+  r = get_table(ctx, rw, dw, true, &tx, st); if (r) return r;
+  TimeScope ts(ctx, UB_T_PREPOST, st);
+  dim3 grid(cdiv(dw, 128), dh, B);
+  size_t stride = (size_t)sh * sw * 3;
+  if (rot) k_resize3<SrcRot><<<grid, 128, 0, st>>>(SrcRot{src, sw}, stride, dst, dh, dw, ty, tx);
+  else k_resize3<SrcPlain><<<grid, 128, 0, st>>>(SrcPlain{src, sw}, stride, dst, dh, dw, ty, tx);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+int argmax_logits(ub_ctx* ctx, const float* logits, int B, int C, int nh, int nw, uint8_t* pred, cudaStream_t st) {
+  size_t hw = (size_t)nh * nw;
+  TimeScope ts(ctx, UB_T_PREPOST, st);
+  k_argmax<<<dim3((unsigned)((hw + 255) / 256), B), 256, 0, st>>>(logits, C, hw, pred);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+int masks_from_pred(ub_ctx* ctx, const uint8_t* pred, int B, int nh, int nw, int H, int W, ub_roi roi,
+                    uint8_t* cable, uint8_t* tape, int32_t* stats, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_PREPOST, st);
+  if (stats) k_stats_init<<<cdiv(B * 4, 256), 256, 0, st>>>(stats, B);
+  double sy = 1.0 / ((double)H / (double)nh), sx = 1.0 / ((double)W / (double)nw);
+  k_masks<<<dim3(cdiv(W, 128), H, B), 128, 0, st>>>(pred, nh, nw, H, W, sy, sx, roi, cable, tape, stats);
+  UB_CHECK_LAUNCH_N(ctx, stats ? 2 : 1);
+  return UB_OK;
+}

@@ -1,0 +1,389 @@
+// stage2.cu -- connected-component labelling (warp-level union-find), Canny hysteresis,
+// component statistics / filter, and the burr-stage schedule
+// (detect_burrs_on_cable, infer_two_stage_burr.py:50-119; detect_burrs_enhanced,
+// infer_enhanced_burr.py:69-138).
+#include <limits.h>
+#include <math.h>
+#include "stage2_kernels.cuh"
+
+namespace s2 {
+
+// ------------------------------------------------------------------------------
+// Union-find over pixel indices (per frame, p = y*W + x).  Links always point from the
+// larger index to the smaller, so a component's root is its first pixel in raster order.
+// ------------------------------------------------------------------------------
+__device__ __forceinline__ int uf_find(const int* lab, int x) {
+  while (true) {
+    int p = __ldcg(lab + x);
+    if (p == x) return x;
+    x = p;
+  }
+}
+__device__ __forceinline__ void uf_union(int* lab, int a, int b) {
+  while (true) {
+    a = uf_find(lab, a);
+    b = uf_find(lab, b);
+    if (a == b) return;
+    if (a < b) { int t = a; a = b; b = t; }
+    int old = atomicMin(lab + a, b);
+    if (old == a) return;
+    a = old;
+  }
+}
+
+// run start / length of the lane's foreground run inside its 32-pixel warp segment
+__device__ __forceinline__ int run_start(uint32_t mask, int lane) {
+  uint32_t inv = ~mask & ((1u << lane) - 1u);
+  return inv ? 32 - __clz(inv) : 0;
+}
+__device__ __forceinline__ int run_end(uint32_t mask, int lane) {       // inclusive
+  uint32_t inv = ~mask & ~((2u << lane) - 1u);                          // zeros above lane
+  return inv ? __ffs(inv) - 2 : 31;
+}
+
+// Pass 1: label = index of the start of the pixel's run within its warp segment (ballot).
+__global__ void __launch_bounds__(256) k_ccl_init(const uint8_t* __restrict__ src, int* __restrict__ lab, int H, int W) {
+  const int segs = (W + 31) >> 5;
+  const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= H * segs) return;
+  const int y = warp / segs, x = (warp - y * segs) * 32 + lane;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const bool fg = x < W && src[base + (size_t)y * W + x] != 0;
+  const uint32_t mask = __ballot_sync(0xffffffffu, fg);
+  if (x < W) lab[base + (size_t)y * W + x] = fg ? y * W + (x - lane) + run_start(mask, lane) : -1;
+}
+
+// Pass 2: merge with the row above (8-connectivity) and across warp-segment boundaries.
+__global__ void __launch_bounds__(256) k_ccl_merge(int* __restrict__ lab_all, int H, int W) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int* lab = lab_all + (size_t)blockIdx.z * H * W;
+  const int p = y * W + x;
+  if (lab[p] < 0) return;
+  const bool w = x > 0 && lab[p - 1] >= 0;
+  if (w && (x & 31) == 0) uf_union(lab, p, p - 1);
+  if (y == 0) return;
+  const int up = p - W;
+  const bool n = lab[up] >= 0;
+  const bool nw = x > 0 && lab[up - 1] >= 0;
+  const bool ne = x + 1 < W && lab[up + 1] >= 0;
+  if (n) {
+    if (!(w && nw)) uf_union(lab, p, up);
+  } else {
+    if (nw && !w) uf_union(lab, p, up - 1);
+    if (ne) uf_union(lab, p, up + 1);
+  }
+}
+
+// Pass 3: full path compression; roots initialise their accumulators when `comp` is given.
+// comp planes (each B*H*W): 0 area, 1 min x, 2 max x, 3 min y, 4 max y, 5 first-appearance key
+__global__ void __launch_bounds__(256) k_ccl_flatten(int* __restrict__ lab_all, int H, int W, int* __restrict__ comp, size_t plane) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  int* lab = lab_all + base;
+  const int p = y * W + x;
+  if (lab[p] < 0) return;
+  const int r = uf_find(lab, p);
+  lab[p] = r;
+  if (comp && r == p) {
+    int* c = comp + base + p;
+    c[0] = 0; c[plane] = INT_MAX; c[2 * plane] = -1; c[3 * plane] = INT_MAX; c[4 * plane] = -1; c[5 * plane] = INT_MAX;
+  }
+}
+
+// Canny hysteresis (second half of cv2.Canny): a candidate survives iff its 8-connected
+// component of candidates holds a strong pixel.  `out` doubles as the per-root flag.
+__global__ void k_hyst_mark(const uint8_t* __restrict__ cand, const int* __restrict__ lab, uint8_t* __restrict__ out, int H, int W) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int p = y * W + x;
+  if (cand[base + p] == 2) out[base + lab[base + p]] = 255;
+}
+__global__ void k_hyst_final(const int* __restrict__ lab, uint8_t* __restrict__ out, int H, int W) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int p = y * W + x;
+  const int r = lab[base + p];
+  if (r >= 0 && r != p) out[base + p] = out[base + r];
+}
+
+// Component statistics: one atomic set per run (warp-aggregated), not per pixel.
+// bgacc (nullable) [B][8]: background area / bbox for stats row 0.
+__global__ void __launch_bounds__(256) k_ccl_stats(const int* __restrict__ lab_all, int H, int W, int* __restrict__ comp, size_t plane,
+                                                   int* __restrict__ bgacc) {
+  const int segs = (W + 31) >> 5;
+  const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= H * segs) return;
+  const int y = warp / segs, x = (warp - y * segs) * 32 + lane;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int r = x < W ? lab_all[base + (size_t)y * W + x] : -2;
+  const bool fg = r >= 0;
+  const uint32_t mask = __ballot_sync(0xffffffffu, fg);
+  if (fg && run_start(mask, lane) == lane) {
+    const int xe = x + (run_end(mask, lane) - lane);
+    int* c = comp + base + r;
+    atomicAdd(c, xe - x + 1);
+    atomicMin(c + plane, x); atomicMax(c + 2 * plane, xe);
+    atomicMin(c + 3 * plane, y); atomicMax(c + 4 * plane, y);
+    // first appearance in cv2's 2x2-block raster scan; the key grows with x inside a row,
+    // so the minimum over a run is at its first pixel.
+    const int key = ((((y >> 1) * ((W + 1) >> 1)) + (x >> 1)) << 2) | ((y & 1) << 1) | (x & 1);
+    atomicMin(c + 5 * plane, key);
+  }
+  if (bgacc) {
+    const bool bg = r == -1;
+    const uint32_t bm = __ballot_sync(0xffffffffu, bg);
+    if (bm && lane == 0) {
+      int* a = bgacc + blockIdx.z * 8;
+      const int xs = (warp - y * segs) * 32;
+      atomicAdd(a, __popc(bm));
+      atomicMin(a + 1, xs + __ffs(bm) - 1); atomicMax(a + 2, xs + 31 - __clz(bm));
+      atomicMin(a + 3, y); atomicMax(a + 4, y);
+    }
+  }
+}
+
+// Component filter (infer_two_stage_burr.py:103-117): burr[p] = 1 iff the component passes.
+__global__ void __launch_bounds__(256) k_ccl_filter(const int* __restrict__ lab_all, int H, int W, const int* __restrict__ comp, size_t plane,
+                                                    ub_burr_params P, uint8_t* __restrict__ burr, int* __restrict__ px, int px_stride) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  bool keep = false;
+  if (x < W) {
+    const int r = lab_all[base + (size_t)y * W + x];
+    if (r >= 0) {
+      const int* c = comp + base + r;
+      const int area = c[0], w = c[2 * plane] - c[plane] + 1, h = c[4 * plane] - c[3 * plane] + 1;
+      const int mx = max(w, h), mn = min(w, h);
+      keep = area >= P.min_area && area <= P.max_area && mx <= P.max_aspect * mn && w >= P.min_side && h >= P.min_side;
+    }
+    burr[base + (size_t)y * W + x] = keep ? 1 : 0;
+  }
+  const uint32_t m = __ballot_sync(0xffffffffu, keep);
+  if (px && m && (threadIdx.x & 31) == 0) atomicAdd(px + blockIdx.z * px_stride, __popc(m));
+}
+
+// ---- export in OpenCV numbering (ub_ccl) --------------------------------------
+__global__ void k_mark_roots(const int* __restrict__ lab_all, int H, int W, const int* __restrict__ comp, size_t plane,
+                             int* __restrict__ mark, int K) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int p = y * W + x;
+  if (lab_all[base + p] == p) mark[(size_t)blockIdx.z * K + comp[5 * plane + base + p]] = 1;
+}
+// inclusive prefix sum of mark[b][0..K) in place, one 1024-thread block per frame
+__global__ void __launch_bounds__(1024) k_scan(int* __restrict__ mark, int K, int* __restrict__ n_labels) {
+  __shared__ int s_w[32];
+  __shared__ int s_carry;
+  int* m = mark + (size_t)blockIdx.x * K;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < K; i0 += 1024) {
+    const int i = i0 + threadIdx.x;
+    int v = i < K ? m[i] : 0;
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+    if (lane == 31) s_w[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+      int t = s_w[lane];
+      for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t += u; }
+      s_w[lane] = t;
+    }
+    __syncthreads();
+    const int carry = s_carry;
+    v += carry + (warp ? s_w[warp - 1] : 0);
+    if (i < K) m[i] = v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) n_labels[blockIdx.x] = s_carry + 1;
+}
+__global__ void k_relabel(const int* __restrict__ lab_all, int H, int W, const int* __restrict__ comp, size_t plane,
+                          const int* __restrict__ rank, int K, int* __restrict__ labels, int* __restrict__ stats, int max_labels,
+                          const int* __restrict__ bgacc) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int p = y * W + x;
+  const int r = lab_all[base + p];
+  int out = 0;
+  if (r >= 0) {
+    const int* c = comp + base + r;
+    out = rank[(size_t)blockIdx.z * K + c[5 * plane]];
+    if (r == p && stats && out < max_labels) {
+      int* s = stats + ((size_t)blockIdx.z * max_labels + out) * 5;
+      s[0] = c[plane]; s[1] = c[3 * plane]; s[2] = c[2 * plane] - c[plane] + 1; s[3] = c[4 * plane] - c[3 * plane] + 1; s[4] = c[0];
+    }
+  }
+  if (labels) labels[base + p] = out;
+  if (p == 0 && stats && max_labels > 0) {
+    const int* a = bgacc + blockIdx.z * 8;
+    int* s = stats + (size_t)blockIdx.z * max_labels * 5;
+    s[0] = a[1]; s[1] = a[3]; s[2] = a[2] - a[1] + 1; s[3] = a[4] - a[3] + 1; s[4] = a[0];
+  }
+}
+__global__ void k_bg_init(int* bgacc, int B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B * 8) { int k = i & 7; bgacc[i] = (k == 1 || k == 3) ? INT_MAX : (k == 2 || k == 4) ? -1 : 0; }
+}
+
+}  // namespace s2
+
+using namespace s2;
+
+// cv2.getStructuringElement(MORPH_ELLIPSE,(k,k)) as row runs (oracle/cvnp.py: ellipse)
+static bool make_footprint(int k, Footprint& fp) {
+  if (k < 1 || k > 25) return false;
+  const int r = k / 2, c = k / 2;
+  const double inv_r2 = r ? 1.0 / ((double)r * r) : 0.0;
+  fp.nrows = 0; fp.top = 0; fp.bottom = 0;
+  for (int i = 0; i < k; ++i) {
+    const int dy = i - r;
+    if (abs(dy) > r) continue;
+    const int dx = (int)lrint(c * sqrt((r * r - dy * dy) * inv_r2));
+    const int j1 = c - dx > 0 ? c - dx : 0, j2 = c + dx + 1 < k ? c + dx + 1 : k;
+    if (j2 <= j1) continue;
+    fp.dy[fp.nrows] = (int8_t)(i - k / 2);           // anchor (k/2, k/2)
+    fp.xa[fp.nrows] = (int8_t)(j1 - k / 2);
+    fp.xb[fp.nrows] = (int8_t)(j2 - 1 - k / 2);
+    if (-(i - k / 2) > fp.top) fp.top = -(i - k / 2);
+    if ((i - k / 2) > fp.bottom) fp.bottom = i - k / 2;
+    ++fp.nrows;
+  }
+  return true;
+}
+
+static int morph_once(ub_ctx* ctx, bool dil, int k, const uint8_t* src, uint8_t* dst, int B, int H, int W, int value,
+                      const uint8_t* notmask, cudaStream_t st) {
+  Footprint fp;
+  if (!make_footprint(k, fp)) return ub_fail(ctx, UB_ERR_ARG, "ellipse size %d unsupported (1..25)", k);
+  dim3 grid(cdiv(W, MT_W), cdiv(H, MT_H), B);
+  if (dil) k_morph<true><<<grid, 256, 0, st>>>(src, dst, H, W, fp, value, notmask);
+  else k_morph<false><<<grid, 256, 0, st>>>(src, dst, H, W, fp, value, notmask);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+#define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
+
+// op: 0 dilate, 1 erode, 2 close (dilate->erode), 3 open (erode->dilate); tmp needed for 2,3
+int morph_op(ub_ctx* ctx, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_STENCIL, st);
+  switch (op) {
+    case 0: return morph_once(ctx, true, k, src, dst, B, H, W, value, nullptr, st);
+    case 1: return morph_once(ctx, false, k, src, dst, B, H, W, value, nullptr, st);
+    case 2: RUN(morph_once(ctx, true, k, src, tmp, B, H, W, value, nullptr, st));
+            return morph_once(ctx, false, k, tmp, dst, B, H, W, value, nullptr, st);
+    case 3: RUN(morph_once(ctx, false, k, src, tmp, B, H, W, value, nullptr, st));
+            return morph_once(ctx, true, k, tmp, dst, B, H, W, value, nullptr, st);
+  }
+  return ub_fail(ctx, UB_ERR_ARG, "bad morph op %d", op);
+}
+
+static int ccl_label(ub_ctx* ctx, const uint8_t* src, int* lab, int B, int H, int W, int* comp, size_t plane, cudaStream_t st) {
+  const int segs = (W + 31) / 32;
+  dim3 gseg(cdiv(H * segs * 32, 256), 1, B), gpix(cdiv(W, 256), H, B);
+  k_ccl_init<<<gseg, 256, 0, st>>>(src, lab, H, W);
+  k_ccl_merge<<<gpix, 256, 0, st>>>(lab, H, W);
+  k_ccl_flatten<<<gpix, 256, 0, st>>>(lab, H, W, comp, plane);
+  UB_CHECK_LAUNCH_N(ctx, 3);
+  return UB_OK;
+}
+
+int gaussian5(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_STENCIL, st);
+  k_gauss5<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), 256, 0, st>>>(src, dst, H, W);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+// cv2.Canny: candidates (stencil) then hysteresis (union-find).  cand: u8 scratch, lab: i32 scratch.
+int canny(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, uint8_t* cand, int* lab, int B, int H, int W, int low, int high, cudaStream_t st) {
+  dim3 gpix(cdiv(W, 256), H, B);
+  {
+    TimeScope ts(ctx, UB_T_STENCIL, st);
+    k_canny_nms<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), 256, 0, st>>>(src, cand, H, W, low, high);
+    UB_CHECK_LAUNCH(ctx);
+  }
+  TimeScope ts(ctx, UB_T_CCL, st);
+  RUN(ccl_label(ctx, cand, lab, B, H, W, nullptr, 0, st));
+  UB_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t)B * H * W, st));
+  k_hyst_mark<<<gpix, 256, 0, st>>>(cand, lab, dst, H, W);
+  k_hyst_final<<<gpix, 256, 0, st>>>(lab, dst, H, W);
+  UB_CHECK_LAUNCH_N(ctx, 2);
+  return UB_OK;
+}
+
+int enh_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int mode, int sobel_t, int lap_t,
+              const uint8_t* base_edges, uint8_t* out, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_STENCIL, st);
+  dim3 gpix(cdiv(W, 256), H, B);
+  int* fmax = ctx->d_counts + (size_t)ctx->max_batch * 8;          // [B] after the bg accumulators
+  if (mode & 1) {
+    UB_CUDA(ctx, cudaMemsetAsync(fmax, 0, sizeof(int) * B, st));
+    k_sobel_max<<<gpix, 256, 0, st>>>(gray, H, W, fmax);
+  }
+  k_enh_edges<<<gpix, 256, 0, st>>>(gray, H, W, fmax, mode, sobel_t, lap_t, base_edges, out);
+  UB_CHECK_LAUNCH_N(ctx, (mode & 1) ? 2 : 1);
+  return UB_OK;
+}
+
+// labels / stats in OpenCV numbering (ub_ccl)
+int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels, int* stats, int max_labels, int* n_labels, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
+  int* lab = ctx->d_lab[0];
+  int* mark = ctx->d_lab[1];
+  const int K = ((H + 1) / 2) * ((W + 1) / 2) * 4;
+  const int segs = (W + 31) / 32;
+  dim3 gseg(cdiv(H * segs * 32, 256), 1, B), gpix(cdiv(W, 256), H, B);
+  int* bg = ctx->d_counts;
+  RUN(ccl_label(ctx, src, lab, B, H, W, ctx->d_comp, plane, st));
+  k_bg_init<<<cdiv(B * 8, 256), 256, 0, st>>>(bg, B);
+  k_ccl_stats<<<gseg, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, bg);
+  UB_CUDA(ctx, cudaMemsetAsync(mark, 0, sizeof(int) * (size_t)B * K, st));
+  k_mark_roots<<<gpix, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, mark, K);
+  k_scan<<<B, 1024, 0, st>>>(mark, K, n_labels ? n_labels : bg + (size_t)ctx->max_batch * 8 + ctx->max_batch);
+  if (stats) UB_CUDA(ctx, cudaMemsetAsync(stats, 0, sizeof(int) * (size_t)B * max_labels * 5, st));
+  k_relabel<<<gpix, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, mark, K, labels, stats, max_labels, bg);
+  UB_CHECK_LAUNCH_N(ctx, 5);
+  return UB_OK;
+}
+
+// The whole burr stage for a batch.
+int burr_stage(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
+               const ub_burr_params& P, uint8_t* burr, int32_t* burr_px, int px_stride, cudaStream_t st) {
+  uint8_t *t0 = ctx->d_tmp[0], *t1 = ctx->d_tmp[1], *t2 = ctx->d_tmp[2], *t3 = ctx->d_tmp[3];
+  int* lab = ctx->d_lab[0];
+  const size_t n = (size_t)B * H * W;
+  const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
+  // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
+  RUN(gaussian5(ctx, gray, t0, B, H, W, st));
+  RUN(canny(ctx, t0, t1, t2, lab, B, H, W, P.canny_low, P.canny_high, st));
+  if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
+  {
+    TimeScope ts(ctx, UB_T_STENCIL, st);
+    // detection band = dilate(mask) & ~mask                                      [t0]
+    RUN(morph_once(ctx, true, P.band_k, mask, t0, B, H, W, 1, mask, st));
+    // candidates = edges & band                                                  [t2]
+    k_and01<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(t1, t0, t2, n);
+    UB_CHECK_LAUNCH(ctx);
+  }
+  RUN(morph_op(ctx, 2, P.close_k, t2, t1, t3, B, H, W, 1, st));                   // CLOSE -> t1
+  RUN(morph_op(ctx, 3, P.open_k, t1, t2, t3, B, H, W, 1, st));                    // OPEN  -> t2
+  // components + filter
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const int segs = (W + 31) / 32;
+  dim3 gseg(cdiv(H * segs * 32, 256), 1, B), gpix(cdiv(W, 256), H, B);
+  RUN(ccl_label(ctx, t2, lab, B, H, W, ctx->d_comp, plane, st));
+  k_ccl_stats<<<gseg, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, nullptr);
+  k_ccl_filter<<<gpix, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, P, burr, burr_px, px_stride);
+  UB_CHECK_LAUNCH_N(ctx, 2);
+  return UB_OK;
+}

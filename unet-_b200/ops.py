@@ -1,0 +1,126 @@
+"""Function contract of the reference's per-frame helpers, executed by libunetb200.
+
+Same names, argument meaning and results as the reference functions:
+  map_roi_to_original     infer_two_stage_burr.py:37-47
+  preprocess_image        infer_two_stage_burr.py:122-127
+  detect_burrs_on_cable   infer_two_stage_burr.py:50-119
+  detect_burrs_enhanced   infer_enhanced_burr.py:69-138
+  normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
+Each accepts what the reference accepts (one numpy frame on the host) and returns the same
+kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
+without touching the host.  All arithmetic runs in the CUDA library; there is no CPU path.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+FIXED_ROI_512 = {"x1": 140, "y1": 0, "x2": 270, "y2": 512}
+VERTICAL_ROI = {"x1": 200, "y1": 0, "x2": 600, "y2": 448}
+BURR_CONFIGS = {
+    "low": {"band_out": 10, "laplacian_threshold": 35, "min_area": 50, "max_area": 800, "morph_kernel": 3},
+    "medium": {"band_out": 15, "laplacian_threshold": 25, "min_area": 30, "max_area": 800, "morph_kernel": 3},
+    "high": {"band_out": 20, "laplacian_threshold": 20, "min_area": 20, "max_area": 1000, "morph_kernel": 5},
+}
+
+_contexts = {}
+
+
+def _ctx(device, batch, frame_hw, net_hw=(512, 512)) -> _lib.Context:
+    """Cached scratch context for stand-alone operator calls."""
+    dev = torch.device(device)
+    key = (dev.index or 0, tuple(frame_hw), tuple(net_hw))
+    c = _contexts.get(key)
+    if c is None or c.max_batch < batch:
+        if c is not None:
+            c.close()
+        c = _lib.Context(dev.index or 0, max_batch=max(batch, 1), frame_hw=frame_hw, net_hw=net_hw)
+        _contexts[key] = c
+    return c
+
+
+def _default_device():
+    if not torch.cuda.is_available():
+        raise _lib.UbError("no CUDA device: unet_b200 has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def map_roi_to_original(original_size, target_size=(512, 512)):
+    orig_w, orig_h = original_size
+    tw, th = target_size
+    sx, sy = orig_w / tw, orig_h / th
+    r = FIXED_ROI_512
+    return (int(r["x1"] * sx), int(r["y1"] * sy), int(r["x2"] * sx), int(r["y2"] * sy))
+
+
+def _batched(a, ndim_single):
+    """-> (cuda tensor with batch dim, was_numpy, was_single)"""
+    if isinstance(a, np.ndarray):
+        t = torch.from_numpy(np.ascontiguousarray(a)).to(_default_device())
+        return (t[None] if a.ndim == ndim_single else t).contiguous(), True, a.ndim == ndim_single
+    single = a.dim() == ndim_single
+    return (a[None] if single else a).contiguous(), False, single
+
+
+def _unbatch(t, was_numpy, was_single):
+    if was_single:
+        t = t[0]
+    return t.cpu().numpy() if was_numpy else t
+
+
+def preprocess_image(frame, target_size=(512, 512)):
+    """BGR uint8 frame [H,W,3] -> float32 tensor [3,th,tw] (RGB, /255).  A numpy frame gives a
+    CPU tensor like the reference; a CUDA uint8 tensor ([H,W,3] or [B,H,W,3]) stays on the GPU."""
+    f, was_np, single = _batched(frame, 3)
+    tw, th = target_size
+    c = _ctx(f.device, f.shape[0], tuple(f.shape[1:3]), (th, tw))
+    with torch.cuda.device(f.device):
+        x, _ = c.preprocess(f, want_x=True, want_gray=False)
+    x = x[0] if single else x
+    return x.cpu() if was_np else x
+
+
+def bgr2gray(frame):
+    """cv2.cvtColor(frame, COLOR_BGR2GRAY) (infer_two_stage_burr.py:317)."""
+    f, was_np, single = _batched(frame, 3)
+    c = _ctx(f.device, f.shape[0], tuple(f.shape[1:3]))
+    with torch.cuda.device(f.device):
+        _, g = c.preprocess(f, want_x=False, want_gray=True)
+    return _unbatch(g, was_np, single)
+
+
+def normalize_frame(frame, size=(800, 448), rotate=False):
+    f, was_np, single = _batched(frame, 3)
+    c = _ctx(f.device, f.shape[0], (size[1], size[0]))
+    with torch.cuda.device(f.device):
+        out = c.normalize_frames(f, size, rotate)
+    return _unbatch(out, was_np, single)
+
+
+def _detect(variant, frame_gray, mask_cable, params):
+    g, was_np, single = _batched(frame_gray, 2)
+    m, _, _ = _batched(mask_cable, 2)
+    c = _ctx(g.device, g.shape[0], tuple(g.shape[1:3]))
+    with torch.cuda.device(g.device):
+        out, _ = c.burr(g, m.to(g.device), variant, params)
+    return _unbatch(out, was_np, single)
+
+
+def detect_burrs_on_cable(frame_gray, mask_cable, config=None):
+    """Standard burr detector; only min_area / max_area of `config` are read, exactly like the
+    reference (infer_two_stage_burr.py:114)."""
+    cfg = config or {"min_area": 30, "max_area": 800}
+    return _detect(_lib.VARIANT_STANDARD, frame_gray, mask_cable,
+                   _lib.standard_params(cfg["min_area"], cfg["max_area"]))
+
+
+def detect_burrs_enhanced(frame_gray, mask_cable, config):
+    return _detect(_lib.VARIANT_ENHANCED, frame_gray, mask_cable,
+                   _lib.enhanced_params(config["min_area"], config["max_area"]))
+
+
+def enhance_image(frame):
+    raise NotImplementedError("enhance_image (CLAHE + NLM + sharpen, infer_enhanced_burr.py:38-66) is not built yet "
+                              "(SURVEY section 8 row a10); there is no CPU fallback")

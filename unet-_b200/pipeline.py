@@ -1,0 +1,95 @@
+"""Batched two-stage inspection step and frame-sharded multi-GPU driver.
+
+One call of :meth:`InspectionPipeline.run` is the body of the reference's hot loop
+(infer_two_stage_burr.py:286-343) for a whole batch of frames: preprocess -> NestedUNet ->
+argmax -> class masks -> ROI -> gray -> burr stage -> per-frame pixel counts.
+Frames are independent, so across GPUs they are sharded by contiguous index ranges (one
+process per GPU); the only exchange is an all-gather of the int32 [frames,4] statistics.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from .ops import BURR_CONFIGS, VERTICAL_ROI, map_roi_to_original
+
+
+def shard_range(n_items: int, rank: int, world: int):
+    """Contiguous block partition: rank r owns [r*n/world, (r+1)*n/world)."""
+    return (rank * n_items) // world, ((rank + 1) * n_items) // world
+
+
+def stats_line(idx, frame_no, total, cable_px, tape_px, burr_px, roi):
+    """The reference's progress line (infer_two_stage_burr.py:333-343,358-359)."""
+    x1, y1, x2, y2 = roi
+    area = (x2 - x1) * (y2 - y1)
+    cable = cable_px / area * 100 if area > 0 else 0
+    tape = tape_px / area * 100 if area > 0 else 0
+    burr = burr_px / area * 100 if area > 0 else 0
+    status = "[BURR!]" if burr_px > 0 else "[OK]"
+    return (f"[{idx:4d}] Frame {frame_no}/{total} {status} | "
+            f"Cable:{cable:5.1f}% Tape:{tape:5.1f}% Burr:{burr:5.1f}%")
+
+
+class InspectionPipeline:
+    def __init__(self, state_dict, batch: int, frame_hw=(448, 800), net_hw=(512, 512), variant="standard",
+                 sensitivity="medium", device=None, roi=None, num_classes=3):
+        if device is None:
+            device = torch.cuda.current_device()
+        self.ctx = _lib.Context(device, max_batch=batch, frame_hw=frame_hw, net_hw=net_hw, num_classes=num_classes)
+        self.ctx.set_weights(state_dict)
+        self.device = self.ctx.device
+        self.batch, self.frame_hw = batch, tuple(frame_hw)
+        self.variant = _lib.VARIANT_ENHANCED if variant == "enhanced" else _lib.VARIANT_STANDARD
+        if self.variant == _lib.VARIANT_ENHANCED:
+            self.params = _lib.enhanced_params()
+            r = VERTICAL_ROI
+            self.roi = roi or (r["x1"], r["y1"], r["x2"], r["y2"])
+        else:
+            cfg = BURR_CONFIGS[sensitivity]
+            self.params = _lib.standard_params(cfg["min_area"], cfg["max_area"])
+            self.roi = roi or map_roi_to_original((frame_hw[1], frame_hw[0]), (512, 512))
+
+    def run(self, frames: torch.Tensor, want_masks=False):
+        """frames: CUDA uint8 [B,H,W,3] BGR -> (stats int32 [B,4] on device, masks or None).
+        stats columns: index in batch, cable_px, tape_px, burr_px.  Asynchronous."""
+        with torch.cuda.device(self.device):
+            return self.ctx.pipeline(frames, self.variant, self.roi, self.params, want_masks)
+
+    def run_host(self, frames_host, stats_host=None, masks_host=None):
+        """frames_host: (pinned) uint8 [B,H,W,3] on the host -> stats int32 [B,4] on the host.
+        Includes the host->device and device->host copies; synchronous."""
+        b = frames_host.shape[0]
+        if stats_host is None:
+            stats_host = torch.empty((b, 4), dtype=torch.int32).pin_memory()
+        with torch.cuda.device(self.device):
+            self.ctx.pipeline_host(frames_host, stats_host, self.variant, self.roi, self.params, masks_host)
+        return stats_host
+
+    @staticmethod
+    def gather_stats(stats: torch.Tensor, frame_offset: int, group=None) -> torch.Tensor:
+        """All-gather per-frame statistics across ranks (NCCL on GPU tensors, gloo on CPU
+        tensors).  Column 0 becomes the global frame index.  Returns [sum B_r, 4] sorted by frame."""
+        import torch.distributed as dist
+        s = stats.clone()
+        s[:, 0] += frame_offset
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return s
+        world = dist.get_world_size(group)
+        n = torch.tensor([s.shape[0]], dtype=torch.int64, device=s.device)
+        sizes = [torch.zeros_like(n) for _ in range(world)]
+        dist.all_gather(sizes, n, group=group)
+        mx = int(max(int(x) for x in sizes))
+        pad = torch.full((mx, 4), -1, dtype=s.dtype, device=s.device)
+        pad[: s.shape[0]] = s
+        parts = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(parts, pad, group=group)
+        out = torch.cat([p[: int(k)] for p, k in zip(parts, sizes)], dim=0)
+        return out[torch.argsort(out[:, 0])]
+
+    def summary(self, all_stats) -> dict:
+        """Counters of infer_two_stage_burr.py:321-323,369-372 from gathered stats."""
+        a = all_stats.cpu().numpy() if isinstance(all_stats, torch.Tensor) else np.asarray(all_stats)
+        return {"frames": int(a.shape[0]), "burr_frames": int((a[:, 3] > 0).sum()),
+                "cable_px": int(a[:, 1].sum()), "tape_px": int(a[:, 2].sum()), "burr_px": int(a[:, 3].sum())}

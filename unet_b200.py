@@ -8,6 +8,7 @@ import os as _os
 
 _dir = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "unet-_b200")
 __path__ = [_dir]
+__package__ = __name__          # so `from .model import ...` inside __init__.py resolves
 if __spec__ is not None:
     __spec__.submodule_search_locations = __path__
 with open(_os.path.join(_dir, "__init__.py")) as _f:
