@@ -237,7 +237,7 @@ def run_ours(args):
                 "ms_per_step_by_class": {k: v[0] / args.steps for k, v in tm.items()}}
         line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "vs_baseline": None, "dtype": "f16", "data": "synthetic",
                 "config": {"workload": f"two_stage_pipeline_800x448_batch{B}", "frame": "800x448", "net": "512x512",
                            "batch_per_gpu": B, "parallelism": f"frames sharded over {world} GPU(s)",
                            "l2": "activation working set ~12 GB/step per GPU >> 126 MB L2; no explicit flush"},

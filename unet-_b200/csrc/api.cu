@@ -111,7 +111,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   auto fail = [&](int code) { ub_destroy(c); return code; };
   for (int i = 0; i < 22 && r == UB_OK; ++i) {
     size_t bytes = pp_bytes(max_batch, kActC[i], net_h >> kActL[i], net_w >> kActL[i]);
-    r = dmalloc(c, &c->act[i], bytes / sizeof(__nv_bfloat16));
+    r = dmalloc(c, &c->act[i], bytes / sizeof(act_t));
   }
   if (r) return fail(r);
   const size_t fpix = (size_t)max_batch * frame_h * frame_w, npix = (size_t)max_batch * net_h * net_w;
@@ -186,7 +186,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     RUN(get(bn + ".running_mean", d.cout, &mu));
     RUN(get(bn + ".running_var", d.cout, &var));
     const int kbn = cin_pad / d.kc, cpk = d.kc / 8, nnt = d.cout / d.bn;
-    std::vector<__nv_bfloat16> wp((size_t)d.cout * cin_pad * 9);
+    std::vector<act_t> wp((size_t)d.cout * cin_pad * 9);
     std::vector<float> bias(d.cout);
     for (int co = 0; co < d.cout; ++co) {
       const double scale = (double)g[co] / sqrt((double)var[co] + 1e-5);
@@ -201,7 +201,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
         for (int tap = 0; tap < 9; ++tap) {
           const float v = cr < 0 ? 0.f : (float)((double)w[((size_t)co * cin_real + cr) * 9 + tap] * scale);
           const size_t o = ((((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * d.bn + r) * 8) + j;
-          wp[o] = __float2bfloat16_rn(v);
+          wp[o] = f2a(v);
         }
       }
     }
@@ -210,7 +210,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn;
     if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
     if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
-    UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(act_t), cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
   const float *hw, *hb;
@@ -383,7 +383,7 @@ int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0, const float* x1, int 
   cudaStream_t st = as_stream(stream);
   // scratch: buffers of the same level that are large enough: in0 -> x/skip slot, in1 -> up slot, out -> t slot
   static const int in0[5] = {2, 5, 8, 11, 14}, in1[5] = {21, 19, 17, 15, 15}, outb[5] = {1, 4, 7, 10, 13};
-  __nv_bfloat16* s0 = layer == 0 ? ctx->act[0] : ctx->act[in0[lvl]];
+  act_t* s0 = layer == 0 ? ctx->act[0] : ctx->act[in0[lvl]];
   RUN(nchw_to_pp(ctx, x0, B, d.real_cin0, H, W, s0, d.cin0, st));
   if (x1) RUN(nchw_to_pp(ctx, x1, B, d.cin1, H, W, ctx->act[in1[lvl]], d.cin1, st));
   ConvArgs a{};

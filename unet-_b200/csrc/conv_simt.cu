@@ -6,8 +6,8 @@
 namespace {
 
 struct SimtParams {
-  const __nv_bfloat16* src0; const __nv_bfloat16* src1; __nv_bfloat16* out;
-  const __nv_bfloat16* w; const float* bias;
+  const act_t* src0; const act_t* src1; act_t* out;
+  const act_t* w; const float* bias;
   int B, cin0, cin1, cout, kc, bn;
   PPLayout L;
   const float* head_w; const float* head_b; int ncls; float* logits; uint8_t* pred;
@@ -35,25 +35,25 @@ __global__ void __launch_bounds__(128) k_conv_simt(SimtParams P) {
     if (interior) {
       int nt = (coc * 8) / P.bn, r0 = (coc * 8) % P.bn;
       for (int kb = 0; kb < kbn; ++kb) {
-        const __nv_bfloat16* plane0;
+        const act_t* plane0;
         if (kb < kb0) plane0 = P.src0 + ((size_t)b * nch0 + (size_t)kb * cpk) * L.Ppl * 8;
         else          plane0 = P.src1 + ((size_t)b * nch1 + (size_t)(kb - kb0) * cpk) * L.Ppl * 8;
         for (int tap = 0; tap < 9; ++tap) {
           int off = (tap / 3 - 1) * L.pitch + (tap % 3 - 1);
           for (int cc = 0; cc < cpk; ++cc) {
             uint4 iv = *reinterpret_cast<const uint4*>(plane0 + ((size_t)cc * L.Ppl + p + off) * 8);
-            const __nv_bfloat16* ih = reinterpret_cast<const __nv_bfloat16*>(&iv);
+            const act_t* ih = reinterpret_cast<const act_t*>(&iv);
             float fi[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) fi[j] = __bfloat162float(ih[j]);
-            const __nv_bfloat16* wp =
+            for (int j = 0; j < 8; ++j) fi[j] = a2f(ih[j]);
+            const act_t* wp =
                 P.w + (((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * P.bn + r0) * 8;
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
               uint4 wv = *reinterpret_cast<const uint4*>(wp + r * 8);
-              const __nv_bfloat16* wh = reinterpret_cast<const __nv_bfloat16*>(&wv);
+              const act_t* wh = reinterpret_cast<const act_t*>(&wv);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) acc[r] = fmaf(fi[j], __bfloat162float(wh[j]), acc[r]);
+              for (int j = 0; j < 8; ++j) acc[r] = fmaf(fi[j], a2f(wh[j]), acc[r]);
             }
           }
         }
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(128) k_conv_simt(SimtParams P) {
     }
     float v[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) v[r] = interior ? fmaxf(acc[r] + P.bias[coc * 8 + r], 0.f) : 0.f;
+    for (int r = 0; r < 8; ++r) v[r] = interior ? fminf(fmaxf(acc[r] + P.bias[coc * 8 + r], 0.f), UB_ACT_MAX) : 0.f;
     if (head) {
 #pragma unroll
       for (int c = 0; c < 8; ++c)
@@ -69,9 +69,9 @@ __global__ void __launch_bounds__(128) k_conv_simt(SimtParams P) {
 #pragma unroll
           for (int r = 0; r < 8; ++r) lg[c] = fmaf(P.head_w[c * P.cout + coc * 8 + r], v[r], lg[c]);
     } else {
-      __nv_bfloat16 h[8];
+      act_t h[8];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) h[r] = __float2bfloat16_rn(v[r]);
+      for (int r = 0; r < 8; ++r) h[r] = f2a(v[r]);
       *reinterpret_cast<uint4*>(P.out + (((size_t)b * nco_chunks + coc) * L.Ppl + p) * 8) =
           *reinterpret_cast<uint4*>(h);
     }

@@ -27,8 +27,8 @@ constexpr int SEG_BYTES = SEG_POS * 16;      // 2176
 constexpr int TILE_M = 128;
 
 struct TcParams {
-  const __nv_bfloat16* src0; const __nv_bfloat16* src1; __nv_bfloat16* out;
-  const __nv_bfloat16* w; const float* bias;
+  const act_t* src0; const act_t* src1; act_t* out;
+  const act_t* w; const float* bias;
   int B, kb0, kbn, nch0, nch1, cout, n_ntiles, num_stages, b_resident;
   long long total_items;
   PPLayout L;
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(TcParams P) {
           mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
         }
         __syncwarp();
-        const __nv_bfloat16* plane0 =
+        const act_t* plane0 =
             kb < P.kb0 ? P.src0 + ((size_t)b * P.nch0 + (size_t)kb * C::CPK) * L.Ppl * 8
                        : P.src1 + ((size_t)b * P.nch1 + (size_t)(kb - P.kb0) * C::CPK) * L.Ppl * 8;
         const uint32_t a_st = a_base + s * C::A_STAGE;
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(TcParams P) {
   } else if (warp == 5) {
     // ===================== MMA issuer (single thread) =====================
     if (lane == 0) {
-      constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+      constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)(TILE_M >> 4) << 24);
       int s = 0; uint32_t ph = 0; int it = 0;
       for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(TcParams P) {
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          f[j] = interior ? fmaxf(__uint_as_float(v[j]) + __ldg(P.bias + co0 + j), 0.f) : 0.f;
+          f[j] = interior ? fminf(fmaxf(__uint_as_float(v[j]) + __ldg(P.bias + co0 + j), 0.f), UB_ACT_MAX) : 0.f;
         if (P.head_w != nullptr) {
           if (interior) {
             float lg[8];
@@ -264,9 +264,9 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(TcParams P) {
         } else {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            __nv_bfloat162 h[4];
+            act2_t h[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[g * 8 + 2 * j], f[g * 8 + 2 * j + 1]);
+            for (int j = 0; j < 4; ++j) h[j] = f2a2(f[g * 8 + 2 * j], f[g * 8 + 2 * j + 1]);
             *reinterpret_cast<uint4*>(P.out + (((size_t)b * nco_chunks + (co0 >> 3) + g) * L.Ppl + L.G + q) * 8) =
                 *reinterpret_cast<uint4*>(h);
           }

@@ -10,26 +10,26 @@ __device__ __forceinline__ size_t pp_off(int b, int chunk, int nchunks, int Ppl,
 
 // fp32 NCHW -> bf16 PP (zero border, zero channel padding)
 __global__ void k_nchw_to_pp(const float* __restrict__ x, int B, int C, int H, int W,
-                             __nv_bfloat16* __restrict__ out, int nchunks, PPLayout L) {
+                             act_t* __restrict__ out, int nchunks, PPLayout L) {
   int q = blockIdx.x * blockDim.x + threadIdx.x;
   int chunk = blockIdx.y, b = blockIdx.z;
   if (q >= L.ntiles * 128) return;
   int yy = q / L.pitch, xx = q - yy * L.pitch;
   uint4 v = make_uint4(0, 0, 0, 0);
   if (q < L.npos && yy >= 1 && yy <= H && xx >= 1 && xx <= W) {
-    __nv_bfloat16 h[8];
+    act_t h[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       int c = chunk * 8 + j;
       float f = (c < C) ? x[(((size_t)b * C + c) * H + (yy - 1)) * W + (xx - 1)] : 0.f;
-      h[j] = __float2bfloat16_rn(f);
+      h[j] = f2a(f);
     }
     v = *reinterpret_cast<uint4*>(h);
   }
   *reinterpret_cast<uint4*>(out + pp_off(b, chunk, nchunks, L.Ppl, L.G + q)) = v;
 }
 
-__global__ void k_pp_to_nchw(const __nv_bfloat16* __restrict__ in, int B, int C, int H, int W,
+__global__ void k_pp_to_nchw(const act_t* __restrict__ in, int B, int C, int H, int W,
                              float* __restrict__ out, int nchunks, PPLayout L) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   int y = blockIdx.y, bc = blockIdx.z;
@@ -37,26 +37,26 @@ __global__ void k_pp_to_nchw(const __nv_bfloat16* __restrict__ in, int B, int C,
   if (x >= W) return;
   int p = L.G + (y + 1) * L.pitch + x + 1;
   uint4 v = *reinterpret_cast<const uint4*>(in + pp_off(b, chunk, nchunks, L.Ppl, p));
-  const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&v);
+  const act_t* h = reinterpret_cast<const act_t*>(&v);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     int c = chunk * 8 + j;
-    if (c < C) out[(((size_t)b * C + c) * H + y) * W + x] = __bfloat162float(h[j]);
+    if (c < C) out[(((size_t)b * C + c) * H + y) * W + x] = a2f(h[j]);
   }
 }
 
 __device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
   uint4 r;
-  const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
-  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
-  __nv_bfloat162* pr = reinterpret_cast<__nv_bfloat162*>(&r);
+  const act2_t* pa = reinterpret_cast<const act2_t*>(&a);
+  const act2_t* pb = reinterpret_cast<const act2_t*>(&b);
+  act2_t* pr = reinterpret_cast<act2_t*>(&r);
 #pragma unroll
   for (int i = 0; i < 4; ++i) pr[i] = __hmax2(pa[i], pb[i]);
   return r;
 }
 
 // MaxPool2d(2,2) (src/models/unetpp.py:75): in [H,W] -> out [H/2,W/2], both PP.
-__global__ void k_maxpool2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+__global__ void k_maxpool2(const act_t* __restrict__ in, act_t* __restrict__ out,
                            int nchunks, PPLayout Li, PPLayout Lo) {
   int q = blockIdx.x * blockDim.x + threadIdx.x;
   int chunk = blockIdx.y, b = blockIdx.z;
@@ -65,7 +65,7 @@ __global__ void k_maxpool2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* 
   uint4 v = make_uint4(0, 0, 0, 0);
   if (q < Lo.npos && yy >= 1 && yy <= Lo.H && xx >= 1 && xx <= Lo.W) {
     int iy = 2 * (yy - 1), ix = 2 * (xx - 1);
-    const __nv_bfloat16* base = in + pp_off(b, chunk, nchunks, Li.Ppl, Li.G + (iy + 1) * Li.pitch + ix + 1);
+    const act_t* base = in + pp_off(b, chunk, nchunks, Li.Ppl, Li.G + (iy + 1) * Li.pitch + ix + 1);
     uint4 a = *reinterpret_cast<const uint4*>(base);
     uint4 c = *reinterpret_cast<const uint4*>(base + 8);
     uint4 d = *reinterpret_cast<const uint4*>(base + (size_t)Li.pitch * 8);
@@ -77,7 +77,7 @@ __global__ void k_maxpool2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* 
 
 // Upsample(scale 2, bilinear, align_corners=True) (src/models/unetpp.py:76):
 // src = dst * (in-1)/(out-1) in fp32, as ATen's area_pixel_compute_source_index does.
-__global__ void k_upsample2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+__global__ void k_upsample2(const act_t* __restrict__ in, act_t* __restrict__ out,
                             int nchunks, PPLayout Li, PPLayout Lo, float sy, float sx) {
   int q = blockIdx.x * blockDim.x + threadIdx.x;
   int chunk = blockIdx.y, b = blockIdx.z;
@@ -89,22 +89,22 @@ __global__ void k_upsample2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16*
     int y0 = (int)fy, x0 = (int)fx;
     float ly = fy - (float)y0, lx = fx - (float)x0;
     int y1 = y0 + (y0 < Li.H - 1 ? 1 : 0), x1 = x0 + (x0 < Li.W - 1 ? 1 : 0);
-    const __nv_bfloat16* pl = in + pp_off(b, chunk, nchunks, Li.Ppl, 0);
+    const act_t* pl = in + pp_off(b, chunk, nchunks, Li.Ppl, 0);
     auto ld = [&](int y, int x) {
       return *reinterpret_cast<const uint4*>(pl + (size_t)(Li.G + (y + 1) * Li.pitch + x + 1) * 8);
     };
     uint4 a = ld(y0, x0), c = ld(y0, x1), d = ld(y1, x0), e = ld(y1, x1);
-    const __nv_bfloat16* ha = reinterpret_cast<const __nv_bfloat16*>(&a);
-    const __nv_bfloat16* hc = reinterpret_cast<const __nv_bfloat16*>(&c);
-    const __nv_bfloat16* hd = reinterpret_cast<const __nv_bfloat16*>(&d);
-    const __nv_bfloat16* he = reinterpret_cast<const __nv_bfloat16*>(&e);
-    __nv_bfloat16 r[8];
+    const act_t* ha = reinterpret_cast<const act_t*>(&a);
+    const act_t* hc = reinterpret_cast<const act_t*>(&c);
+    const act_t* hd = reinterpret_cast<const act_t*>(&d);
+    const act_t* he = reinterpret_cast<const act_t*>(&e);
+    act_t r[8];
     float wy0 = 1.f - ly, wx0 = 1.f - lx;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float top = wx0 * __bfloat162float(ha[j]) + lx * __bfloat162float(hc[j]);
-      float bot = wx0 * __bfloat162float(hd[j]) + lx * __bfloat162float(he[j]);
-      r[j] = __float2bfloat16_rn(wy0 * top + ly * bot);
+      float top = wx0 * a2f(ha[j]) + lx * a2f(hc[j]);
+      float bot = wx0 * a2f(hd[j]) + lx * a2f(he[j]);
+      r[j] = f2a(wy0 * top + ly * bot);
     }
     v = *reinterpret_cast<uint4*>(r);
   }
@@ -113,7 +113,7 @@ __global__ void k_upsample2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16*
 
 }  // namespace
 
-int nchw_to_pp(ub_ctx* ctx, const float* x, int B, int C, int H, int W, __nv_bfloat16* out,
+int nchw_to_pp(ub_ctx* ctx, const float* x, int B, int C, int H, int W, act_t* out,
                int Cpad, cudaStream_t st) {
   PPLayout L = pp_layout(H, W);
   TimeScope ts(ctx, UB_T_GLUE, st);
@@ -123,7 +123,7 @@ int nchw_to_pp(ub_ctx* ctx, const float* x, int B, int C, int H, int W, __nv_bfl
   return UB_OK;
 }
 
-int pp_to_nchw(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int W, float* out,
+int pp_to_nchw(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W, float* out,
                cudaStream_t st) {
   PPLayout L = pp_layout(H, W);
   int nchunks = (C + 7) / 8;
@@ -134,8 +134,8 @@ int pp_to_nchw(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int W,
   return UB_OK;
 }
 
-int maxpool2_pp(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int W,
-                __nv_bfloat16* out, cudaStream_t st) {
+int maxpool2_pp(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W,
+                act_t* out, cudaStream_t st) {
   PPLayout Li = pp_layout(H, W), Lo = pp_layout(H / 2, W / 2);
   TimeScope ts(ctx, UB_T_GLUE, st);
   dim3 grid(cdiv(Lo.ntiles * 128, 256), C / 8, B);
@@ -144,8 +144,8 @@ int maxpool2_pp(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int W
   return UB_OK;
 }
 
-int upsample2_pp(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int W,
-                 __nv_bfloat16* out, cudaStream_t st) {
+int upsample2_pp(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W,
+                 act_t* out, cudaStream_t st) {
   PPLayout Li = pp_layout(H, W), Lo = pp_layout(2 * H, 2 * W);
   float sy = (2 * H > 1) ? (float)(H - 1) / (float)(2 * H - 1) : 0.f;
   float sx = (2 * W > 1) ? (float)(W - 1) / (float)(2 * W - 1) : 0.f;
@@ -160,8 +160,8 @@ int upsample2_pp(ub_ctx* ctx, const __nv_bfloat16* in, int B, int C, int H, int 
 enum { A_XIN = 0, A_T0, A_X00, A_P0, A_T1, A_X10, A_P1, A_T2, A_X20, A_P2, A_T3, A_X30, A_P3,
        A_T4, A_X40, A_UP4, A_X31, A_UP3, A_X22, A_UP2, A_X13, A_UP1, A_X04 };
 
-static int run_conv(ub_ctx* ctx, int li, const __nv_bfloat16* s0, const __nv_bfloat16* s1,
-                    __nv_bfloat16* out, int B, int H, int W, cudaStream_t st,
+static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
+                    act_t* out, int B, int H, int W, cudaStream_t st,
                     float* logits = nullptr, uint8_t* pred = nullptr, bool head = false) {
   ConvArgs a{};
   a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W;
@@ -177,7 +177,7 @@ static int run_conv(ub_ctx* ctx, int li, const __nv_bfloat16* s0, const __nv_bfl
 
 // Input already in act[A_XIN] (PP, 16 channels).  Writes logits (fp32 NCHW) and/or pred.
 int net_forward_pp(ub_ctx* ctx, int B, int H, int W, float* logits, uint8_t* pred, cudaStream_t st) {
-  __nv_bfloat16** A = ctx->act;
+  act_t** A = ctx->act;
   int h1 = H / 2, w1 = W / 2, h2 = H / 4, w2 = W / 4, h3 = H / 8, w3 = W / 8, h4 = H / 16, w4 = W / 16;
   // encoder (unetpp.py:104-108)
   RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));

@@ -87,7 +87,7 @@ struct SrcRot {
 // preprocess_image (infer_two_stage_burr.py:122-127): BGR->RGB, resize, /255.
 __global__ void k_preprocess(const uint8_t* __restrict__ frames, int H, int W, int nh, int nw,
                              const int4* __restrict__ ty, const int4* __restrict__ tx,
-                             __nv_bfloat16* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L) {
+                             act_t* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L) {
   int q = blockIdx.x * blockDim.x + threadIdx.x;
   int b = blockIdx.y;
   if (q >= L.ntiles * 128) return;
@@ -97,16 +97,16 @@ __global__ void k_preprocess(const uint8_t* __restrict__ frames, int H, int W, i
   if (interior) {
     SrcPlain S{frames + (size_t)b * H * W * 3, W};
     int4 cy = ty[yy - 1], cx = tx[xx - 1];
-    __nv_bfloat16 h[8];
+    act_t h[8];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       int u = bilerp(S, cy, cx, 2 - c);                       // RGB order: channel c reads B,G,R[2-c]
       float f = __fdiv_rn((float)u, 255.0f);
-      h[c] = __float2bfloat16_rn(f);
+      h[c] = f2a(f);
       if (x_nchw) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = f;
     }
 #pragma unroll
-    for (int c = 3; c < 8; ++c) h[c] = __float2bfloat16_rn(0.f);
+    for (int c = 3; c < 8; ++c) h[c] = f2a(0.f);
     v = *reinterpret_cast<uint4*>(h);
   }
   if (x_pp) *reinterpret_cast<uint4*>(x_pp + (((size_t)b * 2) * L.Ppl + L.G + q) * 8) = v;
@@ -189,7 +189,7 @@ __global__ void k_stats_init(int32_t* stats, int B) {
 }  // namespace
 
 int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, int nh, int nw,
-                      __nv_bfloat16* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t st) {
+                      act_t* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t st) {
   if (x_pp || x_nchw) {
     const int4 *ty, *tx;
     int r = get_table(ctx, H, nh, false, &ty, st); if (r) return r;
