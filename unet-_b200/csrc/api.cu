@@ -48,18 +48,18 @@ int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cu
 
 // ---------------------------------------------------------------- layer tables
 namespace {
-struct LayerDef { const char* block; int idx; int cin0, cin1, cout, kc, bn; int real_cin0; };
+struct LayerDef { const char* block; int idx; int cin0, cin1, cout, kc, bn; int real_cin0; int fold; };
 // cin0 of the first layer is the 3 input channels zero-padded to 16 (one UMMA K step)
 const LayerDef kLayers[18] = {
-    {"conv0_0", 1, 16, 0, 32, 16, 32, 3},     {"conv0_0", 2, 32, 0, 32, 32, 32, 32},
-    {"conv1_0", 1, 32, 0, 64, 32, 64, 32},    {"conv1_0", 2, 64, 0, 64, 32, 64, 64},
-    {"conv2_0", 1, 64, 0, 128, 16, 128, 64},  {"conv2_0", 2, 128, 0, 128, 16, 128, 128},
-    {"conv3_0", 1, 128, 0, 256, 16, 256, 128}, {"conv3_0", 2, 256, 0, 256, 16, 256, 256},
-    {"conv4_0", 1, 256, 0, 512, 16, 256, 256}, {"conv4_0", 2, 512, 0, 512, 16, 256, 512},
-    {"conv3_1", 1, 256, 512, 256, 16, 256, 256}, {"conv3_1", 2, 256, 0, 256, 16, 256, 256},
-    {"conv2_2", 1, 128, 256, 128, 16, 128, 128}, {"conv2_2", 2, 128, 0, 128, 16, 128, 128},
-    {"conv1_3", 1, 64, 128, 64, 32, 64, 64},  {"conv1_3", 2, 64, 0, 64, 32, 64, 64},
-    {"conv0_4", 1, 32, 64, 32, 32, 32, 32},   {"conv0_4", 2, 32, 0, 32, 32, 32, 32},
+    {"conv0_0", 1, 16, 0, 32, 16, 32, 3, 1},     {"conv0_0", 2, 32, 0, 32, 32, 32, 32, 1},
+    {"conv1_0", 1, 32, 0, 64, 32, 64, 32, 1},    {"conv1_0", 2, 64, 0, 64, 32, 64, 64, 1},
+    {"conv2_0", 1, 64, 0, 128, 16, 128, 64, 0},  {"conv2_0", 2, 128, 0, 128, 16, 128, 128, 0},
+    {"conv3_0", 1, 128, 0, 256, 16, 256, 128, 0}, {"conv3_0", 2, 256, 0, 256, 16, 256, 256, 0},
+    {"conv4_0", 1, 256, 0, 512, 16, 256, 256, 0}, {"conv4_0", 2, 512, 0, 512, 16, 256, 512, 0},
+    {"conv3_1", 1, 256, 512, 256, 16, 256, 256, 0}, {"conv3_1", 2, 256, 0, 256, 16, 256, 256, 0},
+    {"conv2_2", 1, 128, 256, 128, 16, 128, 128, 0}, {"conv2_2", 2, 128, 0, 128, 16, 128, 128, 0},
+    {"conv1_3", 1, 64, 128, 64, 32, 64, 64, 1},  {"conv1_3", 2, 64, 0, 64, 32, 64, 64, 1},
+    {"conv0_4", 1, 32, 64, 32, 32, 32, 32, 1},   {"conv0_4", 2, 32, 0, 32, 32, 32, 32, 1},
 };
 // activation buffers: channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu
 const int kActC[23] = {16, 32, 32, 32, 64, 64, 64, 128, 128, 128, 256, 256, 256, 512, 512, 512, 256, 256, 128, 128, 64, 64, 0};
@@ -124,7 +124,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
   if (r) return fail(r);
-  if ((r = conv_tc_init(c)) != UB_OK) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_fold_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
   *out = c;
@@ -200,14 +200,15 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
         const int kb = ci / d.kc, cc = (ci % d.kc) / 8, j = ci % 8;
         for (int tap = 0; tap < 9; ++tap) {
           const float v = cr < 0 ? 0.f : (float)((double)w[((size_t)co * cin_real + cr) * 9 + tap] * scale);
-          const size_t o = ((((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * d.bn + r) * 8) + j;
+          const size_t o = d.fold ? (((((size_t)kb * 3 + tap / 3) * cpk + cc) * (3 * d.cout) + (tap % 3) * d.cout + co) * 8) + j
+                                  : ((((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * d.bn + r) * 8) + j;
           wp[o] = f2a(v);
         }
       }
     }
     (void)nnt;
     ConvLayer& L = ctx->conv[li];
-    L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn;
+    L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn; L.fold = d.fold;
     if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
     if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
     UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(act_t), cudaMemcpyHostToDevice));
@@ -220,6 +221,8 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
   if (!ctx->head_b) RUN(dmalloc(ctx, &ctx->head_b, (size_t)ctx->num_classes));
   UB_CUDA(ctx, cudaMemcpy(ctx->head_w, hw, sizeof(float) * ctx->num_classes * 32, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(ctx->head_b, hb, sizeof(float) * ctx->num_classes, cudaMemcpyHostToDevice));
+  memcpy(ctx->head_host, hw, sizeof(float) * ctx->num_classes * 32);
+  memcpy(ctx->head_host + ctx->num_classes * 32, hb, sizeof(float) * ctx->num_classes);
   ctx->weights_set = true;
   return UB_OK;
 }
@@ -388,7 +391,7 @@ int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0, const float* x1, int 
   if (x1) RUN(nchw_to_pp(ctx, x1, B, d.cin1, H, W, ctx->act[in1[lvl]], d.cin1, st));
   ConvArgs a{};
   a.src0 = s0; a.src1 = x1 ? ctx->act[in1[lvl]] : nullptr; a.out = ctx->act[outb[lvl]]; a.B = B; a.H = H; a.W = W;
-  RUN(ctx->conv_impl == 1 ? conv3x3_simt(ctx, ctx->conv[layer], a, st) : conv3x3_tc(ctx, ctx->conv[layer], a, st));
+  RUN(run_conv_layer(ctx, ctx->conv[layer], a, st));
   return pp_to_nchw(ctx, ctx->act[outb[lvl]], B, d.cout, H, W, out, st);
 }
 

@@ -59,6 +59,7 @@ struct PPLayout {
   int G;           // leading guard (positions), multiple of 8
   int npos;        // (H+2)*(W+2)
   int ntiles;      // ceil(npos / 128)
+  int ntiles_fold; // ceil(npos / 126): tiles of the kx-folded conv kernel (126 valid rows + 2 halo)
   int Ppl;         // positions per plane, multiple of 8
 };
 
@@ -68,7 +69,8 @@ static inline PPLayout pp_layout(int H, int W) {
   L.G = ((W + 3) + 7) & ~7;
   L.npos = (H + 2) * (W + 2);
   L.ntiles = (L.npos + 127) / 128;
-  L.Ppl = ((L.G + L.ntiles * 128 + (W + 3) + 8) + 7) & ~7;
+  L.ntiles_fold = (L.npos + 125) / 126;
+  L.Ppl = ((L.G + L.npos + 400 + (W + 3)) + 7) & ~7;   // covers the over-reads of both tilings
   return L;
 }
 static inline size_t pp_bytes(int B, int C, int H, int W) {
@@ -84,6 +86,7 @@ struct ConvLayer {
   int cout;
   int kc;              // channels per k-block (16 / 32 / 64); divides cin0 and cin1
   int bn;              // N tile (<= 256); divides cout
+  int fold = 0;        // 1: kx-folded weights [kblock][ky][kc/8][kx*cout+co][8] (conv_fold.cu, cout <= 64)
   // weights bf16 [cout/bn][kblocks][9 taps][kc/8][bn][8], bias fp32 [cout]
   act_t* w = nullptr;
   float* bias = nullptr;
@@ -111,6 +114,7 @@ struct ub_ctx {
   ConvLayer conv[18];
   float* head_w = nullptr;           // [num_classes][32] fp32
   float* head_b = nullptr;           // [num_classes]
+  float head_host[8 * 33] = {0};     // host mirror: [num_classes][32] weights then [num_classes] biases
   // activation arena (PP layout, sized for max_batch at net_h x net_w)
   act_t* act[24] = {nullptr};
   // pre/post + stage-2 scratch
@@ -167,6 +171,9 @@ struct ConvArgs {
 int conv3x3_simt(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_tc_init(ub_ctx* ctx);
+int conv3x3_fold(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
+int conv_fold_init(ub_ctx* ctx);
+int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // net_glue.cu
 int nchw_to_pp(ub_ctx*, const float* x, int B, int C, int H, int W, act_t* out, int Cpad, cudaStream_t);

@@ -8,7 +8,7 @@ namespace {
 struct SimtParams {
   const act_t* src0; const act_t* src1; act_t* out;
   const act_t* w; const float* bias;
-  int B, cin0, cin1, cout, kc, bn;
+  int B, cin0, cin1, cout, kc, bn, fold;
   PPLayout L;
   const float* head_w; const float* head_b; int ncls; float* logits; uint8_t* pred;
 };
@@ -47,7 +47,8 @@ __global__ void __launch_bounds__(128) k_conv_simt(SimtParams P) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) fi[j] = a2f(ih[j]);
             const act_t* wp =
-                P.w + (((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * P.bn + r0) * 8;
+                P.fold ? P.w + ((((size_t)kb * 3 + tap / 3) * cpk + cc) * (3 * P.cout) + (tap % 3) * P.cout + coc * 8) * 8
+                       : P.w + (((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * P.bn + r0) * 8;
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
               uint4 wv = *reinterpret_cast<const uint4*>(wp + r * 8);
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(128) k_conv_simt(SimtParams P) {
 int conv3x3_simt(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t st) {
   SimtParams P{};
   P.src0 = a.src0; P.src1 = a.src1; P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
-  P.B = a.B; P.cin0 = Lr.cin0; P.cin1 = Lr.cin1; P.cout = Lr.cout; P.kc = Lr.kc; P.bn = Lr.bn;
+  P.B = a.B; P.cin0 = Lr.cin0; P.cin1 = Lr.cin1; P.cout = Lr.cout; P.kc = Lr.kc; P.bn = Lr.bn; P.fold = Lr.fold;
   P.L = pp_layout(a.H, a.W);
   P.head_w = a.head_w; P.head_b = a.head_b; P.ncls = a.num_classes; P.logits = a.logits; P.pred = a.pred;
   if (a.head_w && Lr.cout != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == 32");

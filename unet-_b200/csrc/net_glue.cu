@@ -160,6 +160,11 @@ int upsample2_pp(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W,
 enum { A_XIN = 0, A_T0, A_X00, A_P0, A_T1, A_X10, A_P1, A_T2, A_X20, A_P2, A_T3, A_X30, A_P3,
        A_T4, A_X40, A_UP4, A_X31, A_UP3, A_X22, A_UP2, A_X13, A_UP1, A_X04 };
 
+int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st) {
+  if (ctx->conv_impl == 1) return conv3x3_simt(ctx, L, a, st);
+  return L.fold ? conv3x3_fold(ctx, L, a, st) : conv3x3_tc(ctx, L, a, st);
+}
+
 static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
                     act_t* out, int B, int H, int W, cudaStream_t st,
                     float* logits = nullptr, uint8_t* pred = nullptr, bool head = false) {
@@ -169,8 +174,7 @@ static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
     a.head_w = ctx->head_w; a.head_b = ctx->head_b; a.num_classes = ctx->num_classes;
     a.logits = logits; a.pred = pred;
   }
-  return ctx->conv_impl == 1 ? conv3x3_simt(ctx, ctx->conv[li], a, st)
-                             : conv3x3_tc(ctx, ctx->conv[li], a, st);
+  return run_conv_layer(ctx, ctx->conv[li], a, st);
 }
 
 #define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
