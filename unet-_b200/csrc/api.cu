@@ -124,7 +124,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
   if (r) return fail(r);
-  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_fold_init(c)) != UB_OK) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_fold_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
   *out = c;
@@ -152,7 +152,7 @@ void ub_destroy(ub_ctx* c) {
 
 int ub_set_conv_impl(ub_ctx* ctx, int impl) {
   NEED_CTX(ctx);
-  if (impl < 0 || impl > 2) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A)", impl);
+  if (impl < 0 || impl > 3) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A, 3 tcgen05 flat kx-fold)", impl);
   ctx->conv_impl = impl;
   return UB_OK;
 }

@@ -107,7 +107,7 @@ struct Timing {
 struct ub_ctx {
   int device = 0, sm_count = 148;
   int max_batch = 0, frame_h = 0, frame_w = 0, net_h = 0, net_w = 0, num_classes = 3;
-  int conv_impl = 0;                 // 0 tcgen05, 1 simt, 2 tcgen05 with aligned A segments
+  int conv_impl = 0;                 // 0 tcgen05, 1 simt, 2 tcgen05 with aligned A segments, 3 tcgen05 with the flat kx-fold kernel
   int64_t launches = 0;              // kernels launched so far
   std::string err;
   bool weights_set = false;
@@ -173,6 +173,8 @@ int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t 
 int conv_tc_init(ub_ctx* ctx);
 int conv3x3_fold(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_fold_init(ub_ctx* ctx);
+int conv3x3_rows(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
+int conv_rows_init(ub_ctx* ctx);
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // net_glue.cu

@@ -1,0 +1,335 @@
+// conv_rows.cu -- 3x3 conv (+folded BN bias, ReLU, optional fused 1x1 head + argmax) for the
+// two high-resolution pyramid levels (Cout = 32 / 64), the layers that hold the pixels.
+//
+// Replaces ConvBlock.forward's conv+bn+relu (src/models/unetpp.py:23-26) and, for the last
+// layer, `final` (unetpp.py:119) + softmax/argmax (infer_two_stage_burr.py:299-300).
+//
+// GEMM view.  The kernel's x-taps are folded into the GEMM N dimension (N' = 3*Cout, so one
+// activation tile feeds all three x-taps and the shared-memory operand path is not the limit:
+// 128 B/clk feeds N' = 96 at 86 % and N' = 192 at 100 % of the tensor pipe, N = 32 only 40 %):
+//   D[(r,l), kx*Cout+co] = sum_{ky,ci} X[y0+r+ky-1, x0-1+l, ci] * W[co,ky,kx,ci]
+//   out[y0+r, x0-1+l, co] = D[(r,l-1), 0*Cout+co] + D[(r,l), 1*Cout+co] + D[(r,l+1), 2*Cout+co]
+// One work item is a 2-D tile of 4 image rows x 32 columns (M = 128: TMEM lane = r*32 + l, so
+// warp = image row, lane = column).  The column neighbours l-1 / l+1 are lanes of the same
+// warp -> two shuffles, no cross-warp exchange; columns 1..30 of a tile are valid and tiles
+// advance by 30 columns.  The six input rows y0-1..y0+4 are staged ONCE per k-block as six
+// 512-byte segments (cp.async.bulk -> UBLKCP); the A operand of tap row ky is segments
+// ky..ky+3, i.e. a +512 B descriptor offset -- half the L2->shared traffic of staging three
+// shifted copies.  Weights stay resident in shared memory when they fit.
+//
+// Warp roles (576 threads): warps 0-15 epilogue, warp 16 bulk-copy producer (+TMEM alloc),
+// warp 17 MMA issuer (one elected lane).  TMEM holds four accumulators of 96 columns (Cout 32,
+// one per epilogue warpgroup) or two of 192 columns (Cout 64, two warpgroups per accumulator,
+// 32 channels each), so the MMAs of tiles i+1.. overlap the epilogue of tile i.
+// Epilogue arithmetic is packed (FADD2, F2FP.RELU.SATFINITE.PACK) -- it is the instruction-
+// bound part of these layers (profiles/r01_conv.md).
+#include <string.h>
+#include "tc_ptx.cuh"
+#include "tmap.cuh"
+
+namespace {
+using namespace tcp;
+
+constexpr int T_ROWS = 4, T_COLS = 32, T_VALID = 30, N_SEG = T_ROWS + 2;
+constexpr int SEG_BYTES = T_COLS * 16;            // one staged row segment of one 8-channel chunk
+
+struct RowsParams {
+  alignas(64) CUtensorMap tm0;                 // source 0 (skip) and source 1 (upsampled): tmap_pp_rows views,
+  alignas(64) CUtensorMap tm1;                 // box = 6 rows x 32 columns x KC/8 chunks
+  act_t* out;
+  const act_t* w; const float* bias;
+  int B, kb0, kbn, num_stages, b_resident;
+  int tiles_x, tiles_y;
+  long long total_items;
+  PPLayout L;
+  int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
+  float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
+};
+
+template <int COUT, int KC>
+struct RCfg {
+  static constexpr int NP = 3 * COUT;                          // folded N
+  static constexpr int CPK = KC / 8;
+  static constexpr int A_CHUNK = N_SEG * SEG_BYTES;            // six segments of one chunk: 3072 B
+  static constexpr int A_STAGE = CPK * A_CHUNK;
+  static constexpr int B_KY = KC * NP * 2;                     // one ky of one k-block
+  static constexpr int B_STAGE = 3 * B_KY;
+  static constexpr bool SPLIT = COUT == 64;                    // two warpgroups share one accumulator
+  static constexpr int NBUF = SPLIT ? 2 : 4;
+  static constexpr int T_STRIDE = SPLIT ? 256 : 128;           // TMEM columns per accumulator slot
+  static constexpr int WARPS_PER_BUF = SPLIT ? 8 : 4;
+  static constexpr int HDR = 1024;                             // barriers, TMEM slot, bias
+};
+
+__device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// relu + saturate-to-finite + round to two 16-bit activations (lo in the low half)
+__device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
+  uint32_t lo, hi, r;
+  asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+#ifdef UB_ACT_BF16
+  asm("cvt.rn.relu.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
+#else
+  asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
+#endif
+  return r;
+}
+
+template <int COUT, int KC>
+__global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
+  using C = RCfg<COUT, KC>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = P.num_stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * S;
+  const uint32_t bar_tfull = bar_empty + 8 * S, bar_tempty = bar_tfull + 8 * 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 8));
+  float* s_bias = reinterpret_cast<float*>(smem + 512);        // [COUT] (<= 64 floats)
+  const uint32_t a_base = smem_u32(smem) + C::HDR;
+  const uint32_t b_base = a_base + S * C::A_STAGE;
+  const PPLayout& L = P.L;
+  const int tiles_per_img = P.tiles_x * P.tiles_y;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, C::WARPS_PER_BUF); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x < COUT) s_bias[threadIdx.x] = P.bias[threadIdx.x];
+  if (warp == 16) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 16) {
+    // ===================== producer: one TMA box (+ one weight copy) per k-block =====================
+    if (lane == 0) {
+      tma_prefetch_desc(&P.tm0);
+      tma_prefetch_desc(&P.tm1);
+      int s = 0; uint32_t ph = 0; bool first = true;
+      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x) {
+        const int b = (int)(item / tiles_per_img), t = (int)(item - (long long)b * tiles_per_img);
+        const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
+        const bool load_b = !P.b_resident || first;
+        for (int kb = 0; kb < P.kbn; ++kb) {
+          const uint32_t full = bar_full + 8 * s;
+          mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
+          // box origin: padded row 4*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
+          if (kb < P.kb0) tma_load_5d(a_base + s * C::A_STAGE, &P.tm0, 0, tx * T_VALID, ty * T_ROWS, kb * C::CPK, b, full);
+          else tma_load_5d(a_base + s * C::A_STAGE, &P.tm1, 0, tx * T_VALID, ty * T_ROWS, (kb - P.kb0) * C::CPK, b, full);
+          if (load_b)
+            bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE, P.w + (size_t)kb * 3 * (size_t)(KC * C::NP), C::B_STAGE, full);
+          if (++s == S) { s = 0; ph ^= 1; }
+        }
+        first = false;
+      }
+    }
+  } else if (warp == 17) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) |
+                                 ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int s = 0; uint32_t ph = 0; int it = 0;
+      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+        const int buf = it % C::NBUF, use = it / C::NBUF;
+        mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
+        for (int kb = 0; kb < P.kbn; ++kb) {
+          mbar_wait(bar_full + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_st = a_base + s * C::A_STAGE;
+          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+            for (int k16 = 0; k16 < KC / 16; ++k16) {
+              // A: rows 16 B apart, 8-row groups 128 B apart, the two K chunks A_CHUNK apart
+              const uint64_t ad = make_desc(a_st + 2 * k16 * C::A_CHUNK + ky * SEG_BYTES, C::A_CHUNK, 128);
+              const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
+              tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+            }
+          }
+          tc_commit(bar_empty + 8 * s);
+          if (++s == S) { s = 0; ph ^= 1; }
+        }
+        tc_commit(bar_tfull + 8 * buf);
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 0-15) =====================
+    const int wq = warp & 3;                                   // TMEM lane quarter = tile row
+    const int grp = warp >> 2;
+    const int my_buf = C::SPLIT ? (grp >> 1) : grp;
+    const int ch0 = C::SPLIT ? (grp & 1) * 32 : 0;             // first of this warp's 32 channels
+    constexpr int NCHUNK = COUT / 8;
+    int it = 0;
+    for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+      if (it % C::NBUF != my_buf) continue;
+      const int use = it / C::NBUF;
+      const int b = (int)(item / tiles_per_img), t = (int)(item - (long long)b * tiles_per_img);
+      const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
+      const int y = ty * T_ROWS + wq, x = tx * T_VALID - 1 + lane;
+      const bool valid = lane >= 1 && lane <= T_VALID && x < L.W;
+      const bool edge = x == -1 || x == L.W;                   // left / right zero border of the PP plane
+      const int q = (y + 1) * L.pitch + (x + 1);               // position relative to G
+      mbar_wait(bar_tfull + 8 * my_buf, use & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + my_buf * C::T_STRIDE;
+      float lg[8];
+      const bool head = COUT == 32 && P.ncls > 0;
+      if (head) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) lg[c] = c < P.ncls ? P.head[P.ncls * 32 + c] : 0.f;
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int c0 = ch0 + half * 16;
+        uint32_t k0[16], k1[16], k2[16];
+        TMEM_LD16(taddr + c0, k0);
+        TMEM_LD16(taddr + COUT + c0, k1);
+        TMEM_LD16(taddr + 2 * COUT + c0, k2);
+        tmem_ld_wait();
+        if (half == 1) {                                       // accumulator fully read: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_tempty + 8 * my_buf);
+        }
+        uint32_t hv[8];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const uint32_t l0 = __shfl_up_sync(0xffffffffu, k0[j], 1), l1 = __shfl_up_sync(0xffffffffu, k0[j + 1], 1);
+          const uint32_t r0 = __shfl_down_sync(0xffffffffu, k2[j], 1), r1 = __shfl_down_sync(0xffffffffu, k2[j + 1], 1);
+          const float2 bb = *reinterpret_cast<const float2*>(s_bias + c0 + j);
+          uint64_t v = add2(pack2(l0, l1), pack2(k1[j], k1[j + 1]));
+          v = add2(v, pack2(r0, r1));
+          v = add2(v, pack2(__float_as_uint(bb.x), __float_as_uint(bb.y)));
+          if (head) {
+            uint32_t lo, hi;
+            asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+            const float f0 = fminf(fmaxf(__uint_as_float(lo), 0.f), UB_ACT_MAX), f1 = fminf(fmaxf(__uint_as_float(hi), 0.f), UB_ACT_MAX);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              if (c < P.ncls) lg[c] = fmaf(P.head[c * 32 + ((c0 + j + 1) & 31)], f1, fmaf(P.head[c * 32 + ((c0 + j) & 31)], f0, lg[c]));
+          } else {
+            hv[j >> 1] = valid ? relu_pack(v) : 0u;
+          }
+        }
+        if (!head && (valid || edge)) {
+          act_t* o = P.out + (((size_t)b * NCHUNK + (c0 >> 3)) * L.Ppl + L.G + q) * 8;
+          *reinterpret_cast<uint4*>(o) = make_uint4(hv[0], hv[1], hv[2], hv[3]);
+          *reinterpret_cast<uint4*>(o + (size_t)L.Ppl * 8) = make_uint4(hv[4], hv[5], hv[6], hv[7]);
+          // top / bottom zero border rows of the plane
+          if ((ty == 0 && wq == 0) || (ty == P.tiles_y - 1 && wq == T_ROWS - 1)) {
+            act_t* z = wq == 0 ? o - (size_t)L.pitch * 8 : o + (size_t)L.pitch * 8;
+            *reinterpret_cast<uint4*>(z) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(z + (size_t)L.Ppl * 8) = make_uint4(0, 0, 0, 0);
+          }
+        }
+      }
+      if (head && valid) {
+        const size_t hw = (size_t)L.H * L.W, pix = (size_t)y * L.W + x;
+        int best = 0;
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          if (c < P.ncls) {
+            if (P.logits) P.logits[((size_t)b * P.ncls + c) * hw + pix] = lg[c];
+            if (c > 0 && lg[c] > lg[best]) best = c;
+          }
+        if (P.pred) P.pred[(size_t)b * hw + pix] = (uint8_t)best;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 16) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
+constexpr int SMEM_BUDGET = 227 * 1024;
+
+template <int COUT, int KC>
+int launch_rows(ub_ctx* ctx, RowsParams& P, cudaStream_t st, bool init_only) {
+  using C = RCfg<COUT, KC>;
+  auto kern = k_conv_rows<COUT, KC>;
+  if (init_only) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+    return UB_OK;
+  }
+  const int resident_bytes = P.kbn * C::B_STAGE;
+  int stages;
+  if (C::HDR + resident_bytes + 3 * C::A_STAGE <= SMEM_BUDGET) {
+    P.b_resident = 1;
+    stages = (SMEM_BUDGET - C::HDR - resident_bytes) / C::A_STAGE;
+  } else {
+    P.b_resident = 0;
+    stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + C::B_STAGE);
+  }
+  if (stages > 8) stages = 8;
+  if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: COUT=%d KC=%d does not fit 2 stages", COUT, KC);
+  P.num_stages = stages;
+  const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
+  kern<<<(unsigned)grid, 576, smem, st>>>(P);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, cudaStream_t st, bool init_only) {
+  if (cout == 32 && kc == 16) return launch_rows<32, 16>(ctx, P, st, init_only);
+  if (cout == 32 && kc == 32) return launch_rows<32, 32>(ctx, P, st, init_only);
+  if (cout == 64 && kc == 32) return launch_rows<64, 32>(ctx, P, st, init_only);
+  return ub_fail(ctx, UB_ERR_ARG, "conv_rows: unsupported COUT=%d KC=%d", cout, kc);
+}
+
+}  // namespace
+
+int conv_rows_init(ub_ctx* ctx) {
+  static RowsParams P{};
+  const int cfgs[3][2] = {{32, 16}, {32, 32}, {64, 32}};
+  for (auto& c : cfgs) {
+    int r = dispatch_rows(ctx, c[0], c[1], P, nullptr, true);
+    if (r != UB_OK) return r;
+  }
+  return UB_OK;
+}
+
+int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t st) {
+  if (a.H % T_ROWS) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: H=%d must be a multiple of %d", a.H, T_ROWS);
+  RowsParams P{};
+  P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
+  P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
+  P.L = pp_layout(a.H, a.W);
+  int r = tmap_pp_rows(ctx, &P.tm0, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8);
+  if (r == UB_OK) r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8)
+                              : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8);
+  if (r != UB_OK) return r;
+  P.tiles_x = cdiv(a.W, T_VALID); P.tiles_y = a.H / T_ROWS;
+  P.total_items = (long long)a.B * P.tiles_x * P.tiles_y;
+  P.ncls = 0; P.logits = a.logits; P.pred = a.pred;
+  if (a.head_w) {
+    if (Lr.cout != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == 32");
+    P.ncls = a.num_classes;
+    // head weights travel in the kernel parameters (constant bank): copy from the host mirror
+    memcpy(P.head, ctx->head_host, sizeof(float) * (size_t)a.num_classes * 33);
+  }
+  TimeScope ts(ctx, UB_T_CONV, st);
+  return dispatch_rows(ctx, Lr.cout, Lr.kc, P, st, false);
+}

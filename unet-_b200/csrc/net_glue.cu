@@ -162,7 +162,8 @@ enum { A_XIN = 0, A_T0, A_X00, A_P0, A_T1, A_X10, A_P1, A_T2, A_X20, A_P2, A_T3,
 
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st) {
   if (ctx->conv_impl == 1) return conv3x3_simt(ctx, L, a, st);
-  return L.fold ? conv3x3_fold(ctx, L, a, st) : conv3x3_tc(ctx, L, a, st);
+  if (!L.fold) return conv3x3_tc(ctx, L, a, st);
+  return (ctx->conv_impl == 3 || a.H % 4) ? conv3x3_fold(ctx, L, a, st) : conv3x3_rows(ctx, L, a, st);
 }
 
 static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
