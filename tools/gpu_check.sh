@@ -3,12 +3,12 @@
 # Usage (from repo root, under gpurun): bash tools/gpu_check.sh [tag]
 TAG=${1:-r01}
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_gpu_tests.log 2>&1
+timeout 300 python -m pytest tests -m gpu -x -q --timeout 60 > gpurun_out/${TAG}_gpu_tests.log 2>&1
 echo "pytest exit $?" >> gpurun_out/${TAG}_gpu_tests.log
 tail -5 gpurun_out/${TAG}_gpu_tests.log
-python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench_err.log
+timeout 240 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench_err.log
 echo "bench exit $?"; cat gpurun_out/${TAG}_bench.json
-python tools/profile_step.py 2 64 > gpurun_out/${TAG}_plain.log 2>&1 &&
+timeout 120 python tools/profile_step.py 2 64 > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv python tools/profile_step.py 2 64 > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu launches exit $?"

@@ -52,19 +52,15 @@ struct LayerDef { const char* block; int idx; int cin0, cin1, cout, kc, bn; int 
 // cin0 of the first layer is the 3 input channels zero-padded to 16 (one UMMA K step)
 const LayerDef kLayers[18] = {
     {"conv0_0", 1, 16, 0, 32, 16, 32, 3, 1},     {"conv0_0", 2, 32, 0, 32, 32, 32, 32, 1},
-    {"conv1_0", 1, 32, 0, 64, 32, 64, 32, 1},    {"conv1_0", 2, 64, 0, 64, 32, 64, 64, 1},
+    {"conv1_0", 1, 32, 0, 64, 32, 64, 32, 1},    {"conv1_0", 2, 64, 0, 64, 64, 64, 64, 1},
     {"conv2_0", 1, 64, 0, 128, 16, 128, 64, 0},  {"conv2_0", 2, 128, 0, 128, 16, 128, 128, 0},
     {"conv3_0", 1, 128, 0, 256, 16, 256, 128, 0}, {"conv3_0", 2, 256, 0, 256, 16, 256, 256, 0},
     {"conv4_0", 1, 256, 0, 512, 16, 256, 256, 0}, {"conv4_0", 2, 512, 0, 512, 16, 256, 512, 0},
     {"conv3_1", 1, 256, 512, 256, 16, 256, 256, 0}, {"conv3_1", 2, 256, 0, 256, 16, 256, 256, 0},
     {"conv2_2", 1, 128, 256, 128, 16, 128, 128, 0}, {"conv2_2", 2, 128, 0, 128, 16, 128, 128, 0},
-    {"conv1_3", 1, 64, 128, 64, 32, 64, 64, 1},  {"conv1_3", 2, 64, 0, 64, 32, 64, 64, 1},
+    {"conv1_3", 1, 64, 128, 64, 32, 64, 64, 1},  {"conv1_3", 2, 64, 0, 64, 64, 64, 64, 1},
     {"conv0_4", 1, 32, 64, 32, 32, 32, 32, 1},   {"conv0_4", 2, 32, 0, 32, 32, 32, 32, 1},
 };
-// activation buffers: channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu
-const int kActC[23] = {16, 32, 32, 32, 64, 64, 64, 128, 128, 128, 256, 256, 256, 512, 512, 512, 256, 256, 128, 128, 64, 64, 0};
-const int kActL[23] = {0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
-
 cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
 
 template <class T>
@@ -124,7 +120,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
   if (r) return fail(r);
-  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_fold_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
   *out = c;
@@ -152,7 +148,7 @@ void ub_destroy(ub_ctx* c) {
 
 int ub_set_conv_impl(ub_ctx* ctx, int impl) {
   NEED_CTX(ctx);
-  if (impl < 0 || impl > 3) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A, 3 tcgen05 flat kx-fold)", impl);
+  if (impl < 0 || impl > 2) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A)", impl);
   ctx->conv_impl = impl;
   return UB_OK;
 }
@@ -243,8 +239,7 @@ int ub_forward(ub_ctx* ctx, const float* x, int B, int H, int W, float* logits, 
   if (!x || !logits) return ub_fail(ctx, UB_ERR_ARG, "null tensor");
   RUN(check_net_shape(ctx, B, H, W));
   cudaStream_t st = as_stream(stream);
-  RUN(nchw_to_pp(ctx, x, B, 3, H, W, ctx->act[0], 16, st));
-  return net_forward_pp(ctx, B, H, W, logits, nullptr, st);
+  return net_forward_pp(ctx, B, H, W, x, nullptr, 0, 0, logits, nullptr, st);
 }
 
 int ub_preprocess(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, float* x_nchw, uint8_t* gray, void* stream) {
@@ -344,8 +339,8 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
   ub_burr_params p = params ? *params : default_params(variant);
   const size_t fpix = (size_t)H * W;
   uint8_t *cable = ctx->d_mask[0], *tape = ctx->d_mask[1], *burr = ctx->d_mask[2];
-  RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, ctx->act[0], nullptr, ctx->d_gray, st));
-  RUN(net_forward_pp(ctx, B, nh, nw, nullptr, ctx->d_pred, st));
+  RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, nullptr, nullptr, ctx->d_gray, st));          // gray only
+  RUN(net_forward_pp(ctx, B, nh, nw, nullptr, frames, H, W, nullptr, ctx->d_pred, st));               // preprocess fused per sub-batch
   RUN(masks_from_pred(ctx, ctx->d_pred, B, nh, nw, H, W, r, cable, tape, frame_stats, st));
   RUN(burr_stage(ctx, variant, ctx->d_gray, cable, B, H, W, p, burr, frame_stats + 3, 4, st));
   if (masks) {

@@ -59,7 +59,6 @@ struct PPLayout {
   int G;           // leading guard (positions), multiple of 8
   int npos;        // (H+2)*(W+2)
   int ntiles;      // ceil(npos / 128)
-  int ntiles_fold; // ceil(npos / 126): tiles of the kx-folded conv kernel (126 valid rows + 2 halo)
   int Ppl;         // positions per plane, multiple of 8
 };
 
@@ -69,7 +68,6 @@ static inline PPLayout pp_layout(int H, int W) {
   L.G = ((W + 3) + 7) & ~7;
   L.npos = (H + 2) * (W + 2);
   L.ntiles = (L.npos + 127) / 128;
-  L.ntiles_fold = (L.npos + 125) / 126;
   L.Ppl = ((L.G + L.npos + 400 + (W + 3)) + 7) & ~7;   // covers the over-reads of both tilings
   return L;
 }
@@ -86,7 +84,7 @@ struct ConvLayer {
   int cout;
   int kc;              // channels per k-block (16 / 32 / 64); divides cin0 and cin1
   int bn;              // N tile (<= 256); divides cout
-  int fold = 0;        // 1: kx-folded weights [kblock][ky][kc/8][kx*cout+co][8] (conv_fold.cu, cout <= 64)
+  int fold = 0;        // 1: kx-folded weights [kblock][ky][kc/8][kx*cout+co][8] (conv_rows.cu, cout <= 64)
   // weights bf16 [cout/bn][kblocks][9 taps][kc/8][bn][8], bias fp32 [cout]
   act_t* w = nullptr;
   float* bias = nullptr;
@@ -107,7 +105,7 @@ struct Timing {
 struct ub_ctx {
   int device = 0, sm_count = 148;
   int max_batch = 0, frame_h = 0, frame_w = 0, net_h = 0, net_w = 0, num_classes = 3;
-  int conv_impl = 0;                 // 0 tcgen05, 1 simt, 2 tcgen05 with aligned A segments, 3 tcgen05 with the flat kx-fold kernel
+  int conv_impl = 0;                 // 0 tcgen05, 1 simt, 2 tcgen05 with aligned A segments (flat kernel only)
   int64_t launches = 0;              // kernels launched so far
   std::string err;
   bool weights_set = false;
@@ -171,18 +169,23 @@ struct ConvArgs {
 int conv3x3_simt(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_tc_init(ub_ctx* ctx);
-int conv3x3_fold(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
-int conv_fold_init(ub_ctx* ctx);
 int conv3x3_rows(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_rows_init(ub_ctx* ctx);
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
+
+// activation buffers (ub_ctx::act): channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu
+static const int kActC[23] = {16, 32, 32, 32, 64, 64, 64, 128, 128, 128, 256, 256, 256, 512, 512, 512, 256, 256, 128, 128, 64, 64, 0};
+static const int kActL[23] = {0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
 
 // net_glue.cu
 int nchw_to_pp(ub_ctx*, const float* x, int B, int C, int H, int W, act_t* out, int Cpad, cudaStream_t);
 int pp_to_nchw(ub_ctx*, const act_t* in, int B, int C, int H, int W, float* out, cudaStream_t);
 int maxpool2_pp(ub_ctx*, const act_t* in, int B, int C, int H, int W, act_t* out, cudaStream_t);
 int upsample2_pp(ub_ctx*, const act_t* in, int B, int C, int H, int W, act_t* out, cudaStream_t);
-int net_forward_pp(ub_ctx*, int B, int H, int W, float* logits, uint8_t* pred, cudaStream_t);
+// Whole forward.  The network input comes from exactly one of: x_nchw (fp32 NCHW [B,3,H,W]) or frames (u8 BGR
+// [B,fh,fw,3], preprocess fused per sub-batch); writes logits (fp32 NCHW, nullable) and/or pred (u8, nullable).
+int net_forward_pp(ub_ctx*, int B, int H, int W, const float* x_nchw, const uint8_t* frames, int fh, int fw,
+                   float* logits, uint8_t* pred, cudaStream_t);
 
 // preprocess.cu
 int preprocess_frames(ub_ctx*, const uint8_t* frames, int B, int H, int W, int nh, int nw,

@@ -12,8 +12,9 @@
 // One work item is a 2-D tile of 4 image rows x 32 columns (M = 128: TMEM lane = r*32 + l, so
 // warp = image row, lane = column).  The column neighbours l-1 / l+1 are lanes of the same
 // warp -> two shuffles, no cross-warp exchange; columns 1..30 of a tile are valid and tiles
-// advance by 30 columns.  The six input rows y0-1..y0+4 are staged ONCE per k-block as six
-// 512-byte segments (cp.async.bulk -> UBLKCP); the A operand of tap row ky is segments
+// advance by 30 columns.  The six input rows y0-1..y0+4 of all KC/8 chunks are staged ONCE per
+// k-block by a single TMA box (cp.async.bulk.tensor -> UTMALDG; per-lane bulk copies would be
+// serialised at ~100 clk each, profiles/r01_conv.md); the A operand of tap row ky is segments
 // ky..ky+3, i.e. a +512 B descriptor offset -- half the L2->shared traffic of staging three
 // shifted copies.  Weights stay resident in shared memory when they fit.
 //
@@ -23,6 +24,7 @@
 // 32 channels each), so the MMAs of tiles i+1.. overlap the epilogue of tile i.
 // Epilogue arithmetic is packed (FADD2, F2FP.RELU.SATFINITE.PACK) -- it is the instruction-
 // bound part of these layers (profiles/r01_conv.md).
+#include <stdlib.h>
 #include <string.h>
 #include "tc_ptx.cuh"
 #include "tmap.cuh"
@@ -39,7 +41,8 @@ struct RowsParams {
   act_t* out;
   const act_t* w; const float* bias;
   int B, kb0, kbn, num_stages, b_resident;
-  int tiles_x, tiles_y;
+  int tiles_x, tiles_y;                        // tiles_y counts tile GROUPS: mt vertically adjacent 4-row M-tiles share one box
+  int mt, a_chunk, a_stage;                    // M-tiles per group; bytes of one chunk / one stage of the box ((4*mt+2) rows)
   long long total_items;
   PPLayout L;
   int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
@@ -50,8 +53,6 @@ template <int COUT, int KC>
 struct RCfg {
   static constexpr int NP = 3 * COUT;                          // folded N
   static constexpr int CPK = KC / 8;
-  static constexpr int A_CHUNK = N_SEG * SEG_BYTES;            // six segments of one chunk: 3072 B
-  static constexpr int A_STAGE = CPK * A_CHUNK;
   static constexpr int B_KY = KC * NP * 2;                     // one ky of one k-block
   static constexpr int B_STAGE = 3 * B_KY;
   static constexpr bool SPLIT = COUT == 64;                    // two warpgroups share one accumulator
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 8));
   float* s_bias = reinterpret_cast<float*>(smem + 512);        // [COUT] (<= 64 floats)
   const uint32_t a_base = smem_u32(smem) + C::HDR;
-  const uint32_t b_base = a_base + S * C::A_STAGE;
+  const uint32_t b_base = a_base + S * P.a_stage;
   const PPLayout& L = P.L;
   const int tiles_per_img = P.tiles_x * P.tiles_y;
 
@@ -120,17 +121,17 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
       tma_prefetch_desc(&P.tm0);
       tma_prefetch_desc(&P.tm1);
       int s = 0; uint32_t ph = 0; bool first = true;
-      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x) {
-        const int b = (int)(item / tiles_per_img), t = (int)(item - (long long)b * tiles_per_img);
+      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
+        const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
         const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
         const bool load_b = !P.b_resident || first;
         for (int kb = 0; kb < P.kbn; ++kb) {
           const uint32_t full = bar_full + 8 * s;
           mbar_wait(bar_empty + 8 * s, ph ^ 1);
-          mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
-          // box origin: padded row 4*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
-          if (kb < P.kb0) tma_load_5d(a_base + s * C::A_STAGE, &P.tm0, 0, tx * T_VALID, ty * T_ROWS, kb * C::CPK, b, full);
-          else tma_load_5d(a_base + s * C::A_STAGE, &P.tm1, 0, tx * T_VALID, ty * T_ROWS, (kb - P.kb0) * C::CPK, b, full);
+          mbar_expect_tx(full, P.a_stage + (load_b ? C::B_STAGE : 0));
+          // box origin: padded row 4*mt*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
+          if (kb < P.kb0) tma_load_4d(a_base + s * P.a_stage, &P.tm0, tx * T_VALID * 8, ty * T_ROWS * P.mt, kb * C::CPK, b, full);
+          else tma_load_4d(a_base + s * P.a_stage, &P.tm1, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb - P.kb0) * C::CPK, b, full);
           if (load_b)
             bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE, P.w + (size_t)kb * 3 * (size_t)(KC * C::NP), C::B_STAGE, full);
           if (++s == S) { s = 0; ph ^= 1; }
@@ -143,31 +144,36 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
     if (lane == 0) {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) |
                                  ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-      int s = 0; uint32_t ph = 0; int it = 0;
-      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
-        const int buf = it % C::NBUF, use = it / C::NBUF;
-        mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
+      int s = 0; uint32_t ph = 0; int it = 0;                    // it counts M-tiles (accumulator uses)
+      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x, it += P.mt) {
         for (int kb = 0; kb < P.kbn; ++kb) {
           mbar_wait(bar_full + 8 * s, ph);
           tc_fence_after();
-          const uint32_t a_st = a_base + s * C::A_STAGE;
+          const uint32_t a_st = a_base + s * P.a_stage;
           const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
-#pragma unroll
-          for (int ky = 0; ky < 3; ++ky) {
-#pragma unroll
-            for (int k16 = 0; k16 < KC / 16; ++k16) {
-              // A: rows 16 B apart, 8-row groups 128 B apart, the two K chunks A_CHUNK apart
-              const uint64_t ad = make_desc(a_st + 2 * k16 * C::A_CHUNK + ky * SEG_BYTES, C::A_CHUNK, 128);
-              const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
-              tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+          for (int m = 0; m < P.mt; ++m) {
+            const int buf = (it + m) % C::NBUF, use = (it + m) / C::NBUF;
+            if (kb == 0) {                                     // first touch of this accumulator: the epilogue must have drained it
+              mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
+              tc_fence_after();
             }
+            const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+              for (int k16 = 0; k16 < KC / 16; ++k16) {
+                // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
+                // the two K chunks a_chunk apart
+                const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
+                const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
+                tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+              }
+            }
+            if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);   // accumulator of M-tile m complete
           }
-          tc_commit(bar_empty + 8 * s);
+          tc_commit(bar_empty + 8 * s);                        // the box is free once every M-tile has read it
           if (++s == S) { s = 0; ph ^= 1; }
         }
-        tc_commit(bar_tfull + 8 * buf);
       }
     }
   } else {
@@ -178,11 +184,13 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
     const int ch0 = C::SPLIT ? (grp & 1) * 32 : 0;             // first of this warp's 32 channels
     constexpr int NCHUNK = COUT / 8;
     int it = 0;
-    for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+    for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x)
+    for (int m = 0; m < P.mt; ++m, ++it) {
       if (it % C::NBUF != my_buf) continue;
       const int use = it / C::NBUF;
-      const int b = (int)(item / tiles_per_img), t = (int)(item - (long long)b * tiles_per_img);
-      const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
+      const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
+      const int tgy = t / P.tiles_x, tx = t - tgy * P.tiles_x;
+      const int ty = tgy * P.mt + m;                           // 4-row M-tile index inside the image
       const int y = ty * T_ROWS + wq, x = tx * T_VALID - 1 + lane;
       const bool valid = lane >= 1 && lane <= T_VALID && x < L.W;
       const bool edge = x == -1 || x == L.W;                   // left / right zero border of the PP plane
@@ -234,7 +242,7 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
           *reinterpret_cast<uint4*>(o) = make_uint4(hv[0], hv[1], hv[2], hv[3]);
           *reinterpret_cast<uint4*>(o + (size_t)L.Ppl * 8) = make_uint4(hv[4], hv[5], hv[6], hv[7]);
           // top / bottom zero border rows of the plane
-          if ((ty == 0 && wq == 0) || (ty == P.tiles_y - 1 && wq == T_ROWS - 1)) {
+          if ((ty == 0 && wq == 0) || (ty == P.tiles_y * P.mt - 1 && wq == T_ROWS - 1)) {
             act_t* z = wq == 0 ? o - (size_t)L.pitch * 8 : o + (size_t)L.pitch * 8;
             *reinterpret_cast<uint4*>(z) = make_uint4(0, 0, 0, 0);
             *reinterpret_cast<uint4*>(z + (size_t)L.Ppl * 8) = make_uint4(0, 0, 0, 0);
@@ -266,36 +274,53 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
 constexpr int SMEM_BUDGET = 227 * 1024;
 
 template <int COUT, int KC>
-int launch_rows(ub_ctx* ctx, RowsParams& P, cudaStream_t st, bool init_only) {
+int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
   using C = RCfg<COUT, KC>;
   auto kern = k_conv_rows<COUT, KC>;
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
   }
+  // One TMA box costs ~0.42 us of the SM's TMA unit whatever its size (tools/ubench_tma.cu): make it big.
+  // mt vertically adjacent M-tiles share one box of 4*mt+2 rows.  With several k-blocks all mt accumulators are live
+  // at once, so mt = NBUF gives up the TMEM double buffering across groups -- measured faster anyway (UB_ROWS_MT sweep,
+  // profiles/r01_conv.md).
   const int resident_bytes = P.kbn * C::B_STAGE;
-  int stages;
-  if (C::HDR + resident_bytes + 3 * C::A_STAGE <= SMEM_BUDGET) {
-    P.b_resident = 1;
-    stages = (SMEM_BUDGET - C::HDR - resident_bytes) / C::A_STAGE;
-  } else {
-    P.b_resident = 0;
-    stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + C::B_STAGE);
+  static const int mt_env = getenv("UB_ROWS_MT") ? atoi(getenv("UB_ROWS_MT")) : 4;
+  const int mt_max = mt_env < 1 ? 1 : (mt_env < C::NBUF ? mt_env : C::NBUF);
+  int mt = 1, stages = 0;
+  for (int cand = mt_max; cand >= 1; cand >>= 1) {
+    if (a.H % (T_ROWS * cand)) continue;
+    const int a_stage = C::CPK * (T_ROWS * cand + 2) * SEG_BYTES;
+    int st_n;
+    if (C::HDR + resident_bytes + 2 * a_stage <= SMEM_BUDGET) { P.b_resident = 1; st_n = (SMEM_BUDGET - C::HDR - resident_bytes) / a_stage; }
+    else { P.b_resident = 0; st_n = (SMEM_BUDGET - C::HDR) / (a_stage + C::B_STAGE); }
+    if (st_n >= 2 || cand == 1) { mt = cand; stages = st_n; break; }
   }
   if (stages > 8) stages = 8;
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: COUT=%d KC=%d does not fit 2 stages", COUT, KC);
   P.num_stages = stages;
-  const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  P.mt = mt;
+  P.a_chunk = (T_ROWS * mt + 2) * SEG_BYTES;
+  P.a_stage = C::CPK * P.a_chunk;
+  P.tiles_y = a.H / (T_ROWS * mt);
+  P.total_items = (long long)a.B * P.tiles_x * P.tiles_y;
+  int r = tmap_pp_rows(ctx, &P.tm0, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
+  if (r == UB_OK) r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK)
+                              : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
+  if (r != UB_OK) return r;
+  const int smem = C::HDR + stages * P.a_stage + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
   kern<<<(unsigned)grid, 576, smem, st>>>(P);
   UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
 
-int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, cudaStream_t st, bool init_only) {
-  if (cout == 32 && kc == 16) return launch_rows<32, 16>(ctx, P, st, init_only);
-  if (cout == 32 && kc == 32) return launch_rows<32, 32>(ctx, P, st, init_only);
-  if (cout == 64 && kc == 32) return launch_rows<64, 32>(ctx, P, st, init_only);
+int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
+  if (cout == 32 && kc == 16) return launch_rows<32, 16>(ctx, P, a, Lr, st, init_only);
+  if (cout == 32 && kc == 32) return launch_rows<32, 32>(ctx, P, a, Lr, st, init_only);
+  if (cout == 64 && kc == 32) return launch_rows<64, 32>(ctx, P, a, Lr, st, init_only);
+  if (cout == 64 && kc == 64) return launch_rows<64, 64>(ctx, P, a, Lr, st, init_only);
   return ub_fail(ctx, UB_ERR_ARG, "conv_rows: unsupported COUT=%d KC=%d", cout, kc);
 }
 
@@ -303,9 +328,10 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, cudaStream_t st,
 
 int conv_rows_init(ub_ctx* ctx) {
   static RowsParams P{};
-  const int cfgs[3][2] = {{32, 16}, {32, 32}, {64, 32}};
+  const int cfgs[4][2] = {{32, 16}, {32, 32}, {64, 32}, {64, 64}};
+  ConvArgs a{}; ConvLayer Lr{};
   for (auto& c : cfgs) {
-    int r = dispatch_rows(ctx, c[0], c[1], P, nullptr, true);
+    int r = dispatch_rows(ctx, c[0], c[1], P, a, Lr, nullptr, true);
     if (r != UB_OK) return r;
   }
   return UB_OK;
@@ -317,12 +343,7 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
   P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
   P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
   P.L = pp_layout(a.H, a.W);
-  int r = tmap_pp_rows(ctx, &P.tm0, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8);
-  if (r == UB_OK) r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8)
-                              : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, N_SEG, Lr.kc / 8);
-  if (r != UB_OK) return r;
-  P.tiles_x = cdiv(a.W, T_VALID); P.tiles_y = a.H / T_ROWS;
-  P.total_items = (long long)a.B * P.tiles_x * P.tiles_y;
+  P.tiles_x = cdiv(a.W, T_VALID);
   P.ncls = 0; P.logits = a.logits; P.pred = a.pred;
   if (a.head_w) {
     if (Lr.cout != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == 32");
@@ -331,5 +352,5 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
     memcpy(P.head, ctx->head_host, sizeof(float) * (size_t)a.num_classes * 33);
   }
   TimeScope ts(ctx, UB_T_CONV, st);
-  return dispatch_rows(ctx, Lr.cout, Lr.kc, P, st, false);
+  return dispatch_rows(ctx, Lr.cout, Lr.kc, P, a, Lr, st, false);
 }

@@ -19,7 +19,6 @@
 // Persistent CTAs, one per SM; TMEM accumulators double-buffered so the epilogue of item i
 // overlaps the MMAs of item i+1.
 #include "tc_ptx.cuh"
-#include "tmap.cuh"
 
 namespace {
 using namespace tcp;
@@ -29,11 +28,9 @@ constexpr int SEG_BYTES = SEG_POS * 16;      // 2176
 constexpr int TILE_M = 128;
 
 struct TcParams {
-  alignas(64) CUtensorMap tm0;                 // tmap_pp_flat views of source 0 / source 1:
-  alignas(64) CUtensorMap tm1;                 // box = one staged segment (136 or 128 positions) x KC/8 chunks
-  act_t* out;
+  const act_t* src0; const act_t* src1; act_t* out;
   const act_t* w; const float* bias;
-  int B, kb0, kbn, cout, n_ntiles, num_stages, b_resident;
+  int B, kb0, kbn, nch0, nch1, cout, n_ntiles, num_stages, b_resident;
   long long total_items;
   PPLayout L;
   const float* head_w; const float* head_b; int ncls; float* logits; uint8_t* pred;
@@ -88,10 +85,10 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 4) {
-    // ===================== producer: TMA boxes (activations) + one bulk copy (weights) per k-block =====================
+    // ===================== producer: contiguous bulk copies, issued by ONE lane =====================
+    // (UBLKCP takes uniform operands: per-lane addresses would be serialised by a divergent loop that
+    //  costs ~100 cycles per copy -- profiles/r01_conv.md)
     if (lane == 0) {
-      tma_prefetch_desc(&P.tm0);
-      tma_prefetch_desc(&P.tm1);
       int s = 0; uint32_t ph = 0; bool first = true;
       for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x) {
         const int nt = (int)(item % P.n_ntiles);
@@ -103,13 +100,16 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
           const uint32_t full = bar_full + 8 * s;
           mbar_wait(bar_empty + 8 * s, ph ^ 1);
           mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
-          const void* tm = kb < P.kb0 ? &P.tm0 : &P.tm1;
-          const int chunk0 = (kb < P.kb0 ? kb : kb - P.kb0) * C::CPK;
+          const act_t* plane0 =
+              kb < P.kb0 ? P.src0 + ((size_t)b * P.nch0 + (size_t)kb * C::CPK) * L.Ppl * 8
+                         : P.src1 + ((size_t)b * P.nch1 + (size_t)(kb - P.kb0) * C::CPK) * L.Ppl * 8;
           const uint32_t a_st = a_base + s * C::A_STAGE;
 #pragma unroll
           for (int seg = 0; seg < C::A_SEGS; ++seg) {
             const int off = SHIFT_A ? (seg - 1) * L.pitch - 1 : (seg / 3 - 1) * L.pitch + (seg % 3 - 1);
-            tma_load_4d(a_st + seg * C::CPK * C::A_SEG_BYTES, tm, 0, p0 + off, chunk0, b, full);
+#pragma unroll
+            for (int cc = 0; cc < C::CPK; ++cc)
+              bulk_g2s(a_st + (seg * C::CPK + cc) * C::A_SEG_BYTES, plane0 + ((size_t)cc * L.Ppl + p0 + off) * 8, C::A_SEG_BYTES, full);
           }
           if (load_b)
             bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE,
@@ -278,14 +278,10 @@ int conv_tc_init(ub_ctx* ctx) {
 
 int conv3x3_tc(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t st) {
   TcParams P{};
-  P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
+  P.src0 = a.src0; P.src1 = a.src1; P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
   P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
-  P.cout = Lr.cout; P.n_ntiles = Lr.cout / Lr.bn;
+  P.nch0 = Lr.cin0 / 8; P.nch1 = Lr.cin1 / 8; P.cout = Lr.cout; P.n_ntiles = Lr.cout / Lr.bn;
   P.L = pp_layout(a.H, a.W);
-  const int box_pos = ctx->conv_impl == 2 ? TILE_M : SEG_POS;
-  int rc = tmap_pp_flat(ctx, &P.tm0, a.src0, a.B, Lr.cin0 / 8, P.L, box_pos, Lr.kc / 8);
-  if (rc == UB_OK) rc = tmap_pp_flat(ctx, &P.tm1, Lr.cin1 ? a.src1 : a.src0, a.B, (Lr.cin1 ? Lr.cin1 : Lr.cin0) / 8, P.L, box_pos, Lr.kc / 8);
-  if (rc != UB_OK) return rc;
   P.total_items = (long long)a.B * P.L.ntiles * P.n_ntiles;
   P.head_w = a.head_w; P.head_b = a.head_b; P.ncls = a.num_classes; P.logits = a.logits; P.pred = a.pred;
   if (a.head_w && (Lr.cout != 32 || Lr.bn != 32)) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == bn == 32");

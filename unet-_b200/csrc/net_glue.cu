@@ -1,5 +1,6 @@
 // net_glue.cu -- layout conversion, 2x2 max-pool, bilinear x2 upsample in the PP layout,
 // and the layer schedule of NestedUNet.forward (src/models/unetpp.py:93-135).
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -163,7 +164,7 @@ enum { A_XIN = 0, A_T0, A_X00, A_P0, A_T1, A_X10, A_P1, A_T2, A_X20, A_P2, A_T3,
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st) {
   if (ctx->conv_impl == 1) return conv3x3_simt(ctx, L, a, st);
   if (!L.fold) return conv3x3_tc(ctx, L, a, st);
-  return (ctx->conv_impl == 3 || a.H % 4) ? conv3x3_fold(ctx, L, a, st) : conv3x3_rows(ctx, L, a, st);
+  return conv3x3_rows(ctx, L, a, st);
 }
 
 static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
@@ -180,10 +181,15 @@ static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
 
 #define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
 
-// Input already in act[A_XIN] (PP, 16 channels).  Writes logits (fp32 NCHW) and/or pred.
-int net_forward_pp(ub_ctx* ctx, int B, int H, int W, float* logits, uint8_t* pred, cudaStream_t st) {
+// The network input comes from exactly one of x_nchw / frames; with frames the preprocess kernel writes the PP input.
+int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const uint8_t* frames, int fh, int fw,
+                   float* logits, uint8_t* pred, cudaStream_t st) {
   act_t** A = ctx->act;
-  int h1 = H / 2, w1 = W / 2, h2 = H / 4, w2 = W / 4, h3 = H / 8, w3 = W / 8, h4 = H / 16, w4 = W / 16;
+  const int h1 = H / 2, w1 = W / 2, h2 = H / 4, w2 = W / 4, h3 = H / 8, w3 = W / 8, h4 = H / 16, w4 = W / 16;
+  // (Running the high-resolution levels a few frames at a time so that their intermediates stay inside the 126 MB
+  //  L2 was tried and is slower: the small launches cost more than the residency gains, profiles/r01_conv.md.)
+  if (frames) RUN(preprocess_frames(ctx, frames, B, fh, fw, H, W, A[A_XIN], nullptr, nullptr, st));
+  else RUN(nchw_to_pp(ctx, x_nchw, B, 3, H, W, A[A_XIN], 16, st));
   // encoder (unetpp.py:104-108)
   RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));
   RUN(run_conv(ctx, 1, A[A_T0], nullptr, A[A_X00], B, H, W, st));
@@ -199,8 +205,8 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, float* logits, uint8_t* pre
   RUN(maxpool2_pp(ctx, A[A_X30], B, 256, h3, w3, A[A_P3], st));
   RUN(run_conv(ctx, 8, A[A_P3], nullptr, A[A_T4], B, h4, w4, st));
   RUN(run_conv(ctx, 9, A[A_T4], nullptr, A[A_X40], B, h4, w4, st));
-  // decoder (unetpp.py:111-116): cat([skip, up(below)]) is never materialised -- the
-  // conv reads its K range from two sources.
+  // decoder (unetpp.py:111-116): cat([skip, up(below)]) is never materialised -- the conv reads its K range from
+  // two sources
   RUN(upsample2_pp(ctx, A[A_X40], B, 512, h4, w4, A[A_UP4], st));
   RUN(run_conv(ctx, 10, A[A_X30], A[A_UP4], A[A_T3], B, h3, w3, st));
   RUN(run_conv(ctx, 11, A[A_T3], nullptr, A[A_X31], B, h3, w3, st));

@@ -39,10 +39,12 @@ int tmap_make(ub_ctx* ctx, CUtensorMap* out, const void* base, int rank, const u
 
 int tmap_pp_rows(ub_ctx* ctx, CUtensorMap* out, const act_t* base, int B, int nchunks, const PPLayout& L,
                  int box_cols, int box_rows, int box_chunks) {
-  const uint64_t dims[5] = {8, (uint64_t)L.pitch, (uint64_t)L.H + 2, (uint64_t)nchunks, (uint64_t)B};
-  const uint64_t strides[4] = {16, (uint64_t)L.pitch * 16, (uint64_t)L.Ppl * 16, (uint64_t)nchunks * L.Ppl * 16};
-  const uint32_t box[5] = {8, (uint32_t)box_cols, (uint32_t)box_rows, (uint32_t)box_chunks, 1};
-  return tmap_make(ctx, out, base + (size_t)L.G * 8, 5, dims, strides, box);
+  // the 8 channels of a position and the positions of a row are contiguous: one inner dimension of pitch*8
+  // elements, so a box row is a single box_cols*16-byte run (a 16-byte inner box would be one request per position)
+  const uint64_t dims[4] = {(uint64_t)L.pitch * 8, (uint64_t)L.H + 2, (uint64_t)nchunks, (uint64_t)B};
+  const uint64_t strides[3] = {(uint64_t)L.pitch * 16, (uint64_t)L.Ppl * 16, (uint64_t)nchunks * L.Ppl * 16};
+  const uint32_t box[4] = {(uint32_t)box_cols * 8, (uint32_t)box_rows, (uint32_t)box_chunks, 1};
+  return tmap_make(ctx, out, base + (size_t)L.G * 8, 4, dims, strides, box);
 }
 
 int tmap_pp_flat(ub_ctx* ctx, CUtensorMap* out, const act_t* base, int B, int nchunks, const PPLayout& L,
