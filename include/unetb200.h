@@ -56,7 +56,10 @@ typedef struct ub_burr_params {
 } ub_burr_params;
 
 enum { UB_VARIANT_STANDARD = 0,   /* detect_burrs_on_cable, infer_two_stage_burr.py:50-119 */
-       UB_VARIANT_ENHANCED = 1 }; /* detect_burrs_enhanced, infer_enhanced_burr.py:69-138  */
+       UB_VARIANT_ENHANCED = 1,   /* detect_burrs_enhanced, infer_enhanced_burr.py:69-138  */
+       /* OR-ed into `variant` of ub_pipeline / ub_pipeline_host: run enhance_image on every frame
+        * before the net and the gray conversion (--enhance, infer_enhanced_burr.py:279-280) */
+       UB_FLAG_ENHANCE_IMAGE = 0x100 };
 
 /* ---- lifetime ------------------------------------------------------------------- */
 /* Allocates all scratch for batches of up to max_batch frames of frame_h x frame_w and
@@ -125,6 +128,24 @@ int ub_burr(ub_ctx* ctx, int variant, const uint8_t* gray_dev, const uint8_t* ma
             int B, int H, int W, const ub_burr_params* params, uint8_t* burr_mask_dev,
             int32_t* burr_px_dev, void* stream);
 
+/* ---- enhance_image (infer_enhanced_burr.py:38-66; --enhance only) -------------------- */
+/* The individual cv2 calls, bit-exact for uint8.  Images are u8 [B,H,W,3] on the device.
+ * code: 0 COLOR_BGR2LAB (:46), 1 COLOR_LBGR2Lab, 2 COLOR_LAB2BGR (:55), 3 COLOR_Lab2LBGR
+ * (1 and 3 are what fastNlMeansDenoisingColored uses internally).  src may equal dst. */
+int ub_cvt_lab(ub_ctx* ctx, int code, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);
+/* cv2.createCLAHE(clip_limit, (tiles_x,tiles_y)).apply on a single-channel u8 [B,H,W] (:50-51);
+ * W % tiles_x == 0, H % tiles_y == 0, tiles_x*tiles_y <= 64 (800x448 with 8x8 qualifies; OpenCV
+ * pads other sizes, this entry point rejects them).  src may equal dst. */
+int ub_clahe(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, double clip_limit, int tiles_x, int tiles_y,
+             uint8_t* dst_dev, void* stream);
+/* cv2.fastNlMeansDenoising(src, None, 10, 7, 21) on u8 [B,H,W,cn], cn = 1 or 2; H,W >= 14. */
+int ub_nlm(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int cn, uint8_t* dst_dev, void* stream);
+/* cv2.filter2D(src, -1, [[-1,-1,-1],[-1,9,-1],[-1,-1,-1]]) on u8 [B,H,W,3] (:61-64). */
+int ub_sharpen3(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);
+/* Whole enhance_image for a batch: frames u8 BGR [B,H,W,3] -> u8 BGR [B,H,W,3]
+ * (BGR2LAB, CLAHE(3.0, 8x8) on L, LAB2BGR, fastNlMeansDenoisingColored(10,10,7,21), sharpen). */
+int ub_enhance(ub_ctx* ctx, const uint8_t* frames_bgr_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);
+
 /* ---- the whole per-frame step (body of the loop, infer_two_stage_burr.py:286-343) -- */
 /* frames u8 BGR [B,frame_h,frame_w,3] -> frame_stats i32 [B,4] = (index in batch,
  * cable_px, tape_px, burr_px); masks (nullable) u8 [B,3,frame_h,frame_w] = cable, tape,
@@ -151,8 +172,8 @@ int ub_debug_activation(ub_ctx* ctx, int index, int B, int C, int H, int W, floa
 /* ---- instrumentation -------------------------------------------------------------- */
 /* When enabled, every kernel class is bracketed by CUDA events on the launch stream;
  * ub_timing_read sums them (synchronises).  classes: 0 conv3x3, 1 net glue (pool,
- * upsample, layout), 2 pre/post, 3 stage-2 stencil/morphology, 4 CCL/hysteresis. */
-enum { UB_T_CONV = 0, UB_T_GLUE = 1, UB_T_PREPOST = 2, UB_T_STENCIL = 3, UB_T_CCL = 4, UB_T_NCLASS = 5 };
+ * upsample, layout), 2 pre/post, 3 stage-2 stencil/morphology, 4 CCL/hysteresis, 5 enhance_image. */
+enum { UB_T_CONV = 0, UB_T_GLUE = 1, UB_T_PREPOST = 2, UB_T_STENCIL = 3, UB_T_CCL = 4, UB_T_ENHANCE = 5, UB_T_NCLASS = 6 };
 int ub_timing_enable(ub_ctx* ctx, int on);
 int ub_timing_read(ub_ctx* ctx, float* ms_per_class, int64_t* scopes_per_class, int reset);
 /* Number of kernels this context has launched so far. */

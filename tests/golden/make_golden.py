@@ -119,8 +119,43 @@ def net():
     np.savez_compressed(os.path.join(HERE, "net.npz"), **out)
 
 
+def colour_cube(b_values=None):
+    """All 2^24 (or the given blue planes of) uint8 triples as [n*256, 256, 3] images."""
+    g, r = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), indexing="ij")
+    bs = range(256) if b_values is None else b_values
+    return np.concatenate([np.stack([np.full_like(g, b), g, r], -1) for b in bs], 0)
+
+
+def enhance():
+    """enhance_image (infer_enhanced_burr.py:38-66) of the real reference + the cv2 calls inside it."""
+    import zlib
+    out = {"versions": VERS}
+    cube = colour_cube()
+    for name, code in (("bgr2lab", cv2.COLOR_BGR2LAB), ("lbgr2lab", cv2.COLOR_LBGR2Lab),
+                       ("lab2bgr", cv2.COLOR_LAB2BGR), ("lab2lbgr", cv2.COLOR_Lab2LBGR)):
+        out[f"cube_crc_{name}"] = np.array(zlib.crc32(cv2.cvtColor(cube, code).tobytes()), np.uint32)
+    for tag, fr in (("cable", S.frames_cable(1, 64, 96, seed=2)[0]), ("noise", S.frames_noise(1, 72, 104, seed=3)[0]),
+                    ("speckle", S.frames_speckle(1, 48, 56, seed=4, n_blobs=12)[0])):
+        out[f"{tag}_in"] = fr
+        out[f"{tag}_out"] = E.enhance_image(fr)
+        lab = cv2.cvtColor(fr, cv2.COLOR_BGR2LAB)
+        out[f"{tag}_nlm1"] = cv2.fastNlMeansDenoising(np.ascontiguousarray(lab[..., 0]), None, 10, 7, 21)
+        out[f"{tag}_nlm2"] = cv2.fastNlMeansDenoising(np.ascontiguousarray(lab[..., 1:]), None, 10, 7, 21)
+    full = S.frames_cable(1, 448, 800, seed=0)[0]
+    out["full_in_crc"] = np.array(zlib.crc32(full.tobytes()), np.uint32)
+    eo = E.enhance_image(full)
+    out["full_out_crc"] = np.array(zlib.crc32(eo.tobytes()), np.uint32)
+    out["full_out_crop"] = eo[192:256, 368:432].copy()
+    np.savez_compressed(os.path.join(HERE, "enhance.npz"), **out)
+
+
 if __name__ == "__main__":
-    stage2()
-    net()
-    for f in ("stage2.npz", "net.npz"):
+    which = sys.argv[1:] or ["stage2", "net", "enhance"]
+    if "stage2" in which:
+        stage2()
+    if "net" in which:
+        net()
+    if "enhance" in which:
+        enhance()
+    for f in ("stage2.npz", "net.npz", "enhance.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)))

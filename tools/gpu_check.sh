@@ -3,7 +3,7 @@
 # Usage (from repo root, under gpurun): bash tools/gpu_check.sh [tag]
 TAG=${1:-r01}
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests -m gpu -x -q --timeout 60 > gpurun_out/${TAG}_gpu_tests.log 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q --timeout 120 > gpurun_out/${TAG}_gpu_tests.log 2>&1
 echo "pytest exit $?" >> gpurun_out/${TAG}_gpu_tests.log
 tail -5 gpurun_out/${TAG}_gpu_tests.log
 timeout 240 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench_err.log

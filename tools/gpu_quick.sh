@@ -2,7 +2,7 @@
 # Quick GPU visit: parity tests + bench + launch list (no full ncu capture).
 TAG=${1:-q}
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests -m gpu -x -q --timeout 60 > gpurun_out/${TAG}_gpu_tests.log 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q --timeout 120 > gpurun_out/${TAG}_gpu_tests.log 2>&1
 echo "pytest exit $?" >> gpurun_out/${TAG}_gpu_tests.log
 tail -15 gpurun_out/${TAG}_gpu_tests.log
 timeout 240 python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench_err.log

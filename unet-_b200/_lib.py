@@ -18,7 +18,9 @@ LIB_PATH = os.path.join(_HERE, "libunetb200.so")
 _lib = None
 
 VARIANT_STANDARD, VARIANT_ENHANCED = 0, 1
-T_CLASSES = ("conv3x3", "net_glue", "prepost", "stencil_morph", "ccl")
+FLAG_ENHANCE_IMAGE = 0x100
+CVT_BGR2LAB, CVT_LBGR2LAB, CVT_LAB2BGR, CVT_LAB2LBGR = 0, 1, 2, 3
+T_CLASSES = ("conv3x3", "net_glue", "prepost", "stencil_morph", "ccl", "enhance")
 
 
 class UbError(RuntimeError):
@@ -59,6 +61,11 @@ SIGNATURES = {
     "ub_sobel_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "ub_laplacian_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "ub_burr": (_I, [_P, _I, _P, _P, _I, _I, _I, C.POINTER(BurrParams), _P, _P, _P]),
+    "ub_cvt_lab": (_I, [_P, _I, _P, _I, _I, _I, _P, _P]),
+    "ub_clahe": (_I, [_P, _P, _I, _I, _I, C.c_double, _I, _I, _P, _P]),
+    "ub_nlm": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_sharpen3": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "ub_enhance": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_pipeline": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P, _P]),
     "ub_pipeline_host": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P]),
     "ub_debug_conv": (_I, [_P, _I, _P, _P, _I, _I, _I, _P, _P]),
@@ -253,6 +260,41 @@ class Context:
                                   C.byref(p), out.data_ptr(), px.data_ptr(), self.stream))
         return out, px
 
+    # -- enhance_image pieces (u8 [B,H,W,3] unless noted)
+    def cvt_lab(self, src, code):
+        b, h, w, _ = src.shape
+        dst = torch.empty_like(src)
+        self._check(lib().ub_cvt_lab(self._h, code, self._dev(src, torch.uint8), b, h, w, dst.data_ptr(), self.stream))
+        return dst
+
+    def clahe(self, src, clip_limit=3.0, tiles=(8, 8)):
+        """src u8 [B,H,W]"""
+        b, h, w = src.shape
+        dst = torch.empty_like(src)
+        self._check(lib().ub_clahe(self._h, self._dev(src, torch.uint8), b, h, w, float(clip_limit), tiles[0], tiles[1],
+                                   dst.data_ptr(), self.stream))
+        return dst
+
+    def nlm(self, src):
+        """src u8 [B,H,W] or [B,H,W,2]; fastNlMeansDenoising(h=10, 7, 21)"""
+        b, h, w = src.shape[:3]
+        cn = 1 if src.dim() == 3 else src.shape[3]
+        dst = torch.empty_like(src)
+        self._check(lib().ub_nlm(self._h, self._dev(src, torch.uint8), b, h, w, cn, dst.data_ptr(), self.stream))
+        return dst
+
+    def sharpen3(self, src):
+        b, h, w, _ = src.shape
+        dst = torch.empty_like(src)
+        self._check(lib().ub_sharpen3(self._h, self._dev(src, torch.uint8), b, h, w, dst.data_ptr(), self.stream))
+        return dst
+
+    def enhance(self, frames):
+        b, h, w, _ = frames.shape
+        dst = torch.empty_like(frames)
+        self._check(lib().ub_enhance(self._h, self._dev(frames, torch.uint8), b, h, w, dst.data_ptr(), self.stream))
+        return dst
+
     # -- whole step
     def pipeline(self, frames: torch.Tensor, variant=VARIANT_STANDARD, roi=None, params=None, want_masks=False):
         b = frames.shape[0]
@@ -292,8 +334,8 @@ class Context:
         self._check(lib().ub_timing_enable(self._h, int(on)))
 
     def timing_read(self, reset=True):
-        ms = (C.c_float * 5)()
-        n = (C.c_int64 * 5)()
+        ms = (C.c_float * len(T_CLASSES))()
+        n = (C.c_int64 * len(T_CLASSES))()
         self._check(lib().ub_timing_read(self._h, ms, n, int(reset)))
         return {k: (ms[i], n[i]) for i, k in enumerate(T_CLASSES)}
 

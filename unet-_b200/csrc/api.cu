@@ -120,7 +120,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
   if (r) return fail(r);
-  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK || (r = enhance_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
   *out = c;
@@ -140,6 +140,7 @@ void ub_destroy(ub_ctx* c) {
   for (auto& p : c->d_lab) cudaFree(p);
   cudaFree(c->d_comp); cudaFree(c->d_counts); cudaFree(c->d_stats); cudaFree(c->d_logits);
   resize_cache_free(c);
+  enhance_free(c);
   for (auto& r : c->tm.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (auto& e : c->tm.pool) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -325,6 +326,47 @@ int ub_burr(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, 
   return burr_stage(ctx, variant, gray, mask, B, H, W, p, burr, burr_px, 1, st);
 }
 
+static int check_enh_shape(ub_ctx* ctx, int B, int H, int W) {
+  RUN(check_frame_shape(ctx, B, H, W));
+  if (H < 14 || W < 14) return ub_fail(ctx, UB_ERR_ARG, "image %dx%d smaller than the 13-pixel NLM border", H, W);
+  return UB_OK;
+}
+
+int ub_cvt_lab(ub_ctx* ctx, int code, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  if (!src || !dst) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return cvt_lab(ctx, code, src, dst, B, H, W, as_stream(stream));
+}
+
+int ub_clahe(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, double clip_limit, int tiles_x, int tiles_y, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  if (!src || !dst) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return clahe(ctx, src, dst, B, H, W, 1, 0, clip_limit, tiles_x, tiles_y, as_stream(stream));
+}
+
+int ub_nlm(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int cn, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  if (!src || !dst) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_enh_shape(ctx, B, H, W));
+  return nlm(ctx, src, dst, B, H, W, cn, 0, cn, as_stream(stream));
+}
+
+int ub_sharpen3(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  if (!src || !dst) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return sharpen3(ctx, src, dst, B, H, W, as_stream(stream));
+}
+
+int ub_enhance(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || !dst) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_enh_shape(ctx, B, H, W));
+  return enhance_frames(ctx, frames, dst, B, H, W, as_stream(stream));
+}
+
 int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub_roi* roi, const ub_burr_params* params,
                 int32_t* frame_stats, uint8_t* masks, void* stream) {
   NEED_CTX(ctx);
@@ -332,6 +374,17 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
   const int H = ctx->frame_h, W = ctx->frame_w, nh = ctx->net_h, nw = ctx->net_w;
   RUN(check_net_shape(ctx, B, nh, nw));
   cudaStream_t st = as_stream(stream);
+  const bool do_enhance = (variant & UB_FLAG_ENHANCE_IMAGE) != 0;
+  variant &= ~UB_FLAG_ENHANCE_IMAGE;
+  if (variant != UB_VARIANT_STANDARD && variant != UB_VARIANT_ENHANCED) return ub_fail(ctx, UB_ERR_ARG, "variant %d", variant);
+  if (do_enhance) {
+    // the enhanced frames feed BOTH the net and the gray conversion (infer_enhanced_burr.py:279-280);
+    // they live in the CCL scratch, which stage 2 only touches after the net has consumed them
+    uint8_t* enh = reinterpret_cast<uint8_t*>(ctx->d_comp) + (size_t)ctx->max_batch * H * W * 4;
+    RUN(check_enh_shape(ctx, B, H, W));
+    RUN(enhance_frames(ctx, frames, enh, B, H, W, st));
+    frames = enh;
+  }
   ub_roi r;
   if (roi) r = *roi;
   else if (variant == UB_VARIANT_ENHANCED) r = {200, 0, 600, 448};                     // VERTICAL_ROI, infer_enhanced_burr.py:23-28

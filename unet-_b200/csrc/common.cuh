@@ -128,6 +128,8 @@ struct ub_ctx {
   float* d_logits = nullptr;         // [B,C,nh,nw] fp32 (module path / debug)
   int* d_rs_tab = nullptr;           // resize coefficient tables
   void* cache = nullptr;             // host-side cache of resize tables (ResizeCache*)
+  void* enh_host = nullptr;          // enhance.cu lookup tables (EnhTables*), host copy
+  void* d_enh = nullptr;             // ... and device copy
   cudaStream_t own_stream = nullptr;
   Timing tm;
 };
@@ -193,6 +195,16 @@ int preprocess_frames(ub_ctx*, const uint8_t* frames, int B, int H, int W, int n
 int masks_from_pred(ub_ctx*, const uint8_t* pred, int B, int nh, int nw, int H, int W, ub_roi roi,
                     uint8_t* cable, uint8_t* tape, int32_t* stats, cudaStream_t);
 int argmax_logits(ub_ctx*, const float* logits, int B, int C, int nh, int nw, uint8_t* pred, cudaStream_t);
+
+// enhance.cu (enhance_image: Lab conversions, CLAHE, non-local means, sharpen); images u8 interleaved
+int enhance_init(ub_ctx*);
+void enhance_free(ub_ctx*);
+int cvt_lab(ub_ctx*, int code, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t);
+int clahe(ub_ctx*, const uint8_t* src, uint8_t* dst, int B, int H, int W, int pstride, int ch, double clip_limit,
+          int tiles_x, int tiles_y, cudaStream_t);
+int nlm(ub_ctx*, const uint8_t* src, uint8_t* dst, int B, int H, int W, int pstride, int ch, int cn, cudaStream_t);
+int sharpen3(ub_ctx*, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t);
+int enhance_frames(ub_ctx*, const uint8_t* frames, uint8_t* out, int B, int H, int W, cudaStream_t);
 
 // stage2.cu
 int burr_stage(ub_ctx*, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,

@@ -5,6 +5,7 @@ Same names, argument meaning and results as the reference functions:
   preprocess_image        infer_two_stage_burr.py:122-127
   detect_burrs_on_cable   infer_two_stage_burr.py:50-119
   detect_burrs_enhanced   infer_enhanced_burr.py:69-138
+  enhance_image           infer_enhanced_burr.py:38-66
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
@@ -122,5 +123,12 @@ def detect_burrs_enhanced(frame_gray, mask_cable, config):
 
 
 def enhance_image(frame):
-    raise NotImplementedError("enhance_image (CLAHE + NLM + sharpen, infer_enhanced_burr.py:38-66) is not built yet "
-                              "(SURVEY section 8 row a10); there is no CPU fallback")
+    """enhance_image (infer_enhanced_burr.py:38-66): BGR2LAB, CLAHE(3.0, 8x8) on L, LAB2BGR,
+    fastNlMeansDenoisingColored(10, 10, 7, 21), 3x3 sharpen -- bit-exact with cv2 on uint8.
+    frame: u8 BGR [H,W,3] (numpy -> numpy) or a CUDA tensor [H,W,3] / [B,H,W,3] (stays on the GPU).
+    W and H must be multiples of 8 (the reference only ever passes 800x448 frames)."""
+    f, was_np, single = _batched(frame, 3)
+    c = _ctx(f.device, f.shape[0], tuple(f.shape[1:3]))
+    with torch.cuda.device(f.device):
+        out = c.enhance(f)
+    return _unbatch(out, was_np, single)

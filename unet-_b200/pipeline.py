@@ -34,7 +34,7 @@ def stats_line(idx, frame_no, total, cable_px, tape_px, burr_px, roi):
 
 class InspectionPipeline:
     def __init__(self, state_dict, batch: int, frame_hw=(448, 800), net_hw=(512, 512), variant="standard",
-                 sensitivity="medium", device=None, roi=None, num_classes=3):
+                 sensitivity="medium", device=None, roi=None, num_classes=3, enhance=False):
         if device is None:
             device = torch.cuda.current_device()
         self.ctx = _lib.Context(device, max_batch=batch, frame_hw=frame_hw, net_hw=net_hw, num_classes=num_classes)
@@ -50,6 +50,8 @@ class InspectionPipeline:
             cfg = BURR_CONFIGS[sensitivity]
             self.params = _lib.standard_params(cfg["min_area"], cfg["max_area"])
             self.roi = roi or map_roi_to_original((frame_hw[1], frame_hw[0]), (512, 512))
+        if enhance:       # --enhance of infer_enhanced_burr.py:201,279-280: enhance_image before the net and the gray conversion
+            self.variant |= _lib.FLAG_ENHANCE_IMAGE
 
     def run(self, frames: torch.Tensor, want_masks=False):
         """frames: CUDA uint8 [B,H,W,3] BGR -> (stats int32 [B,4] on device, masks or None).
