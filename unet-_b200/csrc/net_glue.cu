@@ -78,38 +78,73 @@ __global__ void k_maxpool2(const act_t* __restrict__ in, act_t* __restrict__ out
 
 // Upsample(scale 2, bilinear, align_corners=True) (src/models/unetpp.py:76):
 // src = dst * (in-1)/(out-1) in fp32, as ATen's area_pixel_compute_source_index does.
-__global__ void k_upsample2(const act_t* __restrict__ in, act_t* __restrict__ out,
-                            int nchunks, PPLayout Li, PPLayout Lo, float sy, float sx) {
-  int q = blockIdx.x * blockDim.x + threadIdx.x;
-  int chunk = blockIdx.y, b = blockIdx.z;
-  if (q >= Lo.ntiles * 128) return;
-  int yy = q / Lo.pitch, xx = q - yy * Lo.pitch;
-  uint4 v = make_uint4(0, 0, 0, 0);
-  if (q < Lo.npos && yy >= 1 && yy <= Lo.H && xx >= 1 && xx <= Lo.W) {
-    float fy = sy * (float)(yy - 1), fx = sx * (float)(xx - 1);
-    int y0 = (int)fy, x0 = (int)fx;
-    float ly = fy - (float)y0, lx = fx - (float)x0;
-    int y1 = y0 + (y0 < Li.H - 1 ? 1 : 0), x1 = x0 + (x0 < Li.W - 1 ? 1 : 0);
-    const act_t* pl = in + pp_off(b, chunk, nchunks, Li.Ppl, 0);
-    auto ld = [&](int y, int x) {
-      return *reinterpret_cast<const uint4*>(pl + (size_t)(Li.G + (y + 1) * Li.pitch + x + 1) * 8);
-    };
-    uint4 a = ld(y0, x0), c = ld(y0, x1), d = ld(y1, x0), e = ld(y1, x1);
-    const act_t* ha = reinterpret_cast<const act_t*>(&a);
-    const act_t* hc = reinterpret_cast<const act_t*>(&c);
-    const act_t* hd = reinterpret_cast<const act_t*>(&d);
-    const act_t* he = reinterpret_cast<const act_t*>(&e);
-    act_t r[8];
-    float wy0 = 1.f - ly, wx0 = 1.f - lx;
+// A thread owns one output column of one (image, chunk) plane and walks DOWN UP_R output rows:
+// the column terms (x0, lx) are computed once, every input row is loaded and x-blended once
+// (the source row index advances by 0 or 1 per output row, block-uniformly), and an output costs
+// one y-blend.  The blend is packed 16-bit arithmetic, a + l*(c-a).  With one thread per output
+// and fp32 math the kernel was issue-bound at 220 instructions per 16-byte output, 2.3x its HBM
+// time (profiles/r01_glue.md).  No index clamps are needed: x0+1 / y0+1 can only leave the image
+// with weight 0, where they read the zero border.  Edge threads also write the zero border.
+constexpr int UP_R = 8;
+__global__ void __launch_bounds__(128) k_upsample2(const act_t* __restrict__ in, act_t* __restrict__ out,
+                                                   PPLayout Li, PPLayout Lo, float sy, float sx) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;            // output image column
+  const int oy0 = blockIdx.y * UP_R;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  act_t* oplane = out + ((size_t)blockIdx.z * Lo.Ppl + Lo.G) * 8;
+  if (blockIdx.x == 0 && blockIdx.y == gridDim.y - 1)             // tail the flat conv tiles over-read
+    for (int q = Lo.npos + threadIdx.x; q < Lo.ntiles * 128; q += blockDim.x) *reinterpret_cast<uint4*>(oplane + (size_t)q * 8) = zero;
+  if (x >= Lo.W) return;
+  const bool left = x == 0, right = x == Lo.W - 1;
+  auto put = [&](act_t* p, uint4 v) {                             // p = this thread's position in a padded row
+    *reinterpret_cast<uint4*>(p) = v;
+    if (left) *reinterpret_cast<uint4*>(p - 8) = zero;
+    if (right) *reinterpret_cast<uint4*>(p + 8) = zero;
+  };
+  if (blockIdx.y == 0) put(oplane + (size_t)(x + 1) * 8, zero);
+  if (blockIdx.y == gridDim.y - 1) put(oplane + ((size_t)(Lo.H + 1) * Lo.pitch + x + 1) * 8, zero);
+
+  const float fx = sx * (float)x;
+  const int x0 = (int)fx;
+  const float lx = fx - (float)x0;
+  const act2_t lx2 = f2a2(lx, lx);
+  const act_t* pin = in + ((size_t)blockIdx.z * Li.Ppl + Li.G + Li.pitch + 1 + x0) * 8;     // image row 0, column x0
+  act_t* po = oplane + ((size_t)(oy0 + 1) * Lo.pitch + x + 1) * 8;
+  const int in_row = Li.pitch * 8, out_row = Lo.pitch * 8;
+  act2_t top[4], bot[4];
+  auto blend_row = [&](int y, act2_t* r) {
+    const uint4 a = *reinterpret_cast<const uint4*>(pin + (size_t)y * in_row);
+    const uint4 c = *reinterpret_cast<const uint4*>(pin + (size_t)y * in_row + 8);
+    const act2_t* ha = reinterpret_cast<const act2_t*>(&a);
+    const act2_t* hc = reinterpret_cast<const act2_t*>(&c);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float top = wx0 * a2f(ha[j]) + lx * a2f(hc[j]);
-      float bot = wx0 * a2f(hd[j]) + lx * a2f(he[j]);
-      r[j] = f2a(wy0 * top + ly * bot);
+    for (int j = 0; j < 4; ++j) r[j] = __hfma2(lx2, __hsub2(hc[j], ha[j]), ha[j]);
+  };
+  int cur = -2;
+#pragma unroll
+  for (int r = 0; r < UP_R; ++r) {
+    const int oy = oy0 + r;
+    if (oy >= Lo.H) break;
+    const float fy = sy * (float)oy;
+    const int y0 = (int)fy;
+    const float ly = fy - (float)y0;
+    const act2_t ly2 = f2a2(ly, ly);
+    if (y0 != cur) {
+      if (y0 == cur + 1) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) top[j] = bot[j];
+      } else {
+        blend_row(y0, top);
+      }
+      blend_row(y0 + 1, bot);
+      cur = y0;
     }
-    v = *reinterpret_cast<uint4*>(r);
+    uint4 v;
+    act2_t* o2 = reinterpret_cast<act2_t*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o2[j] = __hfma2(ly2, __hsub2(bot[j], top[j]), top[j]);
+    put(po + (size_t)r * out_row, v);
   }
-  *reinterpret_cast<uint4*>(out + pp_off(b, chunk, nchunks, Lo.Ppl, Lo.G + q)) = v;
 }
 
 }  // namespace
@@ -151,8 +186,10 @@ int upsample2_pp(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W,
   float sy = (2 * H > 1) ? (float)(H - 1) / (float)(2 * H - 1) : 0.f;
   float sx = (2 * W > 1) ? (float)(W - 1) / (float)(2 * W - 1) : 0.f;
   TimeScope ts(ctx, UB_T_GLUE, st);
-  dim3 grid(cdiv(Lo.ntiles * 128, 256), C / 8, B);
-  k_upsample2<<<grid, 256, 0, st>>>(in, out, C / 8, Li, Lo, sy, sx);
+  if ((long long)B * (C / 8) > 65535) return ub_fail(ctx, UB_ERR_ARG, "upsample: %d planes exceed the grid limit", B * (C / 8));
+  const int tx = Lo.W >= 128 ? 128 : ((Lo.W + 31) & ~31);
+  dim3 grid(cdiv(Lo.W, tx), cdiv(Lo.H, UP_R), B * (C / 8));
+  k_upsample2<<<grid, tx, 0, st>>>(in, out, Li, Lo, sy, sx);
   UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
