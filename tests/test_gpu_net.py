@@ -96,6 +96,23 @@ def test_forward_vs_fp32_oracle(ctx, sd, hw, golden_net):
     assert agree >= 0.998
 
 
+@pytest.mark.parametrize("ncls", [2, 5, 8])
+def test_forward_other_class_counts(ncls):
+    """The fused 1x1 head has a 3-class fast path; other class counts take the generic one."""
+    from unet_b200 import _lib
+    sdn = S.make_state_dict(seed=3, num_classes=ncls)
+    c = _lib.Context(0, max_batch=2, frame_hw=(64, 64), net_hw=(64, 96), num_classes=ncls)
+    c.set_weights(sdn)
+    x = torch.rand(2, 3, 64, 96, generator=torch.Generator().manual_seed(ncls))
+    want = R.unet_forward(x, sdn)
+    got = c.forward(x.cuda()).cpu()
+    c.close()
+    assert got.shape == (2, ncls, 64, 96)
+    rel = float((got - want).abs().max() / want.abs().max())
+    print(f"{ncls} classes: max-rel {rel:.4g}")
+    assert rel <= LOGIT_REL_TOL
+
+
 def test_forward_golden_reference_outputs(ctx, sd, golden_net):
     """Against logits produced by the REAL reference module (tests/golden/net.npz)."""
     for tag in ("a", "b"):

@@ -84,7 +84,11 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
   return r;
 }
 
-template <int COUT, int KC>
+// NCLS: 0 = plain layer; 3 = fused head with exactly 3 classes (the shipped model); 8 = fused head with a run-time
+// class count <= 8.  The class count must be a compile-time constant on the hot configuration: with the run-time
+// bound the head cost 8x32 predicated FFMAs plus local-memory traffic per pixel and made the last layer issue-bound
+// (845 instructions per warp and tile instead of ~300, profiles/r01_conv.md).
+template <int COUT, int KC, int NCLS>
 __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
   using C = RCfg<COUT, KC>;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -198,11 +202,13 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
       mbar_wait(bar_tfull + 8 * my_buf, use & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + my_buf * C::T_STRIDE;
-      float lg[8];
-      const bool head = COUT == 32 && P.ncls > 0;
+      constexpr bool head = NCLS > 0;
+      constexpr int NL = head ? NCLS : 1;
+      const int ncls = NCLS == 8 ? P.ncls : NCLS;
+      float lg[NL];
       if (head) {
 #pragma unroll
-        for (int c = 0; c < 8; ++c) lg[c] = c < P.ncls ? P.head[P.ncls * 32 + c] : 0.f;
+        for (int c = 0; c < NL; ++c) lg[c] = c < ncls ? P.head[ncls * 32 + c] : 0.f;
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -229,10 +235,10 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
           if (head) {
             uint32_t lo, hi;
             asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
-            const float f0 = fminf(fmaxf(__uint_as_float(lo), 0.f), UB_ACT_MAX), f1 = fminf(fmaxf(__uint_as_float(hi), 0.f), UB_ACT_MAX);
+            const float f0 = fmaxf(__uint_as_float(lo), 0.f), f1 = fmaxf(__uint_as_float(hi), 0.f);   // ReLU; fp32 feeds the head directly
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-              if (c < P.ncls) lg[c] = fmaf(P.head[c * 32 + ((c0 + j + 1) & 31)], f1, fmaf(P.head[c * 32 + ((c0 + j) & 31)], f0, lg[c]));
+            for (int c = 0; c < NL; ++c)
+              if (NCLS != 8 || c < ncls) lg[c] = fmaf(P.head[c * 32 + ((c0 + j + 1) & 31)], f1, fmaf(P.head[c * 32 + ((c0 + j) & 31)], f0, lg[c]));
           } else {
             hv[j >> 1] = valid ? relu_pack(v) : 0u;
           }
@@ -252,11 +258,12 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
       if (head && valid) {
         const size_t hw = (size_t)L.H * L.W, pix = (size_t)y * L.W + x;
         int best = 0;
+        float bestv = lg[0];
 #pragma unroll
-        for (int c = 0; c < 8; ++c)
-          if (c < P.ncls) {
-            if (P.logits) P.logits[((size_t)b * P.ncls + c) * hw + pix] = lg[c];
-            if (c > 0 && lg[c] > lg[best]) best = c;
+        for (int c = 0; c < NL; ++c)
+          if (NCLS != 8 || c < ncls) {
+            if (P.logits) P.logits[((size_t)b * ncls + c) * hw + pix] = lg[c];
+            if (c > 0 && lg[c] > bestv) { best = c; bestv = lg[c]; }      // first maximum wins, as np.argmax
           }
         if (P.pred) P.pred[(size_t)b * hw + pix] = (uint8_t)best;
       }
@@ -273,10 +280,10 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 
-template <int COUT, int KC>
+template <int COUT, int KC, int NCLS>
 int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
   using C = RCfg<COUT, KC>;
-  auto kern = k_conv_rows<COUT, KC>;
+  auto kern = k_conv_rows<COUT, KC, NCLS>;
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
@@ -317,10 +324,14 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
 }
 
 int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
-  if (cout == 32 && kc == 16) return launch_rows<32, 16>(ctx, P, a, Lr, st, init_only);
-  if (cout == 32 && kc == 32) return launch_rows<32, 32>(ctx, P, a, Lr, st, init_only);
-  if (cout == 64 && kc == 32) return launch_rows<64, 32>(ctx, P, a, Lr, st, init_only);
-  if (cout == 64 && kc == 64) return launch_rows<64, 64>(ctx, P, a, Lr, st, init_only);
+  if (P.ncls > 0) {
+    if (cout != 32 || kc != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs COUT=32 KC=32 (got %d, %d)", cout, kc);
+    return P.ncls == 3 ? launch_rows<32, 32, 3>(ctx, P, a, Lr, st, init_only) : launch_rows<32, 32, 8>(ctx, P, a, Lr, st, init_only);
+  }
+  if (cout == 32 && kc == 16) return launch_rows<32, 16, 0>(ctx, P, a, Lr, st, init_only);
+  if (cout == 32 && kc == 32) return launch_rows<32, 32, 0>(ctx, P, a, Lr, st, init_only);
+  if (cout == 64 && kc == 32) return launch_rows<64, 32, 0>(ctx, P, a, Lr, st, init_only);
+  if (cout == 64 && kc == 64) return launch_rows<64, 64, 0>(ctx, P, a, Lr, st, init_only);
   return ub_fail(ctx, UB_ERR_ARG, "conv_rows: unsupported COUT=%d KC=%d", cout, kc);
 }
 
@@ -328,9 +339,10 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& 
 
 int conv_rows_init(ub_ctx* ctx) {
   static RowsParams P{};
-  const int cfgs[4][2] = {{32, 16}, {32, 32}, {64, 32}, {64, 64}};
+  const int cfgs[6][3] = {{32, 16, 0}, {32, 32, 0}, {64, 32, 0}, {64, 64, 0}, {32, 32, 3}, {32, 32, 8}};
   ConvArgs a{}; ConvLayer Lr{};
   for (auto& c : cfgs) {
+    P.ncls = c[2];
     int r = dispatch_rows(ctx, c[0], c[1], P, a, Lr, nullptr, true);
     if (r != UB_OK) return r;
   }
