@@ -43,6 +43,7 @@ struct RowsParams {
   int B, kb0, kbn, num_stages, b_resident;
   int tiles_x, tiles_y;                        // tiles_y counts tile GROUPS: mt vertically adjacent 4-row M-tiles share one box
   int mt, a_chunk, a_stage;                    // M-tiles per group; bytes of one chunk / one stage of the box ((4*mt+2) rows)
+  int halves;                                  // 2: the MMA issuer walks a group's boxes twice, half the M-tiles each (kbn > 1)
   long long total_items;
   PPLayout L;
   int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
@@ -144,40 +145,56 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
       }
     }
   } else if (warp == 17) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues =====================
+    {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) |
                                  ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-      int s = 0; uint32_t ph = 0; int it = 0;                    // it counts M-tiles (accumulator uses)
+      int it = 0;                                                 // counts M-tiles (accumulator uses)
+      int s0 = 0; uint32_t ph0 = 0;                                // stage / phase of the group's first box (this warp paces
+                                                                   // the tensor pipe: no divisions in here)
+      // With several k-blocks all mt accumulators of a group are live until its last k-block.  P.halves == 2 walks the
+      // group's staged boxes twice, first for M-tiles 0..mt/2-1 then for the rest, so the first half's accumulators
+      // complete earlier (needs all kbn boxes of a group resident: num_stages >= kbn + 1).
+      const int mh = P.mt / P.halves;
       for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x, it += P.mt) {
-        for (int kb = 0; kb < P.kbn; ++kb) {
-          mbar_wait(bar_full + 8 * s, ph);
-          tc_fence_after();
-          const uint32_t a_st = a_base + s * P.a_stage;
-          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
-          for (int m = 0; m < P.mt; ++m) {
-            const int buf = (it + m) % C::NBUF, use = (it + m) / C::NBUF;
-            if (kb == 0) {                                     // first touch of this accumulator: the epilogue must have drained it
-              mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
+        int s = s0; uint32_t ph = ph0;
+        for (int h = 0; h < P.halves; ++h) {
+          s = s0; ph = ph0;
+          for (int kb = 0; kb < P.kbn; ++kb) {
+            if (h == 0) {
+              mbar_wait(bar_full + 8 * s, ph);
               tc_fence_after();
             }
-            const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
-#pragma unroll
-            for (int ky = 0; ky < 3; ++ky) {
-#pragma unroll
-              for (int k16 = 0; k16 < KC / 16; ++k16) {
-                // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
-                // the two K chunks a_chunk apart
-                const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
-                const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
-                tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+            const uint32_t a_st = a_base + s * P.a_stage;
+            const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+            for (int m = h * mh; m < (h + 1) * mh; ++m) {
+              const int buf = (it + m) % C::NBUF, use = (it + m) / C::NBUF;
+              if (kb == 0) {                                   // first touch of this accumulator: the epilogue must have drained it
+                mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
+                tc_fence_after();
               }
+              const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
+              if (elect_one()) {
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+                  for (int k16 = 0; k16 < KC / 16; ++k16) {
+                    // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
+                    // the two K chunks a_chunk apart
+                    const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
+                    const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
+                    tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+                  }
+                }
+                if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);                         // accumulator of M-tile m complete
+                if (h == P.halves - 1 && m == (h + 1) * mh - 1) tc_commit(bar_empty + 8 * s); // box free once every M-tile read it
+              }
+              __syncwarp();
             }
-            if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);   // accumulator of M-tile m complete
+            if (++s == S) { s = 0; ph ^= 1; }
           }
-          tc_commit(bar_empty + 8 * s);                        // the box is free once every M-tile has read it
-          if (++s == S) { s = 0; ph ^= 1; }
         }
+        s0 = s; ph0 = ph;
       }
     }
   } else {
@@ -308,6 +325,10 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: COUT=%d KC=%d does not fit 2 stages", COUT, KC);
   P.num_stages = stages;
   P.mt = mt;
+  // measured: 5748 frames/s with 1, 5680 with 2 (same box) -- the tensor pipe, not the accumulator hand-over, paces
+  // these layers; the two-pass walk stays available for experiments
+  static const int halves_env = getenv("UB_ROWS_HALVES") ? atoi(getenv("UB_ROWS_HALVES")) : 1;
+  P.halves = (halves_env == 2 && P.kbn > 1 && mt >= 2 && stages >= P.kbn + 1) ? 2 : 1;
   P.a_chunk = (T_ROWS * mt + 2) * SEG_BYTES;
   P.a_stage = C::CPK * P.a_chunk;
   P.tiles_y = a.H / (T_ROWS * mt);

@@ -18,6 +18,7 @@
 // warp 4 bulk-copy producer (+TMEM alloc), warp 5 MMA issuer (one elected lane).
 // Persistent CTAs, one per SM; TMEM accumulators double-buffered so the epilogue of item i
 // overlaps the MMAs of item i+1.
+#include <stdlib.h>
 #include "tc_ptx.cuh"
 
 namespace {
@@ -48,9 +49,34 @@ struct Cfg {
   static constexpr int HDR = 2048;                                     // barriers + head weights
 };
 
-template <int BN, int KC, bool SHIFT_A>
+// Work item i of this CTA.  Unpaired: items (image, m-tile, n-tile) round-robin over the grid.  PAIR: the two CTAs of
+// a cluster walk the SAME (n-tile, k-block) sequence on two neighbouring m-tiles, so each loads half of every weight
+// stage and multicasts it to both (the deep layers stream 74 KB of weights per 13 KB of activations and were bound
+// by L2->SM bandwidth, profiles/r01_conv.md).  An odd tail item is computed by both CTAs (identical stores).
+template <bool PAIR>
+__device__ __forceinline__ bool tc_item(const TcParams& P, int i, uint32_t rank, int& nt, int& mt, int& b) {
+  if (!PAIR) {
+    const long long item = blockIdx.x + (long long)i * gridDim.x;
+    if (item >= P.total_items) return false;
+    nt = (int)(item % P.n_ntiles);
+    const long long r = item / P.n_ntiles;
+    mt = (int)(r % P.L.ntiles); b = (int)(r / P.L.ntiles);
+    return true;
+  }
+  const long long M = (long long)P.B * P.L.ntiles, ppn = (M + 1) / 2;
+  const long long j = (blockIdx.x >> 1) + (long long)i * (gridDim.x >> 1);
+  if (j >= ppn * P.n_ntiles) return false;
+  nt = (int)(j / ppn);
+  long long m = 2 * (j - (long long)nt * ppn) + rank;
+  if (m > M - 1) m = M - 1;
+  mt = (int)(m % P.L.ntiles); b = (int)(m / P.L.ntiles);
+  return true;
+}
+
+template <int BN, int KC, bool SHIFT_A, bool PAIR>
 __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcParams P) {
   using C = Cfg<BN, KC, SHIFT_A>;
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = P.num_stages;
@@ -65,7 +91,8 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
   const PPLayout& L = P.L;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    // PAIR: a stage is free when the MMAs of BOTH CTAs have retired (the peer writes half of it)
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, PAIR ? 2 : 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -82,6 +109,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (PAIR) cluster_sync();                  // the peer's barriers exist before anything is multicast to them
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 4) {
@@ -90,10 +118,8 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
     //  costs ~100 cycles per copy -- profiles/r01_conv.md)
     if (lane == 0) {
       int s = 0; uint32_t ph = 0; bool first = true;
-      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x) {
-        const int nt = (int)(item % P.n_ntiles);
-        const long long r = item / P.n_ntiles;
-        const int mt = (int)(r % L.ntiles), b = (int)(r / L.ntiles);
+      int nt, mt, b;
+      for (int i = 0; tc_item<PAIR>(P, i, cta_rank, nt, mt, b); ++i) {
         const int p0 = L.G + mt * TILE_M;
         const bool load_b = !P.b_resident || first;
         for (int kb = 0; kb < P.kbn; ++kb) {
@@ -111,9 +137,12 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
             for (int cc = 0; cc < C::CPK; ++cc)
               bulk_g2s(a_st + (seg * C::CPK + cc) * C::A_SEG_BYTES, plane0 + ((size_t)cc * L.Ppl + p0 + off) * 8, C::A_SEG_BYTES, full);
           }
-          if (load_b)
-            bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE,
-                     P.w + ((size_t)nt * P.kbn + kb) * 9 * (size_t)(KC * BN), C::B_STAGE, full);
+          if (load_b) {
+            const act_t* wsrc = P.w + ((size_t)nt * P.kbn + kb) * 9 * (size_t)(KC * BN);
+            const uint32_t wdst = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+            if (PAIR) bulk_g2s_mcast(wdst + cta_rank * (C::B_STAGE / 2), wsrc + cta_rank * (C::B_STAGE / 4), C::B_STAGE / 2, full, 3);
+            else bulk_g2s(wdst, wsrc, C::B_STAGE, full);
+          }
           if (++s == S) { s = 0; ph ^= 1; }
         }
         first = false;
@@ -124,8 +153,9 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
     if (lane == 0) {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)(TILE_M >> 4) << 24);
-      int s = 0; uint32_t ph = 0; int it = 0;
-      for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
+      int s = 0; uint32_t ph = 0;
+      int nt, mt, b;
+      for (int it = 0; tc_item<PAIR>(P, it, cta_rank, nt, mt, b); ++it) {
         const int buf = it & 1;
         mbar_wait(bar_tempty + 8 * buf, ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -146,7 +176,8 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
               tc_mma(d_tmem, ad, bd, IDESC, (kb | tap | k16) != 0);
             }
           }
-          tc_commit(bar_empty + 8 * s);          // frees the smem stage when these MMAs retire
+          if (PAIR) tc_commit_mcast(bar_empty + 8 * s, 3);   // ... in both CTAs
+          else tc_commit(bar_empty + 8 * s);     // frees the smem stage when these MMAs retire
           if (++s == S) { s = 0; ph ^= 1; }
         }
         tc_commit(bar_tfull + 8 * buf);          // accumulator ready for the epilogue
@@ -154,13 +185,10 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
     }
   } else {
     // ===================== epilogue: TMEM -> registers -> global =====================
-    int it = 0;
     const int row = warp * 32 + lane;
     const int nco_chunks = P.cout / 8;
-    for (long long item = blockIdx.x; item < P.total_items; item += gridDim.x, ++it) {
-      const int nt = (int)(item % P.n_ntiles);
-      const long long r = item / P.n_ntiles;
-      const int mt = (int)(r % L.ntiles), b = (int)(r / L.ntiles);
+    int nt, mt, b;
+    for (int it = 0; tc_item<PAIR>(P, it, cta_rank, nt, mt, b); ++it) {
       const int buf = it & 1;
       const int q = mt * TILE_M + row;
       const int yy = q / L.pitch, xx = q - yy * L.pitch;
@@ -215,6 +243,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
 
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync();                  // no CTA leaves while its peer may still multicast to it
   if (warp == 4) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS));
@@ -226,9 +255,11 @@ constexpr int SMEM_BUDGET = 227 * 1024;
 template <int BN, int KC, bool SHIFT_A>
 int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
   using C = Cfg<BN, KC, SHIFT_A>;
-  auto kern = k_conv_tc<BN, KC, SHIFT_A>;
+  auto kern = k_conv_tc<BN, KC, SHIFT_A, false>;
+  auto kern_pair = k_conv_tc<BN, KC, SHIFT_A, true>;
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+    UB_CUDA(ctx, cudaFuncSetAttribute(kern_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
   }
   // weights resident in shared memory when they fit beside >= 3 activation stages
@@ -245,6 +276,24 @@ int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_tc: BN=%d KC=%d does not fit 2 stages", BN, KC);
   P.num_stages = stages;
   const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  // streamed weights: CTA pairs (clusters of 2) share every weight stage by multicast
+  static const int pair_env = getenv("UB_TC_PAIR") ? atoi(getenv("UB_TC_PAIR")) : 1;
+  const long long M = (long long)P.B * P.L.ntiles;
+  if (!P.b_resident && pair_env && M >= 2 && ctx->sm_count >= 2) {
+    const long long pairs = (M + 1) / 2 * P.n_ntiles, max_pairs = ctx->sm_count / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * (pairs < max_pairs ? pairs : max_pairs)));
+    cfg.blockDim = dim3(192);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern_pair, P));
+    UB_CHECK_LAUNCH(ctx);
+    return UB_OK;
+  }
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
   kern<<<(unsigned)grid, 192, smem, st>>>(P);
   UB_CHECK_LAUNCH(ctx);
