@@ -3,6 +3,7 @@
 // (detect_burrs_on_cable, infer_two_stage_burr.py:50-119; detect_burrs_enhanced,
 // infer_enhanced_burr.py:69-138).
 #include <limits.h>
+#include <stdlib.h>
 #include <math.h>
 #include "stage2_kernels.cuh"
 
@@ -166,6 +167,189 @@ __global__ void __launch_bounds__(256) k_ccl_filter(const int* __restrict__ lab_
   if (px && m && (threadIdx.x & 31) == 0) atomicAdd(px + blockIdx.z * px_stride, __popc(m));
 }
 
+// ==============================================================================
+// Run-based labelling on bit-packed rows (the path of canny() and burr_stage()).
+// A word holds 32 pixels of a row; a RUN is a maximal group of set bits inside one word and is
+// represented by its first pixel.  Only run starts carry union-find entries, unions are issued
+// per pair of touching runs, and every pass is one thread per word: ~32x fewer threads and
+// memory operations than the per-pixel kernels above (which ub_ccl's OpenCV-numbered export
+// still uses).  Roots are the smallest pixel index of a component, as before.
+// ==============================================================================
+__device__ __forceinline__ uint32_t bits_range(int a, int b) {            // bits a..b inclusive, 0 <= a <= b <= 31
+  return (0xffffffffu >> (31 - b)) & (0xffffffffu << a);
+}
+// first run of m: returns its mask; a = first bit, len = length
+__device__ __forceinline__ uint32_t first_run(uint32_t m, int& a, int& len) {
+  a = __ffs(m) - 1;
+  const uint32_t nt = ~(m >> a);
+  len = nt ? __ffs(nt) - 1 : 32 - a;
+  return bits_range(a, a + len - 1);
+}
+// start bit of the run of word u that contains set bit i
+__device__ __forceinline__ int run_start_of(uint32_t u, int i) {
+  return i == 0 ? 0 : i - __clz(~(u << (32 - i)));
+}
+
+// pack + one union-find entry per run.  strong (nullable): bits of pixels == 2 (Canny strong candidates)
+__global__ void __launch_bounds__(256) k_cclb_init(const uint8_t* __restrict__ src, uint32_t* __restrict__ bits, uint32_t* __restrict__ strong,
+                                                   int* __restrict__ lab, int H, int W, int Wd) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  const size_t fb = (size_t)blockIdx.z * H * W, wb = ((size_t)blockIdx.z * H + y) * Wd + w;
+  uint32_t c = pack32(src + fb, H, W, y, 32 * w);
+  bits[wb] = c;
+  if (strong) strong[wb] = c & ~pack32(src + fb, H, W, y, 32 * w, 0x02020202u);
+  int* l = lab + fb + (size_t)y * W + 32 * w;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    l[a] = y * W + 32 * w + a;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_cclb_merge(const uint32_t* __restrict__ bits, int* __restrict__ lab_all, int H, int W, int Wd) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  const uint32_t* row = bits + ((size_t)blockIdx.z * H + y) * Wd;
+  uint32_t c = row[w];
+  if (!c) return;
+  int* lab = lab_all + (size_t)blockIdx.z * H * W;
+  const int p0 = y * W + 32 * w;
+  if ((c & 1u) && w > 0) {                                   // the run continues from the previous word
+    const uint32_t L = row[w - 1];
+    if (L >> 31) uf_union(lab, p0, p0 - 32 + run_start_of(L, 31));
+  }
+  if (y == 0) return;
+  const uint32_t* up = row - Wd;
+  const uint32_t u = up[w], ul = w > 0 ? up[w - 1] : 0u, ur = w + 1 < Wd ? up[w + 1] : 0u;
+  if (!(u | (ul >> 31) | (ur & 1u))) return;
+  const int q0 = p0 - W;                                     // pixel index of bit 0 of the word above
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int b = a + len - 1, me = p0 + a;
+    uint32_t um = u & bits_range(a > 0 ? a - 1 : 0, b < 31 ? b + 1 : 31);    // 8-connected neighbours in the word above
+    while (um) {
+      int ua, ulen;
+      um &= ~first_run(um, ua, ulen);
+      uf_union(lab, me, q0 + run_start_of(u, ua));
+    }
+    if (a == 0 && (ul >> 31)) uf_union(lab, me, q0 - 32 + run_start_of(ul, 31));
+    if (b == 31 && (ur & 1u)) uf_union(lab, me, q0 + 32);
+  }
+}
+
+// path compression of the run starts; roots initialise their accumulators when `comp` is given
+__global__ void __launch_bounds__(256) k_cclb_flatten(const uint32_t* __restrict__ bits, int* __restrict__ lab_all, int H, int W, int Wd,
+                                                      int* __restrict__ comp, size_t plane) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  int* lab = lab_all + base;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int p = y * W + 32 * w + a;
+    const int r = uf_find(lab, p);
+    lab[p] = r;
+    if (comp && r == p) {
+      int* k = comp + base + p;
+      k[0] = 0; k[plane] = INT_MAX; k[2 * plane] = -1; k[3 * plane] = INT_MAX; k[4 * plane] = -1; k[5 * plane] = INT_MAX;
+    }
+  }
+}
+
+// expand a word to 32 bytes of {0, value} and store (vector store when aligned)
+__device__ __forceinline__ void store_bits_as_bytes(uint8_t* __restrict__ o, uint32_t word, int nvalid, uint32_t value) {
+  if (nvalid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = ((((word >> (4 * k)) & 15u) * 0x00204081u) & 0x01010101u) * value;
+    *reinterpret_cast<uint4*>(o) = make_uint4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<uint4*>(o + 16) = make_uint4(v[4], v[5], v[6], v[7]);
+  } else {
+    for (int k = 0; k < nvalid && k < 32; ++k) o[k] = ((word >> k) & 1u) ? (uint8_t)value : 0;
+  }
+}
+
+// Canny hysteresis: flag[root] = 1 for components holding a strong pixel, then keep flagged runs
+__global__ void __launch_bounds__(256) k_cclb_hyst_mark(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ strong,
+                                                        const int* __restrict__ lab_all, uint8_t* __restrict__ flag_all, int H, int W, int Wd) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  const size_t wb = ((size_t)blockIdx.z * H + y) * Wd + w;
+  const uint32_t sg = strong[wb];
+  if (!sg) return;
+  uint32_t c = bits[wb];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    const uint32_t rm = first_run(c, a, len);
+    c &= ~rm;
+    if (sg & rm) flag_all[base + lab_all[base + y * W + 32 * w + a]] = 1;
+  }
+}
+__global__ void __launch_bounds__(256) k_cclb_hyst_final(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all,
+                                                         const uint8_t* __restrict__ flag_all, uint8_t* __restrict__ out, int H, int W, int Wd) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w], keep = 0;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    const uint32_t rm = first_run(c, a, len);
+    c &= ~rm;
+    if (flag_all[base + lab_all[base + y * W + 32 * w + a]]) keep |= rm;
+  }
+  store_bits_as_bytes(out + base + (size_t)y * W + 32 * w, keep, W - 32 * w, 255u);
+}
+
+// component statistics, one atomic set per run (flattened labels)
+__global__ void __launch_bounds__(256) k_cclb_stats(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                    int* __restrict__ comp, size_t plane) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int x = 32 * w + a, xe = x + len - 1;
+    int* k = comp + base + lab_all[base + y * W + x];
+    atomicAdd(k, len);
+    atomicMin(k + plane, x); atomicMax(k + 2 * plane, xe);
+    atomicMin(k + 3 * plane, y); atomicMax(k + 4 * plane, y);
+  }
+}
+
+// component filter (infer_two_stage_burr.py:103-117) -> burr bytes {0,1} + per-frame pixel count
+__global__ void __launch_bounds__(256) k_cclb_filter(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                     const int* __restrict__ comp, size_t plane, ub_burr_params P,
+                                                     uint8_t* __restrict__ burr, int* __restrict__ px, int px_stride) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  int n = 0;
+  if (w < Wd && y < H) {
+    uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w], keep = 0;
+    const size_t base = (size_t)blockIdx.z * H * W;
+    while (c) {
+      int a, len;
+      const uint32_t rm = first_run(c, a, len);
+      c &= ~rm;
+      const int* k = comp + base + lab_all[base + y * W + 32 * w + a];
+      const int area = k[0], cw = k[2 * plane] - k[plane] + 1, ch = k[4 * plane] - k[3 * plane] + 1;
+      const int mx = max(cw, ch), mn = min(cw, ch);
+      if (area >= P.min_area && area <= P.max_area && mx <= P.max_aspect * mn && cw >= P.min_side && ch >= P.min_side) keep |= rm;
+    }
+    store_bits_as_bytes(burr + base + (size_t)y * W + 32 * w, keep, W - 32 * w, 1u);
+    n = __popc(keep);
+  }
+  if (px) {
+    for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(px + blockIdx.z * px_stride, n);
+  }
+}
+
 // ---- export in OpenCV numbering (ub_ccl) --------------------------------------
 __global__ void k_mark_roots(const int* __restrict__ lab_all, int H, int W, const int* __restrict__ comp, size_t plane,
                              int* __restrict__ mark, int K) {
@@ -296,9 +480,21 @@ static int ccl_label(ub_ctx* ctx, const uint8_t* src, int* lab, int B, int H, in
   return UB_OK;
 }
 
+// run-based labelling of a u8 image on packed rows: bits (+ strong) planes and lab entries at run starts
+static int cclb_label(ub_ctx* ctx, const uint8_t* src, uint32_t* bits, uint32_t* strong, int* lab, int B, int H, int W,
+                      int* comp, size_t plane, cudaStream_t st) {
+  const int Wd = (W + 31) / 32;
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  k_cclb_init<<<g, dim3(32, 8), 0, st>>>(src, bits, strong, lab, H, W, Wd);
+  k_cclb_merge<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd);
+  k_cclb_flatten<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, comp, plane);
+  UB_CHECK_LAUNCH_N(ctx, 3);
+  return UB_OK;
+}
+
 int gaussian5(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_STENCIL, st);
-  k_gauss5<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), 256, 0, st>>>(src, dst, H, W);
+  k_gauss5<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), dim3(GT_W, 4), 0, st>>>(src, dst, H, W);
   UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
@@ -308,10 +504,25 @@ int canny(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, uint8_t* cand, int* lab
   dim3 gpix(cdiv(W, 256), H, B);
   {
     TimeScope ts(ctx, UB_T_STENCIL, st);
-    k_canny_nms<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), 256, 0, st>>>(src, cand, H, W, low, high);
+    k_canny_nms<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), dim3(GT_W, 4), 0, st>>>(src, cand, H, W, low, high);
     UB_CHECK_LAUNCH(ctx);
   }
   TimeScope ts(ctx, UB_T_CCL, st);
+  static const int packed_env = getenv("UB_CCL_PACKED") ? atoi(getenv("UB_CCL_PACKED")) : 1;
+  if (packed_env) {
+    const int Wd = (W + 31) / 32;
+    const size_t nwords = (size_t)B * H * Wd;
+    uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);       // free during the burr stage
+    uint32_t* strong = bits + nwords;
+    uint8_t* flag = reinterpret_cast<uint8_t*>(ctx->d_comp);            // [B*H*W] root flags (accumulator scratch, unused until the final CCL)
+    RUN(cclb_label(ctx, cand, bits, strong, lab, B, H, W, nullptr, 0, st));
+    UB_CUDA(ctx, cudaMemsetAsync(flag, 0, (size_t)B * H * W, st));
+    dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+    k_cclb_hyst_mark<<<g, dim3(32, 8), 0, st>>>(bits, strong, lab, flag, H, W, Wd);
+    k_cclb_hyst_final<<<g, dim3(32, 8), 0, st>>>(bits, lab, flag, dst, H, W, Wd);
+    UB_CHECK_LAUNCH_N(ctx, 2);
+    return UB_OK;
+  }
   RUN(ccl_label(ctx, cand, lab, B, H, W, nullptr, 0, st));
   UB_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t)B * H * W, st));
   k_hyst_mark<<<gpix, 256, 0, st>>>(cand, lab, dst, H, W);
@@ -367,20 +578,42 @@ int burr_stage(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mas
   RUN(gaussian5(ctx, gray, t0, B, H, W, st));
   RUN(canny(ctx, t0, t1, t2, lab, B, H, W, P.canny_low, P.canny_high, st));
   if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
-  {
+  static const int fuse_env = getenv("UB_MORPH_FUSED") ? atoi(getenv("UB_MORPH_FUSED")) : 1;
+  MorphChain mc;
+  const bool fp_ok = make_footprint(P.band_k, mc.band) && make_footprint(P.close_k, mc.close) && make_footprint(P.open_k, mc.open);
+  if (!fp_ok) return ub_fail(ctx, UB_ERR_ARG, "ellipse sizes %d/%d/%d unsupported (1..25)", P.band_k, P.close_k, P.open_k);
+  if (fuse_env && 2 * (P.open_k / 2) + 2 * (P.close_k / 2) + P.band_k / 2 <= FM_HALO) {
+    // band, candidates, CLOSE, OPEN in one pass over bit-packed tiles                -> t2
     TimeScope ts(ctx, UB_T_STENCIL, st);
-    // detection band = dilate(mask) & ~mask                                      [t0]
-    RUN(morph_once(ctx, true, P.band_k, mask, t0, B, H, W, 1, mask, st));
-    // candidates = edges & band                                                  [t2]
-    k_and01<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(t1, t0, t2, n);
+    k_burr_morph<<<dim3(cdiv(W, FM_W), cdiv(H, FM_TH), B), 256, 0, st>>>(mask, t1, t2, H, W, mc);
     UB_CHECK_LAUNCH(ctx);
+  } else {
+    {
+      TimeScope ts(ctx, UB_T_STENCIL, st);
+      // detection band = dilate(mask) & ~mask                                      [t0]
+      RUN(morph_once(ctx, true, P.band_k, mask, t0, B, H, W, 1, mask, st));
+      // candidates = edges & band                                                  [t2]
+      k_and01<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(t1, t0, t2, n);
+      UB_CHECK_LAUNCH(ctx);
+    }
+    RUN(morph_op(ctx, 2, P.close_k, t2, t1, t3, B, H, W, 1, st));                   // CLOSE -> t1
+    RUN(morph_op(ctx, 3, P.open_k, t1, t2, t3, B, H, W, 1, st));                    // OPEN  -> t2
   }
-  RUN(morph_op(ctx, 2, P.close_k, t2, t1, t3, B, H, W, 1, st));                   // CLOSE -> t1
-  RUN(morph_op(ctx, 3, P.open_k, t1, t2, t3, B, H, W, 1, st));                    // OPEN  -> t2
   // components + filter
   TimeScope ts(ctx, UB_T_CCL, st);
   const int segs = (W + 31) / 32;
   dim3 gseg(cdiv(H * segs * 32, 256), 1, B), gpix(cdiv(W, 256), H, B);
+  static const int packed_env = getenv("UB_CCL_PACKED") ? atoi(getenv("UB_CCL_PACKED")) : 1;
+  if (packed_env) {
+    const int Wd = (W + 31) / 32;
+    uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+    RUN(cclb_label(ctx, t2, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+    dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+    k_cclb_stats<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_cclb_filter<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, P, burr, burr_px, px_stride);
+    UB_CHECK_LAUNCH_N(ctx, 2);
+    return UB_OK;
+  }
   RUN(ccl_label(ctx, t2, lab, B, H, W, ctx->d_comp, plane, st));
   k_ccl_stats<<<gseg, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, nullptr);
   k_ccl_filter<<<gpix, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, P, burr, burr_px, px_stride);

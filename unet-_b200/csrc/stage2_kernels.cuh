@@ -18,30 +18,32 @@ __device__ __forceinline__ int clampi(int i, int n) { return i < 0 ? 0 : (i >= n
 // [14,62,104,62,14], REFLECT_101, one rounding (acc + 2^15) >> 16.
 // Tile 64x16 outputs per block of 256 threads; shared-memory staged, halo 2.
 // ------------------------------------------------------------------------------
-constexpr int GT_W = 64, GT_H = 16;
+constexpr int GT_W = 64, GT_H = 16;           // blocks are (64, 4) threads: column = threadIdx.x, rows strided by 4 (no div/mod)
 __global__ void __launch_bounds__(256) k_gauss5(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int H, int W) {
   __shared__ uint8_t s_in[GT_H + 4][GT_W + 4];
   __shared__ int s_h[GT_H + 4][GT_W];
   const int x0 = blockIdx.x * GT_W, y0 = blockIdx.y * GT_H;
+  const int tx = threadIdx.x, ty = threadIdx.y;
   const uint8_t* img = src + (size_t)blockIdx.z * H * W;
-  for (int i = threadIdx.x; i < (GT_H + 4) * (GT_W + 4); i += 256) {
-    int ty = i / (GT_W + 4), tx = i - ty * (GT_W + 4);
-    s_in[ty][tx] = img[(size_t)reflect101(y0 + ty - 2, H) * W + reflect101(x0 + tx - 2, W)];
+  const int gx0 = reflect101(x0 + tx - 2, W), gx1 = reflect101(x0 + tx + GT_W - 2, W);
+  for (int r = ty; r < GT_H + 4; r += 4) {
+    const uint8_t* row = img + (size_t)reflect101(y0 + r - 2, H) * W;
+    s_in[r][tx] = row[gx0];
+    if (tx < 4) s_in[r][tx + GT_W] = row[gx1];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < (GT_H + 4) * GT_W; i += 256) {
-    int ty = i / GT_W, tx = i - ty * GT_W;
-    s_h[ty][tx] = 14 * (s_in[ty][tx] + s_in[ty][tx + 4]) + 62 * (s_in[ty][tx + 1] + s_in[ty][tx + 3]) + 104 * s_in[ty][tx + 2];
-  }
+  for (int r = ty; r < GT_H + 4; r += 4)
+    s_h[r][tx] = 14 * (s_in[r][tx] + s_in[r][tx + 4]) + 62 * (s_in[r][tx + 1] + s_in[r][tx + 3]) + 104 * s_in[r][tx + 2];
   __syncthreads();
-  for (int i = threadIdx.x; i < GT_H * GT_W; i += 256) {
-    int ty = i / GT_W, tx = i - ty * GT_W;
-    int x = x0 + tx, y = y0 + ty;
-    if (x < W && y < H) {
-      int acc = 14 * (s_h[ty][tx] + s_h[ty + 4][tx]) + 62 * (s_h[ty + 1][tx] + s_h[ty + 3][tx]) + 104 * s_h[ty + 2][tx];
-      dst[(size_t)blockIdx.z * H * W + (size_t)y * W + x] = (uint8_t)((acc + (1 << 15)) >> 16);
+  const int x = x0 + tx;
+  if (x < W)
+    for (int r = ty; r < GT_H; r += 4) {
+      const int y = y0 + r;
+      if (y < H) {
+        const int acc = 14 * (s_h[r][tx] + s_h[r + 4][tx]) + 62 * (s_h[r + 1][tx] + s_h[r + 3][tx]) + 104 * s_h[r + 2][tx];
+        dst[(size_t)blockIdx.z * H * W + (size_t)y * W + x] = (uint8_t)((acc + (1 << 15)) >> 16);
+      }
     }
-  }
 }
 
 // ------------------------------------------------------------------------------
@@ -53,47 +55,51 @@ __global__ void __launch_bounds__(256) k_canny_nms(const uint8_t* __restrict__ s
                                                    int H, int W, int low, int high) {
   __shared__ uint8_t s_in[GT_H + 4][GT_W + 4];
   __shared__ int s_mag[GT_H + 2][GT_W + 2];
-  __shared__ short s_gx[GT_H][GT_W], s_gy[GT_H][GT_W];
+  __shared__ short s_gx[GT_H + 2][GT_W + 2], s_gy[GT_H + 2][GT_W + 2];
   const int x0 = blockIdx.x * GT_W, y0 = blockIdx.y * GT_H;
+  const int tx = threadIdx.x, ty = threadIdx.y;
   const uint8_t* img = src + (size_t)blockIdx.z * H * W;
-  for (int i = threadIdx.x; i < (GT_H + 4) * (GT_W + 4); i += 256) {
-    int ty = i / (GT_W + 4), tx = i - ty * (GT_W + 4);
-    s_in[ty][tx] = img[(size_t)clampi(y0 + ty - 2, H) * W + clampi(x0 + tx - 2, W)];
+  const int gx0 = clampi(x0 + tx - 2, W), gx1 = clampi(x0 + tx + GT_W - 2, W);
+  for (int r = ty; r < GT_H + 4; r += 4) {
+    const uint8_t* row = img + (size_t)clampi(y0 + r - 2, H) * W;
+    s_in[r][tx] = row[gx0];
+    if (tx < 4) s_in[r][tx + GT_W] = row[gx1];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < (GT_H + 2) * (GT_W + 2); i += 256) {
-    int ty = i / (GT_W + 2), tx = i - ty * (GT_W + 2);
-    int x = x0 + tx - 1, y = y0 + ty - 1;                  // image coords of this mag sample
-    int m = 0;
-    if (x >= 0 && x < W && y >= 0 && y < H) {
-      // s_in index of (y,x) is [ty+1][tx+1]
-      int a = s_in[ty][tx], b = s_in[ty][tx + 1], c = s_in[ty][tx + 2];
-      int d = s_in[ty + 1][tx], f = s_in[ty + 1][tx + 2];
-      int g = s_in[ty + 2][tx], h = s_in[ty + 2][tx + 1], k = s_in[ty + 2][tx + 2];
-      int gx = (c + 2 * f + k) - (a + 2 * d + g);
-      int gy = (g + 2 * h + k) - (a + 2 * b + c);
-      m = abs(gx) + abs(gy);
-      if (ty >= 1 && ty <= GT_H && tx >= 1 && tx <= GT_W) { s_gx[ty - 1][tx - 1] = (short)gx; s_gy[ty - 1][tx - 1] = (short)gy; }
+  // magnitude / gradients at the (GT_H+2) x (GT_W+2) samples around the tile; sample (r, c) = image (y0+r-1, x0+c-1)
+  for (int r = ty; r < GT_H + 2; r += 4)
+    for (int c = tx; c < GT_W + 2; c += GT_W) {
+      const int x = x0 + c - 1, y = y0 + r - 1;
+      int m = 0, gx = 0, gy = 0;
+      if (x >= 0 && x < W && y >= 0 && y < H) {
+        const int a = s_in[r][c], b = s_in[r][c + 1], cc = s_in[r][c + 2];
+        const int d = s_in[r + 1][c], f = s_in[r + 1][c + 2];
+        const int g = s_in[r + 2][c], h = s_in[r + 2][c + 1], k = s_in[r + 2][c + 2];
+        gx = (cc + 2 * f + k) - (a + 2 * d + g);
+        gy = (g + 2 * h + k) - (a + 2 * b + cc);
+        m = abs(gx) + abs(gy);
+      }
+      s_mag[r][c] = m; s_gx[r][c] = (short)gx; s_gy[r][c] = (short)gy;
     }
-    s_mag[ty][tx] = m;
-  }
   __syncthreads();
-  for (int i = threadIdx.x; i < GT_H * GT_W; i += 256) {
-    int ty = i / GT_W, tx = i - ty * GT_W;
-    int x = x0 + tx, y = y0 + ty;
-    if (x >= W || y >= H) continue;
-    int m = s_mag[ty + 1][tx + 1];
+  const int x = x0 + tx;
+  if (x >= W) return;
+  for (int r = ty; r < GT_H; r += 4) {
+    const int y = y0 + r;
+    if (y >= H) break;
+    const int m = s_mag[r + 1][tx + 1];
     uint8_t out = 0;
     if (m > low) {
-      int gx = s_gx[ty][tx], gy = s_gy[ty][tx];
-      long long ax = abs(gx), ay = (long long)abs(gy) << 15;
-      long long tg22 = ax * 13573, tg67 = tg22 + (ax << 16);
+      const int gx = s_gx[r + 1][tx + 1], gy = s_gy[r + 1][tx + 1];
+      // |gx|, |gy| <= 1020: y << 15 and x * 13573 + (x << 16) fit 32 bits
+      const int ax = abs(gx), ay = abs(gy) << 15;
+      const int tg22 = ax * 13573, tg67 = tg22 + (ax << 16);
       bool keep;
-      if (ay < tg22) keep = m > s_mag[ty + 1][tx] && m >= s_mag[ty + 1][tx + 2];
-      else if (ay > tg67) keep = m > s_mag[ty][tx + 1] && m >= s_mag[ty + 2][tx + 1];
+      if (ay < tg22) keep = m > s_mag[r + 1][tx] && m >= s_mag[r + 1][tx + 2];
+      else if (ay > tg67) keep = m > s_mag[r][tx + 1] && m >= s_mag[r + 2][tx + 1];
       else {
-        int s = ((gx ^ gy) < 0) ? -1 : 1;
-        keep = m > s_mag[ty][tx + 1 - s] && m > s_mag[ty + 2][tx + 1 + s];
+        const int sg = ((gx ^ gy) < 0) ? -1 : 1;
+        keep = m > s_mag[r][tx + 1 - sg] && m > s_mag[r + 2][tx + 1 + sg];
       }
       if (keep) out = m > high ? 2 : 1;
     }
@@ -154,6 +160,122 @@ __global__ void __launch_bounds__(256) k_morph(const uint8_t* __restrict__ src, 
     size_t o = base + (size_t)y * W + x;
     if (notmask) res = res && (notmask[o] == 0);
     dst[o] = res ? (uint8_t)value : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------
+// The whole morphology chain of the burr stage in ONE kernel on bit-packed rows
+// (infer_two_stage_burr.py:78-97 / infer_enhanced_burr.py:82-116):
+//   band = dilate(mask, E_band) & ~mask;  cand = edges & band;
+//   cand = erode(dilate(cand, E_close), E_close);  cand = dilate(erode(cand, E_open), E_open)
+// One thread owns a 32-pixel word: a footprint row [xa, xb] is an OR / AND of funnel shifts of
+// the 96-bit window (w-1, w, w+1), so an operator costs ~2 instructions per footprint cell per
+// 32 pixels instead of a per-pixel loop, and the five intermediate images never leave shared
+// memory (six launches with 46 MB of traffic each before).  Out-of-image samples are ignored
+// as cv2 does: forced to 0 before a dilation and to 1 before an erosion.
+// Tile = 128 x 32 pixels, halo FM_HALO rows / 32 columns: enough for 2*(open/2) + 2*(close/2)
+// + band/2 <= FM_HALO (standard 8, enhanced 18); other parameter sets take the unfused path.
+// ------------------------------------------------------------------------------
+constexpr int FM_W = 128, FM_TH = 32, FM_HALO = 20;
+constexpr int FM_WORDS = FM_W / 32 + 2, FM_ROWS = FM_TH + 2 * FM_HALO;
+struct MorphChain { Footprint band, close, open; };
+
+// 32 pixels starting at x (multiple of 32... relative to the tile) of row y -> bit i = pixel x+i non-zero; 0 outside
+// (xorv != 0: bit i = pixel != xorv's byte, e.g. 0x02020202 -> "pixel != 2")
+__device__ __forceinline__ uint32_t pack32(const uint8_t* __restrict__ img, int H, int W, int y, int x, uint32_t xorv = 0u) {
+  if (y < 0 || y >= H || x >= W || x + 32 <= 0) return 0u;
+  const uint8_t* p = img + (size_t)y * W + x;
+  uint32_t word = 0;
+  if (x >= 0 && x + 32 <= W && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p), b = *reinterpret_cast<const uint4*>(p + 16);
+    const uint32_t v[8] = {a.x ^ xorv, a.y ^ xorv, a.z ^ xorv, a.w ^ xorv, b.x ^ xorv, b.y ^ xorv, b.z ^ xorv, b.w ^ xorv};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t t = ((((v[k] & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v[k]) & 0x80808080u) >> 7;   // bit 8j = byte j non-zero
+      word |= (((t * 0x00204081u) >> 21) & 15u) << (4 * k);
+    }
+  } else {
+    for (int i = 0; i < 32; ++i)
+      if (x + i >= 0 && x + i < W && (p[i] ^ (uint8_t)xorv)) word |= 1u << i;
+  }
+  return word;
+}
+__device__ __forceinline__ uint32_t inside32(int H, int W, int y, int x) {
+  if (y < 0 || y >= H) return 0u;
+  uint32_t m = 0xffffffffu;
+  if (x < 0) m = x <= -32 ? 0u : m << (-x);
+  if (x + 32 > W) m = x >= W ? 0u : m & (0xffffffffu >> (x + 32 - W));
+  return m;
+}
+
+// out[r][w] = dilate / erode of plane `in` with footprint fp at word (r, w)
+template <bool DILATE>
+__device__ __forceinline__ uint32_t fm_apply(const uint32_t (*in)[FM_WORDS], int r, int w, const Footprint& fp) {
+  const uint32_t ident = DILATE ? 0u : 0xffffffffu;
+  uint32_t acc = ident;
+  for (int j = 0; j < fp.nrows; ++j) {
+    const int rr = r + fp.dy[j];
+    if (rr < 0 || rr >= FM_ROWS) continue;
+    const uint32_t lo = w > 0 ? in[rr][w - 1] : ident, mid = in[rr][w], hi = w + 1 < FM_WORDS ? in[rr][w + 1] : ident;
+    for (int sft = fp.xa[j]; sft <= fp.xb[j]; ++sft) {
+      const uint32_t v = sft >= 0 ? __funnelshift_r(mid, hi, sft) : __funnelshift_r(lo, mid, 32 + sft);
+      acc = DILATE ? (acc | v) : (acc & v);
+    }
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(256) k_burr_morph(const uint8_t* __restrict__ mask, const uint8_t* __restrict__ edges,
+                                                    uint8_t* __restrict__ out, int H, int W, MorphChain mc) {
+  __shared__ uint32_t s_a[FM_ROWS][FM_WORDS], s_b[FM_ROWS][FM_WORDS], s_in[FM_ROWS][FM_WORDS];
+  const int x0 = blockIdx.x * FM_W, y0 = blockIdx.y * FM_TH;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  constexpr int NW = FM_ROWS * FM_WORDS;
+  uint32_t e_bits[(NW + 255) / 256], m_bits[(NW + 255) / 256];
+  // load: s_a = mask bits, registers keep the edge / mask words of this thread's positions
+#pragma unroll
+  for (int k = 0; k < (NW + 255) / 256; ++k) {
+    const int i = threadIdx.x + k * 256;
+    if (i < NW) {
+      const int r = i / FM_WORDS, w = i - r * FM_WORDS;
+      const int y = y0 - FM_HALO + r, x = x0 - 32 + 32 * w;
+      m_bits[k] = pack32(mask + base, H, W, y, x);
+      e_bits[k] = pack32(edges + base, H, W, y, x);
+      s_a[r][w] = m_bits[k];
+      s_in[r][w] = inside32(H, W, y, x);
+    }
+  }
+  __syncthreads();
+  // cand = edges & dilate(mask, band) & ~mask                          -> s_b
+#pragma unroll
+  for (int k = 0; k < (NW + 255) / 256; ++k) {
+    const int i = threadIdx.x + k * 256;
+    if (i < NW) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<true>(s_a, r, w, mc.band) & ~m_bits[k] & e_bits[k]; }
+  }
+  __syncthreads();
+  // CLOSE: dilate -> s_a (forced to 1 outside the image for the erosion that follows), erode -> s_b
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<true>(s_b, r, w, mc.close) | ~s_in[r][w]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<false>(s_a, r, w, mc.close) | ~s_in[r][w]; }
+  __syncthreads();
+  // OPEN: erode -> s_a (forced to 0 outside for the dilation), dilate -> output
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<false>(s_b, r, w, mc.open) & s_in[r][w]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < FM_TH * (FM_W / 32); i += 256) {
+    const int ty = i / (FM_W / 32), tw = i - ty * (FM_W / 32);
+    const int y = y0 + ty, x = x0 + 32 * tw;
+    if (y >= H || x >= W) continue;
+    const uint32_t word = fm_apply<true>(s_a, ty + FM_HALO, tw + 1, mc.open);
+    uint8_t* o = out + base + (size_t)y * W + x;
+    if (x + 32 <= W && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      uint32_t v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = (((word >> (4 * k)) & 15u) * 0x00204081u) & 0x01010101u;
+      *reinterpret_cast<uint4*>(o) = make_uint4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<uint4*>(o + 16) = make_uint4(v[4], v[5], v[6], v[7]);
+    } else {
+      for (int k = 0; k < 32 && x + k < W; ++k) o[k] = (word >> k) & 1u;
+    }
   }
 }
 
