@@ -96,7 +96,22 @@ def make_frames(batch, seed):
     return np.concatenate(parts)
 
 
-def cpu_reference_fps(frames, sd, n_frames, warm=1):
+def ref_step(R, frame, sd, workload):
+    """One iteration of the reference loop body for the workload (oracle/ref_pipeline.py)."""
+    if workload == "enhanced":        # BASELINE config 4: rotate + resize + enhance_image + multi-scale detector
+        fr = R.normalize_frame(frame, rotate=True, size=(FRAME_HW[1], FRAME_HW[0]))
+        return R.frame_step(fr, sd, variant="enhanced", do_enhance=True)
+    return R.frame_step(frame, sd, "medium")
+
+
+def make_workload_frames(workload, batch, seed):
+    if workload == "enhanced":
+        import unet_b200.synth as S
+        return S.frames_cable(batch, 1080, 1920, seed=seed)        # SURVEY 8(d) `hires`
+    return make_frames(batch, seed)
+
+
+def cpu_reference_fps(frames, sd, n_frames, warm=1, workload="two_stage"):
     """Times the oracle restatement of the reference loop body (torch CPU + OpenCV, the same
     library calls the reference makes) on the host cores.  Checker-side code: only the
     cpu_baseline / --impl reference legs run it."""
@@ -107,10 +122,10 @@ def cpu_reference_fps(frames, sd, n_frames, warm=1):
     torch.set_num_threads(cores)
     cv2.setNumThreads(cores)
     for i in range(warm):
-        R.frame_step(frames[i % len(frames)], sd, "medium")
+        ref_step(R, frames[i % len(frames)], sd, workload)
     t0 = time.perf_counter()
     for i in range(n_frames):
-        R.frame_step(frames[i % len(frames)], sd, "medium")
+        ref_step(R, frames[i % len(frames)], sd, workload)
     dt = time.perf_counter() - t0
     return n_frames / dt, cores, dt
 
@@ -123,7 +138,7 @@ def run_reference(args):
     import unet_b200.synth as S
     sd = S.make_state_dict(0)
     per_step = args.ref_frames_per_step
-    frames = make_frames(max(per_step, 3), seed=0)
+    frames = make_workload_frames(args.workload, max(per_step, 3), seed=0)
     import cv2
     import torch
     from oracle import ref_pipeline as R
@@ -133,22 +148,28 @@ def run_reference(args):
     k = 0
     for _ in range(args.warmup):
         for _ in range(per_step):
-            R.frame_step(frames[k % len(frames)], sd, "medium"); k += 1
+            ref_step(R, frames[k % len(frames)], sd, args.workload); k += 1
     t0 = time.perf_counter()
     for _ in range(args.steps):
         for _ in range(per_step):
-            R.frame_step(frames[k % len(frames)], sd, "medium"); k += 1
+            ref_step(R, frames[k % len(frames)], sd, args.workload); k += 1
     dt = time.perf_counter() - t0
     fps = args.steps * per_step / dt
     sample = f"{per_step} frames/step of the {args.batch}-frame batch, batch 1, fp32, torch {torch.__version__} + cv2 {cv2.__version__}"
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"two_stage_pipeline_800x448_batch{args.batch}", "frame": "800x448", "net": "512x512",
+            "config": {"workload": workload_name(args.workload, args.batch), "frame": "800x448", "net": "512x512",
                        "batch_per_gpu": args.batch},
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def workload_name(workload, batch):
+    if workload == "enhanced":
+        return f"enhanced_pipeline_1080p_rotate_resize_enhance_800x448_batch{batch}"
+    return f"two_stage_pipeline_800x448_batch{batch}"
 
 
 def run_ours(args):
@@ -166,10 +187,12 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
     sd = S.make_state_dict(0)
-    pipe = InspectionPipeline(sd, batch=B, frame_hw=FRAME_HW, net_hw=NET_HW, device=local)
+    enhanced = args.workload == "enhanced"
+    pipe = InspectionPipeline(sd, batch=B, frame_hw=FRAME_HW, net_hw=NET_HW, device=local,
+                              variant="enhanced" if enhanced else "standard", enhance=enhanced)
     # every rank owns a contiguous block of the global frame index space (weak scaling)
     lo, _ = shard_range(B * world, rank, world)
-    frames_np = make_frames(B, seed=rank)
+    frames_np = make_workload_frames(args.workload, B, seed=rank)
     frames_host = torch.from_numpy(frames_np).pin_memory()
     frames_dev = frames_host.cuda()
     stats_host = torch.empty((B, 4), dtype=torch.int32).pin_memory()
@@ -179,11 +202,23 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_dev():
-        stats, _ = pipe.run(frames_dev)
+    def step_dev(src=None):
+        f = frames_dev if src is None else src
+        if enhanced:      # 1080p source: rotate 90 degrees CCW + resize to 800x448 (infer_enhanced_burr.py:273-276)
+            f = pipe.ctx.normalize_frames(f, (FRAME_HW[1], FRAME_HW[0]), rotate=True)
+        stats, _ = pipe.run(f)
         if world > 1:
             return InspectionPipeline.gather_stats(stats, lo)
         return stats
+
+    def step_host():
+        if enhanced:      # host frames in, host statistics out; copies on the compute stream inside the timed region
+            out = step_dev(frames_host.cuda(non_blocking=True))
+            stats_host.copy_(out[:B] if world == 1 else out[lo:lo + B])
+            return
+        pipe.run_host(frames_host, stats_host)
+        if world > 1:
+            InspectionPipeline.gather_stats(stats_host.cuda(non_blocking=True), lo)
 
     for _ in range(args.warmup):
         out = step_dev()
@@ -210,13 +245,11 @@ def run_ours(args):
 
     # end to end through the host entry point (H2D + compute + D2H inside the timed region)
     for _ in range(max(1, args.warmup // 2)):
-        pipe.run_host(frames_host, stats_host)
+        step_host()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        pipe.run_host(frames_host, stats_host)
-        if world > 1:
-            InspectionPipeline.gather_stats(stats_host.cuda(non_blocking=True), lo)
+        step_host()
     barrier()
     e2e_s = time.perf_counter() - t0
 
@@ -238,7 +271,7 @@ def run_ours(args):
         line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-                "config": {"workload": f"two_stage_pipeline_800x448_batch{B}", "frame": "800x448", "net": "512x512",
+                "config": {"workload": workload_name(args.workload, B), "frame": "800x448", "net": "512x512",
                            "batch_per_gpu": B, "parallelism": f"frames sharded over {world} GPU(s)",
                            "l2": "activation working set ~12 GB/step per GPU >> 126 MB L2; no explicit flush"},
                 "e2e": {"value": B * world * args.steps / (e2e_ms / 1e3), "unit": "frames/s",
@@ -246,7 +279,7 @@ def run_ours(args):
                 "gpu_launches": int(launches), "roofline": roof, "clocks": clocks,
                 "checks": {"burr_frames": summary["burr_frames"], "frames": summary["frames"]}}
         if world == 1 and not args.no_cpu_baseline:
-            fps_cpu, cores, dt = cpu_reference_fps(frames_np, sd, args.cpu_frames)
+            fps_cpu, cores, dt = cpu_reference_fps(frames_np, sd, args.cpu_frames, workload=args.workload)
             line["cpu_baseline"] = {"value": fps_cpu, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{args.cpu_frames} frames of the same batch, batch 1, fp32 ({dt:.1f} s)"}
         print(json.dumps(line), flush=True)
@@ -264,7 +297,11 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=24)
     ap.add_argument("--ref-frames-per-step", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="two_stage", choices=["two_stage", "enhanced"],
+                    help="two_stage: BASELINE metric config (default); enhanced: config 4 (1080p rotate+resize, enhance_image, multi-scale detector)")
     args = ap.parse_args()
+    if args.workload == "enhanced" and args.batch == 64:
+        args.batch = 16
     if args.impl == "reference":
         run_reference(args)
     else:
