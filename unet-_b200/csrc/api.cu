@@ -122,6 +122,9 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   if (r) return fail(r);
   if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK || (r = enhance_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
   *out = c;
   return UB_OK;
@@ -144,6 +147,9 @@ void ub_destroy(ub_ctx* c) {
   for (auto& r : c->tm.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (auto& e : c->tm.pool) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
 
@@ -392,10 +398,21 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
   ub_burr_params p = params ? *params : default_params(variant);
   const size_t fpix = (size_t)H * W;
   uint8_t *cable = ctx->d_mask[0], *tape = ctx->d_mask[1], *burr = ctx->d_mask[2];
-  RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, nullptr, nullptr, ctx->d_gray, st));          // gray only
+  // The gray frame and the edge map depend on the frames only: they run on a second stream beside the network
+  // (fork / join with events; the integer kernels fill the SMs the tensor-core kernels leave idle at their tails).
+  static const int overlap_env = getenv("UB_OVERLAP") ? atoi(getenv("UB_OVERLAP")) : 1;
+  cudaStream_t sa = overlap_env ? ctx->aux_stream : st;
+  if (overlap_env) {
+    UB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
+    UB_CUDA(ctx, cudaStreamWaitEvent(sa, ctx->ev_fork, 0));
+  }
+  RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, nullptr, nullptr, ctx->d_gray, sa));          // gray only
+  RUN(burr_edges(ctx, variant, ctx->d_gray, B, H, W, p, sa));
+  if (overlap_env) UB_CUDA(ctx, cudaEventRecord(ctx->ev_join, sa));
   RUN(net_forward_pp(ctx, B, nh, nw, nullptr, frames, H, W, nullptr, ctx->d_pred, st));               // preprocess fused per sub-batch
   RUN(masks_from_pred(ctx, ctx->d_pred, B, nh, nw, H, W, r, cable, tape, frame_stats, st));
-  RUN(burr_stage(ctx, variant, ctx->d_gray, cable, B, H, W, p, burr, frame_stats + 3, 4, st));
+  if (overlap_env) UB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join, 0));
+  RUN(burr_finish(ctx, cable, B, H, W, p, burr, frame_stats + 3, 4, st));
   if (masks) {
     for (int k = 0; k < 3; ++k)
       UB_CUDA(ctx, cudaMemcpy2DAsync(masks + k * fpix, 3 * fpix, ctx->d_mask[k], fpix, fpix, B, cudaMemcpyDeviceToDevice, st));

@@ -131,6 +131,8 @@ struct ub_ctx {
   void* enh_host = nullptr;          // enhance.cu lookup tables (EnhTables*), host copy
   void* d_enh = nullptr;             // ... and device copy
   cudaStream_t own_stream = nullptr;
+  cudaStream_t aux_stream = nullptr;   // ub_pipeline: gray + edge map run here beside the network
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Timing tm;
 };
 
@@ -207,5 +209,8 @@ int sharpen3(ub_ctx*, const uint8_t* src, uint8_t* dst, int B, int H, int W, cud
 int enhance_frames(ub_ctx*, const uint8_t* frames, uint8_t* out, int B, int H, int W, cudaStream_t);
 
 // stage2.cu
+int burr_edges(ub_ctx*, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& p, cudaStream_t);
+int burr_finish(ub_ctx*, const uint8_t* mask, int B, int H, int W, const ub_burr_params& p, uint8_t* burr,
+                int32_t* burr_px, int px_stride, cudaStream_t);
 int burr_stage(ub_ctx*, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
                const ub_burr_params& p, uint8_t* burr, int32_t* burr_px, int px_stride, cudaStream_t);

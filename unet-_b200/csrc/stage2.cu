@@ -567,17 +567,31 @@ int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels
   return UB_OK;
 }
 
+// First half of the burr stage: the edge map, which depends on the gray frame only (not on the net's masks), so
+// ub_pipeline runs it on a second stream beside the network.  Result in ctx->d_tmp[1].
+int burr_edges(ub_ctx* ctx, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& P, cudaStream_t st) {
+  uint8_t *t0 = ctx->d_tmp[0], *t1 = ctx->d_tmp[1], *t2 = ctx->d_tmp[2];
+  // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
+  RUN(gaussian5(ctx, gray, t0, B, H, W, st));
+  RUN(canny(ctx, t0, t1, t2, ctx->d_lab[0], B, H, W, P.canny_low, P.canny_high, st));
+  if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
+  return UB_OK;
+}
+
 // The whole burr stage for a batch.
 int burr_stage(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
                const ub_burr_params& P, uint8_t* burr, int32_t* burr_px, int px_stride, cudaStream_t st) {
+  RUN(burr_edges(ctx, variant, gray, B, H, W, P, st));
+  return burr_finish(ctx, mask, B, H, W, P, burr, burr_px, px_stride, st);
+}
+
+// Second half: detection band, candidates, CLOSE / OPEN, components, filter (edges in ctx->d_tmp[1]).
+int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_burr_params& P, uint8_t* burr,
+                int32_t* burr_px, int px_stride, cudaStream_t st) {
   uint8_t *t0 = ctx->d_tmp[0], *t1 = ctx->d_tmp[1], *t2 = ctx->d_tmp[2], *t3 = ctx->d_tmp[3];
   int* lab = ctx->d_lab[0];
   const size_t n = (size_t)B * H * W;
   const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
-  // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
-  RUN(gaussian5(ctx, gray, t0, B, H, W, st));
-  RUN(canny(ctx, t0, t1, t2, lab, B, H, W, P.canny_low, P.canny_high, st));
-  if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
   static const int fuse_env = getenv("UB_MORPH_FUSED") ? atoi(getenv("UB_MORPH_FUSED")) : 1;
   MorphChain mc;
   const bool fp_ok = make_footprint(P.band_k, mc.band) && make_footprint(P.close_k, mc.close) && make_footprint(P.open_k, mc.open);
