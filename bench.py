@@ -8,8 +8,9 @@
 A "step" is one pass of the whole two-stage pipeline (preprocess -> NestedUNet 512x512 ->
 argmax/masks/ROI -> gray -> burr stage -> per-frame counts) over one batch of synthetic
 800x448 frames.  `value` is measured with the frames already resident in HBM; `e2e` is the
-same step through the C-ABI host entry point (ub_pipeline_host) with pinned HOST frames in and
-HOST statistics out, copies inside the timed region.  One JSON line is printed by rank 0.
+same steps through the C-ABI host entry points (ub_pipeline_submit / ub_pipeline_wait, two batches
+in flight) with pinned HOST frames in and HOST statistics out, every step's copies inside the
+timed region.  One JSON line is printed by rank 0.
 """
 from __future__ import annotations
 
@@ -244,12 +245,21 @@ def run_ours(args):
     summary = pipe.summary(out)
 
     # end to end through the host entry point (H2D + compute + D2H inside the timed region)
-    for _ in range(max(1, args.warmup // 2)):
-        step_host()
+    def run_host_steps(n):
+        if enhanced:
+            for _ in range(n):
+                step_host()
+            return
+        # the streaming host entry points (ub_pipeline_submit / _wait): every step copies its own frames host->device
+        # and its statistics device->host; the copy of step i+1 overlaps the compute of step i
+        for st_h in pipe.stream_host(frames_host for _ in range(n)):
+            if world > 1:
+                InspectionPipeline.gather_stats(st_h.cuda(non_blocking=True), lo)
+
+    run_host_steps(max(2, args.warmup // 2))
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_host()
+    run_host_steps(args.steps)
     barrier()
     e2e_s = time.perf_counter() - t0
 

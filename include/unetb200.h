@@ -160,6 +160,15 @@ int ub_pipeline_host(ub_ctx* ctx, const uint8_t* frames_bgr_host, int B, int var
                      const ub_roi* roi, const ub_burr_params* params,
                      int32_t* frame_stats_host, uint8_t* masks_host);
 
+/* Streaming form for a loop over batches (the while-loop of infer_two_stage_burr.py:268-361 with the frames
+ * arriving from the host): ub_pipeline_submit enqueues the host->device copy, the step and the copy of the
+ * statistics into stats_host for `slot` (0 or 1) and returns; ub_pipeline_wait blocks until that slot's
+ * statistics have arrived.  Submitting batch i+1 before waiting for batch i overlaps its copy with the
+ * compute of batch i.  frames_host / stats_host must stay valid (and should be pinned) until the wait. */
+int ub_pipeline_submit(ub_ctx* ctx, const uint8_t* frames_bgr_host, int B, int variant,
+                       const ub_roi* roi, const ub_burr_params* params, int32_t* frame_stats_host, int slot);
+int ub_pipeline_wait(ub_ctx* ctx, int slot);
+
 /* ---- test hooks (layer-level parity checks; not used by the product path) ------------ */
 /* Runs conv layer `layer` (0..17 in network order; BN folded, ReLU) on NCHW fp32 inputs:
  * x0 [B,cin0,H,W] (layer 0: 3 channels), x1 [B,cin1,H,W] or NULL -> out [B,cout,H,W]. */

@@ -142,6 +142,29 @@ def test_forward_on_frames(sd):
     assert rel <= LOGIT_REL_TOL and agree >= ARGMAX_MIN_AGREE
 
 
+def test_streaming_host_api_matches_blocking(sd):
+    """ub_pipeline_submit / ub_pipeline_wait (two batches in flight) give the statistics of ub_pipeline_host."""
+    from unet_b200 import _lib
+    from unet_b200.pipeline import InspectionPipeline
+    pipe = InspectionPipeline(sd, batch=3)
+    batches = [torch.from_numpy(np.concatenate([S.frames_cable(2, 448, 800, seed=30 + i), S.frames_speckle(1, 448, 800, seed=40 + i)])).pin_memory()
+               for i in range(4)]
+    batches.append(torch.from_numpy(S.frames_cable(2, 448, 800, seed=50)).pin_memory())          # ragged last batch
+    want = [pipe.run_host(b).numpy().copy() for b in batches]
+    got = [s.numpy() for s in pipe.stream_host(iter(batches))]
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    with pytest.raises(_lib.UbError):
+        pipe.ctx.pipeline_wait(0)                                    # nothing in flight
+    st = torch.empty((3, 4), dtype=torch.int32).pin_memory()
+    pipe.ctx.pipeline_submit(batches[0], st, 0, pipe.variant, pipe.roi, pipe.params)
+    with pytest.raises(_lib.UbError):
+        pipe.ctx.pipeline_submit(batches[1], st, 0, pipe.variant, pipe.roi, pipe.params)   # slot busy
+    pipe.ctx.pipeline_wait(0)
+    assert np.array_equal(st.numpy(), want[0])
+
+
 def test_module_contract(sd, golden_net):
     from unet_b200 import NestedUNet
     m = NestedUNet(num_classes=3, deep_supervision=True, pretrained_encoder=False).to("cuda")

@@ -68,6 +68,8 @@ SIGNATURES = {
     "ub_enhance": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_pipeline": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P, _P]),
     "ub_pipeline_host": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P]),
+    "ub_pipeline_submit": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _I]),
+    "ub_pipeline_wait": (_I, [_P, _I]),
     "ub_debug_conv": (_I, [_P, _I, _P, _P, _I, _I, _I, _P, _P]),
     "ub_debug_activation": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_timing_enable": (_I, [_P, _I]),
@@ -314,6 +316,15 @@ class Context:
         p = C.byref(params) if params is not None else None
         self._check(lib().ub_pipeline_host(self._h, _ptr(frames), b, variant, r, p, _ptr(stats_out), _ptr(masks_out)))
         return stats_out
+
+    def pipeline_submit(self, frames, stats_out, slot, variant=VARIANT_STANDARD, roi=None, params=None):
+        """Asynchronous pipeline_host into `slot` (0/1); frames / stats_out must be pinned and stay alive until pipeline_wait."""
+        r = C.byref(Roi(*roi)) if roi is not None else None
+        p = C.byref(params) if params is not None else None
+        self._check(lib().ub_pipeline_submit(self._h, _ptr(frames), frames.shape[0], variant, r, p, _ptr(stats_out), slot))
+
+    def pipeline_wait(self, slot):
+        self._check(lib().ub_pipeline_wait(self._h, slot))
 
     # -- test hooks
     def debug_conv(self, layer, x0, x1, cout):

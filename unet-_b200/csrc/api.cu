@@ -114,7 +114,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   const size_t ipl = (size_t)max_batch * (frame_h + 1) * (frame_w + 1);
   if ((r = dmalloc(c, &c->d_frames, fpix * 3)) || (r = dmalloc(c, &c->d_gray, fpix)) || (r = dmalloc(c, &c->d_pred, npix)) ||
       (r = dmalloc(c, &c->d_lab[0], ipl)) || (r = dmalloc(c, &c->d_lab[1], ipl)) || (r = dmalloc(c, &c->d_comp, fpix * 6)) ||
-      (r = dmalloc(c, &c->d_counts, (size_t)max_batch * 16)) || (r = dmalloc(c, &c->d_stats, (size_t)max_batch * 4)) ||
+      (r = dmalloc(c, &c->d_counts, (size_t)max_batch * 16)) || (r = dmalloc(c, &c->d_stats, (size_t)max_batch * 8)) ||
       (r = dmalloc(c, &c->d_logits, npix * num_classes)))
     return fail(r);
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
@@ -123,6 +123,11 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK || (r = enhance_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+  }
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
   if (e != cudaSuccess) { ub_fail(nullptr, UB_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); return fail(UB_ERR_CUDA); }
@@ -148,6 +153,9 @@ void ub_destroy(ub_ctx* c) {
   for (auto& e : c->tm.pool) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  for (int i = 0; i < 2; ++i) { if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]); if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]); }
+  cudaFree(c->d_frames2);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
@@ -436,6 +444,45 @@ int ub_pipeline_host(ub_ctx* ctx, const uint8_t* frames_host, int B, int variant
       UB_CUDA(ctx, cudaMemcpy2DAsync(masks_host + k * fpix, 3 * fpix, ctx->d_mask[k], fpix, fpix, B, cudaMemcpyDeviceToHost, st));
   }
   UB_CUDA(ctx, cudaStreamSynchronize(st));
+  return UB_OK;
+}
+
+// Streaming form of ub_pipeline_host.  submit(slot) enqueues: H2D copy of the frames on the copy stream (as soon as the
+// slot's previous batch has been consumed), the whole step on the compute stream, D2H copy of the statistics; wait(slot)
+// blocks until that batch's statistics are in stats_host.  With two slots in flight (submit i+1, then wait i) the copy of
+// the next batch overlaps the compute of the current one -- how a video loop feeds the device.
+int ub_pipeline_submit(ub_ctx* ctx, const uint8_t* frames_host, int B, int variant, const ub_roi* roi,
+                       const ub_burr_params* params, int32_t* stats_host, int slot) {
+  NEED_CTX(ctx);
+  if (!frames_host || !stats_host) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (slot < 0 || slot > 1) return ub_fail(ctx, UB_ERR_ARG, "slot %d (0 or 1)", slot);
+  if (B < 1 || B > ctx->max_batch) return ub_fail(ctx, UB_ERR_ARG, "batch %d outside [1,%d]", B, ctx->max_batch);
+  if (ctx->slot_batch[slot]) return ub_fail(ctx, UB_ERR_STATE, "slot %d is still in flight: call ub_pipeline_wait first", slot);
+  const size_t fbytes = (size_t)ctx->frame_h * ctx->frame_w * 3;
+  if (slot == 1 && !ctx->d_frames2) {
+    cudaError_t e = cudaMalloc(&ctx->d_frames2, fbytes * ctx->max_batch);
+    if (e != cudaSuccess) return ub_fail(ctx, UB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", fbytes * ctx->max_batch, cudaGetErrorString(e));
+  }
+  uint8_t* d_fr = slot ? ctx->d_frames2 : ctx->d_frames;
+  int32_t* d_st = ctx->d_stats + (size_t)slot * ctx->max_batch * 4;
+  // the slot's frame buffer was last read by its previous batch, whose completion ub_pipeline_wait has observed
+  UB_CUDA(ctx, cudaMemcpyAsync(d_fr, frames_host, fbytes * B, cudaMemcpyHostToDevice, ctx->copy_stream));
+  UB_CUDA(ctx, cudaEventRecord(ctx->ev_h2d[slot], ctx->copy_stream));
+  cudaStream_t st = ctx->own_stream;
+  UB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_h2d[slot], 0));
+  RUN(ub_pipeline(ctx, d_fr, B, variant, roi, params, d_st, nullptr, st));
+  UB_CUDA(ctx, cudaMemcpyAsync(stats_host, d_st, sizeof(int32_t) * 4 * B, cudaMemcpyDeviceToHost, st));
+  UB_CUDA(ctx, cudaEventRecord(ctx->ev_done[slot], st));
+  ctx->slot_batch[slot] = B;
+  return UB_OK;
+}
+
+int ub_pipeline_wait(ub_ctx* ctx, int slot) {
+  NEED_CTX(ctx);
+  if (slot < 0 || slot > 1) return ub_fail(ctx, UB_ERR_ARG, "slot %d (0 or 1)", slot);
+  if (!ctx->slot_batch[slot]) return ub_fail(ctx, UB_ERR_STATE, "slot %d has nothing in flight", slot);
+  UB_CUDA(ctx, cudaEventSynchronize(ctx->ev_done[slot]));
+  ctx->slot_batch[slot] = 0;
   return UB_OK;
 }
 

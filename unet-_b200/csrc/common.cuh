@@ -131,6 +131,11 @@ struct ub_ctx {
   void* enh_host = nullptr;          // enhance.cu lookup tables (EnhTables*), host copy
   void* d_enh = nullptr;             // ... and device copy
   cudaStream_t own_stream = nullptr;
+  // ub_pipeline_submit / _wait: two slots so the H2D copy of batch i+1 (copy_stream) overlaps the compute of batch i
+  uint8_t* d_frames2 = nullptr;        // frames of slot 1 (slot 0 uses d_frames), allocated at the first submit
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+  int slot_batch[2] = {0, 0};
   cudaStream_t aux_stream = nullptr;   // ub_pipeline: gray + edge map run here beside the network
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Timing tm;

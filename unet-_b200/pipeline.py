@@ -69,6 +69,26 @@ class InspectionPipeline:
             self.ctx.pipeline_host(frames_host, stats_host, self.variant, self.roi, self.params, masks_host)
         return stats_host
 
+    def stream_host(self, batches):
+        """Generator over an iterable of pinned host uint8 [b,H,W,3] batches -> int32 [b,4] host statistics per batch,
+        in order.  Two batches are in flight: the host->device copy of batch i+1 overlaps the compute of batch i
+        (ub_pipeline_submit / ub_pipeline_wait)."""
+        stats = [torch.empty((self.batch, 4), dtype=torch.int32).pin_memory() for _ in range(2)]
+        pending = None                                   # (slot, frames kept alive, n)
+        i = 0
+        with torch.cuda.device(self.device):
+            for frames in batches:
+                slot = i & 1
+                self.ctx.pipeline_submit(frames, stats[slot], slot, self.variant, self.roi, self.params)
+                if pending is not None:
+                    self.ctx.pipeline_wait(pending[0])
+                    yield stats[pending[0]][: pending[2]].clone()
+                pending = (slot, frames, frames.shape[0])
+                i += 1
+            if pending is not None:
+                self.ctx.pipeline_wait(pending[0])
+                yield stats[pending[0]][: pending[2]].clone()
+
     @staticmethod
     def gather_stats(stats: torch.Tensor, frame_offset: int, group=None) -> torch.Tensor:
         """All-gather per-frame statistics across ranks (NCCL on GPU tensors, gloo on CPU
