@@ -209,7 +209,7 @@ def run_ours(args):
             f = pipe.ctx.normalize_frames(f, (FRAME_HW[1], FRAME_HW[0]), rotate=True)
         stats, _ = pipe.run(f)
         if world > 1:
-            return InspectionPipeline.gather_stats(stats, lo)
+            return InspectionPipeline.gather_stats(stats, lo, equal_counts=True)
         return stats
 
     def step_host():
@@ -219,7 +219,7 @@ def run_ours(args):
             return
         pipe.run_host(frames_host, stats_host)
         if world > 1:
-            InspectionPipeline.gather_stats(stats_host.cuda(non_blocking=True), lo)
+            InspectionPipeline.gather_stats(stats_host.cuda(non_blocking=True), lo, equal_counts=True)
 
     for _ in range(args.warmup):
         out = step_dev()
@@ -254,7 +254,7 @@ def run_ours(args):
         # and its statistics device->host; the copy of step i+1 overlaps the compute of step i
         for st_h in pipe.stream_host(frames_host for _ in range(n)):
             if world > 1:
-                InspectionPipeline.gather_stats(st_h.cuda(non_blocking=True), lo)
+                InspectionPipeline.gather_stats(st_h.cuda(non_blocking=True), lo, equal_counts=True)
 
     run_host_steps(max(2, args.warmup // 2))
     barrier()

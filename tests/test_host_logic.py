@@ -100,6 +100,13 @@ local = torch.stack([torch.arange(b - a, dtype=torch.int32), torch.arange(a, b, 
 out = InspectionPipeline.gather_stats(local, a)
 want = torch.stack([torch.arange(n), torch.arange(n) * 10, torch.arange(n) * 100, torch.arange(n) % 3], 1).int()
 assert torch.equal(out, want), (rank, out)
+# equal shares: one collective, no size exchange
+m = 6
+loc = torch.stack([torch.arange(m, dtype=torch.int32), torch.full((m,), rank, dtype=torch.int32),
+                   torch.arange(m, dtype=torch.int32) + 7, torch.zeros(m, dtype=torch.int32)], 1)
+out = InspectionPipeline.gather_stats(loc, rank * m, equal_counts=True)
+assert out.shape == (world * m, 4) and out[:, 0].tolist() == list(range(world * m))
+assert out[:, 1].tolist() == [r for r in range(world) for _ in range(m)]
 dist.destroy_process_group()
 print("ok", rank)
 """

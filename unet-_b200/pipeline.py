@@ -90,15 +90,21 @@ class InspectionPipeline:
                 yield stats[pending[0]][: pending[2]].clone()
 
     @staticmethod
-    def gather_stats(stats: torch.Tensor, frame_offset: int, group=None) -> torch.Tensor:
+    def gather_stats(stats: torch.Tensor, frame_offset: int, group=None, equal_counts: bool = False) -> torch.Tensor:
         """All-gather per-frame statistics across ranks (NCCL on GPU tensors, gloo on CPU
-        tensors).  Column 0 becomes the global frame index.  Returns [sum B_r, 4] sorted by frame."""
+        tensors).  Column 0 becomes the global frame index.  Returns [sum B_r, 4] sorted by frame.
+        equal_counts=True (every rank holds the same number of frames, offsets ascending with the rank)
+        skips the size exchange and the sort: one collective, no host synchronisation."""
         import torch.distributed as dist
         s = stats.clone()
         s[:, 0] += frame_offset
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return s
         world = dist.get_world_size(group)
+        if equal_counts:
+            out = torch.empty((world * s.shape[0], 4), dtype=s.dtype, device=s.device)
+            dist.all_gather_into_tensor(out, s, group=group)
+            return out
         n = torch.tensor([s.shape[0]], dtype=torch.int64, device=s.device)
         sizes = [torch.zeros_like(n) for _ in range(world)]
         dist.all_gather(sizes, n, group=group)
