@@ -39,12 +39,21 @@ struct TcParams {
 
 template <int BN, int KC, bool SHIFT_A>
 struct Cfg {
+  static constexpr int KYS = BN >= 256 ? 1 : 3;                          // kernel rows per pipeline stage
   static constexpr int CPK = KC / 8;                                   // chunks per k-block
   static constexpr int A_SEGS = SHIFT_A ? 3 : 9;
   static constexpr int A_SEG_BYTES = SHIFT_A ? SEG_BYTES : TILE_M * 16;  // per chunk
-  static constexpr int A_STAGE = A_SEGS * CPK * A_SEG_BYTES;
   static constexpr int B_TAP = KC * BN * 2;
-  static constexpr int B_STAGE = 9 * B_TAP;
+  static constexpr int B_KB = 9 * B_TAP;                                 // weights of one k-block (all taps)
+  // One pipeline stage = KYS kernel rows of one k-block: their activation segment(s) and taps of weights.  N = 256:
+  // one row per stage -- with whole k-blocks only two 87 KB stages fit and the tensor pipe waited for the refill of
+  // the other one; 7 stages of 29 KB hide it better (250 -> 238 us per 309-GFLOP layer).  N <= 128: whole k-blocks --
+  // the three MMAs of one row (~230 clk) are shorter than the producer lane's three bulk-copy issues (~100 clk each),
+  // so row-sized stages made those layers producer-bound (253 -> 422 us).
+  static constexpr int A_KY = (A_SEGS / 3) * CPK * A_SEG_BYTES;          // one kernel row
+  static constexpr int B_KY = 3 * B_TAP;
+  static constexpr int A_STAGE = KYS * A_KY;
+  static constexpr int B_STAGE = KYS * B_KY;
   static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;        // power of two for BN in {32..256}
   static constexpr int HDR = 2048;                                     // barriers + head weights
 };
@@ -123,34 +132,44 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
         const int p0 = L.G + mt * TILE_M;
         const bool load_b = !P.b_resident || first;
         for (int kb = 0; kb < P.kbn; ++kb) {
-          const uint32_t full = bar_full + 8 * s;
-          mbar_wait(bar_empty + 8 * s, ph ^ 1);
-          mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
           const act_t* plane0 =
               kb < P.kb0 ? P.src0 + ((size_t)b * P.nch0 + (size_t)kb * C::CPK) * L.Ppl * 8
                          : P.src1 + ((size_t)b * P.nch1 + (size_t)(kb - P.kb0) * C::CPK) * L.Ppl * 8;
-          const uint32_t a_st = a_base + s * C::A_STAGE;
+          const act_t* wsrc_kb = P.w + ((size_t)nt * P.kbn + kb) * 9 * (size_t)(KC * BN);
+#pragma unroll 1
+          for (int ky0 = 0; ky0 < 3; ky0 += C::KYS) {
+            const uint32_t full = bar_full + 8 * s;
+            mbar_wait(bar_empty + 8 * s, ph ^ 1);
+            mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
+            const uint32_t a_st = a_base + s * C::A_STAGE;
 #pragma unroll
-          for (int seg = 0; seg < C::A_SEGS; ++seg) {
-            const int off = SHIFT_A ? (seg - 1) * L.pitch - 1 : (seg / 3 - 1) * L.pitch + (seg % 3 - 1);
+            for (int kyi = 0; kyi < C::KYS; ++kyi)
 #pragma unroll
-            for (int cc = 0; cc < C::CPK; ++cc)
-              bulk_g2s(a_st + (seg * C::CPK + cc) * C::A_SEG_BYTES, plane0 + ((size_t)cc * L.Ppl + p0 + off) * 8, C::A_SEG_BYTES, full);
+              for (int sg = 0; sg < C::A_SEGS / 3; ++sg) {
+                const int ky = ky0 + kyi;
+                const int off = SHIFT_A ? (ky - 1) * L.pitch - 1 : (ky - 1) * L.pitch + (sg - 1);
+#pragma unroll
+                for (int cc = 0; cc < C::CPK; ++cc)
+                  bulk_g2s(a_st + kyi * C::A_KY + (sg * C::CPK + cc) * C::A_SEG_BYTES, plane0 + ((size_t)cc * L.Ppl + p0 + off) * 8,
+                           C::A_SEG_BYTES, full);
+              }
+            if (load_b) {
+              const act_t* wsrc = wsrc_kb + (size_t)ky0 * 3 * (KC * BN);
+              const uint32_t wdst = b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
+              if (PAIR) bulk_g2s_mcast(wdst + cta_rank * (C::B_STAGE / 2), wsrc + cta_rank * (C::B_STAGE / 4), C::B_STAGE / 2, full, 3);
+              else bulk_g2s(wdst, wsrc, C::B_STAGE, full);
+            }
+            if (++s == S) { s = 0; ph ^= 1; }
           }
-          if (load_b) {
-            const act_t* wsrc = P.w + ((size_t)nt * P.kbn + kb) * 9 * (size_t)(KC * BN);
-            const uint32_t wdst = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
-            if (PAIR) bulk_g2s_mcast(wdst + cta_rank * (C::B_STAGE / 2), wsrc + cta_rank * (C::B_STAGE / 4), C::B_STAGE / 2, full, 3);
-            else bulk_g2s(wdst, wsrc, C::B_STAGE, full);
-          }
-          if (++s == S) { s = 0; ph ^= 1; }
         }
         first = false;
       }
     }
   } else if (warp == 5) {
-    // ===================== MMA issuer (single thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues =====================
+    // (under a plain `lane == 0` branch every UTCHMMA is wrapped in an elect-and-branch loop of ~16 dependent
+    //  uniform-datapath instructions, and this warp paces the tensor pipe)
+    {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)(TILE_M >> 4) << 24);
       int s = 0; uint32_t ph = 0;
@@ -161,26 +180,33 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
         for (int kb = 0; kb < P.kbn; ++kb) {
-          mbar_wait(bar_full + 8 * s, ph);
-          tc_fence_after();
-          const uint32_t a_st = a_base + s * C::A_STAGE;
-          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+#pragma unroll 1
+          for (int ky0 = 0; ky0 < 3; ky0 += C::KYS) {
+            mbar_wait(bar_full + 8 * s, ph);
+            tc_fence_after();
+            const uint32_t a_st = a_base + s * C::A_STAGE;
+            const uint32_t b_st = b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
+            if (elect_one()) {
 #pragma unroll
-          for (int tap = 0; tap < 9; ++tap) {
-            const uint32_t a_tap = SHIFT_A ? a_st + (tap / 3) * C::CPK * C::A_SEG_BYTES + (tap % 3) * 16
-                                           : a_st + tap * C::CPK * C::A_SEG_BYTES;
+              for (int kyi = 0; kyi < C::KYS; ++kyi)
 #pragma unroll
-            for (int k16 = 0; k16 < KC / 16; ++k16) {
-              const uint64_t ad = make_desc(a_tap + 2 * k16 * C::A_SEG_BYTES, C::A_SEG_BYTES, 128);
-              const uint64_t bd = make_desc(b_st + tap * C::B_TAP + 2 * k16 * BN * 16, BN * 16, 128);
-              tc_mma(d_tmem, ad, bd, IDESC, (kb | tap | k16) != 0);
+                for (int kx = 0; kx < 3; ++kx) {
+                  const uint32_t a_tap = a_st + kyi * C::A_KY + (SHIFT_A ? kx * 16 : kx * C::CPK * C::A_SEG_BYTES);
+#pragma unroll
+                  for (int k16 = 0; k16 < KC / 16; ++k16) {
+                    const uint64_t ad = make_desc(a_tap + 2 * k16 * C::A_SEG_BYTES, C::A_SEG_BYTES, 128);
+                    const uint64_t bd = make_desc(b_st + (kyi * 3 + kx) * C::B_TAP + 2 * k16 * BN * 16, BN * 16, 128);
+                    tc_mma(d_tmem, ad, bd, IDESC, (kb | ky0 | kyi | kx | k16) != 0);
+                  }
+                }
+              if (PAIR) tc_commit_mcast(bar_empty + 8 * s, 3);   // frees the stage (in both CTAs) when these MMAs retire
+              else tc_commit(bar_empty + 8 * s);
+              if (kb == P.kbn - 1 && ky0 + C::KYS == 3) tc_commit(bar_tfull + 8 * buf);   // accumulator ready for the epilogue
             }
+            __syncwarp();
+            if (++s == S) { s = 0; ph ^= 1; }
           }
-          if (PAIR) tc_commit_mcast(bar_empty + 8 * s, 3);   // ... in both CTAs
-          else tc_commit(bar_empty + 8 * s);     // frees the smem stage when these MMAs retire
-          if (++s == S) { s = 0; ph ^= 1; }
         }
-        tc_commit(bar_tfull + 8 * buf);          // accumulator ready for the epilogue
       }
     }
   } else {
@@ -263,16 +289,16 @@ int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
     return UB_OK;
   }
   // weights resident in shared memory when they fit beside >= 3 activation stages
-  const int resident_bytes = P.kbn * C::B_STAGE;
+  const int resident_bytes = P.kbn * C::B_KB;
   int stages;
-  if (P.n_ntiles == 1 && C::HDR + resident_bytes + 3 * C::A_STAGE <= SMEM_BUDGET) {
+  if (P.n_ntiles == 1 && C::HDR + resident_bytes + 3 * (3 / C::KYS) * C::A_STAGE <= SMEM_BUDGET) {
     P.b_resident = 1;
     stages = (SMEM_BUDGET - C::HDR - resident_bytes) / C::A_STAGE;
   } else {
     P.b_resident = 0;
     stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + C::B_STAGE);
   }
-  if (stages > 8) stages = 8;
+  if (stages > 24) stages = 24;                // barrier header: 8 * (2 * S + 4) bytes below the head weights at +512
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_tc: BN=%d KC=%d does not fit 2 stages", BN, KC);
   P.num_stages = stages;
   const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
