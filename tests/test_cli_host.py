@@ -101,6 +101,18 @@ def test_open_source_and_unopenable_video(tmp_path):
     assert (s.total_frames, s.height, s.width) == (2, 16, 24) and s.read().shape == (16, 24, 3)
 
 
+def test_checkpoint_layouts(tmp_path):
+    """'model' (infer_two_stage_burr.py:216), 'model_state_dict' and bare state_dicts (infer_video.py:148-153)."""
+    import torch
+    sd = {"final.weight": torch.ones(3, 32, 1, 1), "final.bias": torch.zeros(3)}
+    for name, obj in (("a.pth", {"model": sd, "epoch": 3}), ("b.pth", {"model_state_dict": sd}), ("c.pth", sd)):
+        torch.save(obj, tmp_path / name)
+        got = K.load_state_dict(str(tmp_path / name))
+        assert set(got) == set(sd) and torch.equal(got["final.weight"], sd["final.weight"])
+    with pytest.raises(FileNotFoundError):
+        K.load_state_dict(str(tmp_path / "missing.pth"))
+
+
 _WORKER = r"""
 import os, sys
 import numpy as np

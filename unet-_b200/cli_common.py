@@ -76,10 +76,16 @@ def open_source(video, synthetic: int, synthetic_hw=(448, 800), seed: int = 0):
 
 
 def load_state_dict(path):
-    """torch.load(path)['model'] exactly as infer_two_stage_burr.py:215-216 (a missing file raises)."""
+    """torch.load(path)['model'] as infer_two_stage_burr.py:215-216 (a missing file raises).  Also accepts the
+    other checkpoint layouts the reference's scripts read (infer_video.py:148-153): 'model_state_dict', or a bare
+    state_dict."""
     import torch
     checkpoint = torch.load(path, map_location="cpu", weights_only=False)
-    return checkpoint["model"]
+    if isinstance(checkpoint, dict):
+        for key in ("model", "model_state_dict"):
+            if key in checkpoint and isinstance(checkpoint[key], dict):
+                return checkpoint[key]
+    return checkpoint
 
 
 # ------------------------------------------------------------------------------------- drawing
