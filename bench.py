@@ -29,6 +29,7 @@ FRAME_HW = (448, 800)
 NET_HW = (512, 512)
 GFLOP_PER_FRAME = 111.636          # 18 conv3x3 + final at 512x512, 2*MACs
 METRIC = "frames/sec (800x448 UNet++ + burr)"
+CONV_DRAM_BYTES_PER_FRAME = (11.633741e9 + 6.644805e9) / 64     # measured, see roofline.traffic
 
 
 def load_peaks():
@@ -275,9 +276,14 @@ def run_ours(args):
         roof = {"bound": "tensor", "kernel": "k_conv_tc (18 launches/step, tcgen05 implicit GEMM)",
                 "achieved": tflops, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": tflops / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16_tflops_sustained",
-                "frac_of_burst": tflops / peaks["tf"], "traffic": None,
+                "frac_of_burst": tflops / peaks["tf"],
+                # dram__bytes_read.sum + dram__bytes_write.sum over the 18 conv launches of one 64-frame step
+                # (ncu --set full, profiles/r01g_conv_ncu_full.csv): 11.63 GB read + 6.64 GB written
+                "traffic": CONV_DRAM_BYTES_PER_FRAME * B, "traffic_unit": "bytes per step (18 launches), from profiles/r01g_conv_ncu_full.csv",
                 "algorithmic": f"{GFLOP_PER_FRAME} GFLOP/frame x {B} frames per step over the 18 conv launches",
-                "ms_per_step_by_class": {k: v[0] / args.steps for k, v in tm.items()}}
+                "ms_per_step_by_class": {k: v[0] / args.steps for k, v in tm.items()},
+                "ms_per_step_by_class_note": "CUDA-event brackets per kernel class; gray/edge-map classes run on a second stream "
+                                             "beside the convs, so the classes overlap and do not add up to ms_per_step"}
         line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16", "data": "synthetic",
@@ -300,8 +306,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="frames per step per GPU")
     ap.add_argument("--cpu-frames", type=int, default=24)
