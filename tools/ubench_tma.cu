@@ -186,7 +186,7 @@ int main(int argc, char** argv) {
   CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
   CK(cudaFuncSetAttribute(k_pull, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-  const int geo[2][2] = {{32, 6}, {64, 6}};
+  const int geo[3][2] = {{32, 6}, {32, 10}, {32, 18}};
   for (auto& g : geo) {
     Params P{};
     const int bc = g[0], br = g[1];
@@ -201,11 +201,11 @@ int main(int argc, char** argv) {
     P.tiles_x = (W + bc - 3) / (bc - 2); P.tiles_y = H / (br - 2);
     P.total = (long long)B * P.tiles_x * P.tiles_y; P.kbn = nchunks / cpk; P.buf_bytes = bytes; P.mode = 0; P.nlw = 4; P.pfd = 4;
     const int stage = cpk * br * bc * 16;
-    for (int var : {0})
-    for (int nprod : {1, 2, 4})
-    for (int S : {4, 8}) {
+    for (int var : {0, 1})                       // 1: with the epilogue's store stream beside the loads
+    for (int nprod : {1})
+    for (int S : {3, 5}) {
       if (1024 + S * stage > 227 * 1024) continue;
-      P.S = S; P.out = nullptr; P.pfd = var; P.nlw = nprod;
+      P.S = S; P.out = var ? dout : nullptr; P.write_bytes = write_bytes * ((br - 2) / 4); P.pfd = 0; P.nlw = nprod;
       float best = 1e9;
       for (int rep = 0; rep < 3; ++rep) {
         cudaEventRecord(e0);
@@ -216,8 +216,8 @@ int main(int argc, char** argv) {
       }
       const double rd = (double)P.total * P.kbn * stage;
       const double outpix = (double)B * H * W;
-      printf("nprod %d box %3d pos x %2d rows x %d chunks (%5d B) S %d: %.3f ms  smem-fill %.2f TB/s (%.1f B/clk/SM @1.9GHz)  %.0f clk per 128 output pixels per SM\n",
-             nprod, bc, br, cpk, stage, S, best, rd / best / 1e9, rd / (best * 1e-3) / 148 / 1.9e9, best * 1e-3 * 1.9e9 * 148 / (outpix / 128));
+      printf("writes %d nprod %d box %3d pos x %2d rows x %d chunks (%5d B) S %d: %.3f ms  smem-fill %.2f TB/s (%.1f B/clk/SM @1.9GHz)  %.0f clk per 128 output pixels per SM\n",
+             var, nprod, bc, br, cpk, stage, S, best, rd / best / 1e9, rd / (best * 1e-3) / 148 / 1.9e9, best * 1e-3 * 1.9e9 * 148 / (outpix / 128));
     }
   }
   return 0;

@@ -14,7 +14,8 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libunetb200.so")
+# UNETB200_LIB: an alternative build of the same library (tools/build_trace_lib.sh)
+LIB_PATH = os.environ.get("UNETB200_LIB") or os.path.join(_HERE, "libunetb200.so")
 _lib = None
 
 VARIANT_STANDARD, VARIANT_ENHANCED = 0, 1

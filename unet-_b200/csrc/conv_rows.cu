@@ -18,14 +18,16 @@
 // ky..ky+3, i.e. a +512 B descriptor offset -- half the L2->shared traffic of staging three
 // shifted copies.  Weights stay resident in shared memory when they fit.
 //
-// Warp roles (576 threads): warps 0-15 epilogue, warp 16 bulk-copy producer (+TMEM alloc),
-// warp 17 MMA issuer (one elected lane).  TMEM holds four accumulators of 96 columns (Cout 32,
+// Warp roles (608 threads): warps 0-15 epilogue, warp 16 bulk-copy producer (+TMEM alloc),
+// warps 17-18 MMA issuers (alternate M-tiles, one elected lane each).  TMEM holds four accumulators of 96 columns (Cout 32,
 // one per epilogue warpgroup) or two of 192 columns (Cout 64, two warpgroups per accumulator,
 // 32 channels each), so the MMAs of tiles i+1.. overlap the epilogue of tile i.
 // Epilogue arithmetic is packed (FADD2, F2FP.RELU.SATFINITE.PACK) -- it is the instruction-
 // bound part of these layers (profiles/r01_conv.md).
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 #include "tc_ptx.cuh"
 #include "tmap.cuh"
 
@@ -43,12 +45,29 @@ struct RowsParams {
   int B, kb0, kbn, num_stages, b_resident;
   int tiles_x, tiles_y;                        // tiles_y counts tile GROUPS: mt vertically adjacent 4-row M-tiles share one box
   int mt, a_chunk, a_stage;                    // M-tiles per group; bytes of one chunk / one stage of the box ((4*mt+2) rows)
-  int halves;                                  // 2: the MMA issuer walks a group's boxes twice, half the M-tiles each (kbn > 1)
   long long total_items;
   PPLayout L;
   int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
+#ifdef UB_ROWS_TRACE
+  long long* trace;                            // [6 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
+#endif
 };
+
+// Pipeline trace (debug builds only, tools/build_trace_lib.sh): block 0 stamps clock64 at the hand-over points of every
+// role.  Roles: 0 producer (index = box), 1 MMA issuer (index = M-tile), 2.. epilogue warpgroups (index = use).
+#ifdef UB_ROWS_TRACE
+constexpr int TR_N = 1024;
+int g_trace_dump = 0;
+#define UB_TR(role, idx, ev)                                                                          \
+  do {                                                                                                \
+    if (blockIdx.x == 0 && (idx) < TR_N) P.trace[(((role) * TR_N) + (idx)) * 8 + (ev)] = clock64();   \
+  } while (0)
+#else
+#define UB_TR(role, idx, ev) do { } while (0)
+#endif
+
+constexpr int NTHREADS = 19 * 32;        // 16 epilogue warps, producer, two MMA issuers
 
 template <int COUT, int KC>
 struct RCfg {
@@ -90,7 +109,7 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
 // bound the head cost 8x32 predicated FFMAs plus local-memory traffic per pixel and made the last layer issue-bound
 // (845 instructions per warp and tile instead of ~300, profiles/r01_conv.md).
 template <int COUT, int KC, int NCLS>
-__global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
+__global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
   using C = RCfg<COUT, KC>;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -106,7 +125,7 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
   const int tiles_per_img = P.tiles_x * P.tiles_y;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 2); }
     for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, C::WARPS_PER_BUF); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -126,98 +145,125 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
       tma_prefetch_desc(&P.tm0);
       tma_prefetch_desc(&P.tm1);
       int s = 0; uint32_t ph = 0; bool first = true;
+      [[maybe_unused]] int nbox = 0;
       for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
         const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
         const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
         const bool load_b = !P.b_resident || first;
         for (int kb = 0; kb < P.kbn; ++kb) {
           const uint32_t full = bar_full + 8 * s;
+          UB_TR(0, nbox, 0);
           mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          UB_TR(0, nbox, 1);
           mbar_expect_tx(full, P.a_stage + (load_b ? C::B_STAGE : 0));
           // box origin: padded row 4*mt*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
           if (kb < P.kb0) tma_load_4d(a_base + s * P.a_stage, &P.tm0, tx * T_VALID * 8, ty * T_ROWS * P.mt, kb * C::CPK, b, full);
           else tma_load_4d(a_base + s * P.a_stage, &P.tm1, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb - P.kb0) * C::CPK, b, full);
           if (load_b)
             bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE, P.w + (size_t)kb * 3 * (size_t)(KC * C::NP), C::B_STAGE, full);
+          UB_TR(0, nbox, 2);
+          ++nbox;
           if (++s == S) { s = 0; ph ^= 1; }
         }
         first = false;
       }
     }
-  } else if (warp == 17) {
-    // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues =====================
+  } else if (warp >= 17) {
+    // ===================== MMA issuers (warps 17, 18) =====================
+    // Two warps issue alternate M-tiles (tile parity = accumulator parity).  For a lone issuer the barrier waits and the
+    // two tcgen05.commit per tile (~90 clk each) do not overlap its own MMAs: tools/ubench_commit.cu measures 647 clk per
+    // 6-MMA batch with one issuer against 336 with two (profiles/r01_ubench_commit.log).  In this kernel the change is
+    // neutral on the kbn = 1 layers, which are bound by their load + store streams (profiles/r01_conv.md, findings 10-11);
+    // it keeps the tensor pipe off the critical path.  Each whole warp walks the loop, one elected lane issues; no
+    // divisions in here.
     {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) |
                                  ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      const int wi = warp - 17;
       int it = 0;                                                 // counts M-tiles (accumulator uses)
-      int s0 = 0; uint32_t ph0 = 0;                                // stage / phase of the group's first box (this warp paces
-                                                                   // the tensor pipe: no divisions in here)
-      // With several k-blocks all mt accumulators of a group are live until its last k-block.  P.halves == 2 walks the
-      // group's staged boxes twice, first for M-tiles 0..mt/2-1 then for the rest, so the first half's accumulators
-      // complete earlier (needs all kbn boxes of a group resident: num_stages >= kbn + 1).
-      const int mh = P.mt / P.halves;
+      int s = 0; uint32_t ph = 0;
       for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x, it += P.mt) {
-        int s = s0; uint32_t ph = ph0;
-        for (int h = 0; h < P.halves; ++h) {
-          s = s0; ph = ph0;
-          for (int kb = 0; kb < P.kbn; ++kb) {
-            if (h == 0) {
-              mbar_wait(bar_full + 8 * s, ph);
+        for (int kb = 0; kb < P.kbn; ++kb) {
+          if (lane == 0 && kb == 0) UB_TR(1, it + wi, 4);
+          mbar_wait(bar_full + 8 * s, ph);
+          tc_fence_after();
+          if (lane == 0 && kb == 0) UB_TR(1, it + wi, 3);          // first box of the group landed
+          const uint32_t a_st = a_base + s * P.a_stage;
+          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+          bool mine = false;
+          for (int m = 0; m < P.mt; ++m) {
+            if (((it + m) & 1) != wi) continue;
+            mine = true;
+            const int buf = (it + m) % C::NBUF, use = (it + m) / C::NBUF;
+            if (kb == 0) {                                     // first touch of this accumulator: the epilogue must have drained it
+              if (lane == 0) UB_TR(1, it + m, 0);
+              mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
               tc_fence_after();
+              if (lane == 0) UB_TR(1, it + m, 1);
             }
-            const uint32_t a_st = a_base + s * P.a_stage;
-            const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
-            for (int m = h * mh; m < (h + 1) * mh; ++m) {
-              const int buf = (it + m) % C::NBUF, use = (it + m) / C::NBUF;
-              if (kb == 0) {                                   // first touch of this accumulator: the epilogue must have drained it
-                mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);
-                tc_fence_after();
-              }
-              const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
-              if (elect_one()) {
+            const uint32_t d_tmem = tmem_base + buf * C::T_STRIDE;
+            if (elect_one()) {
 #pragma unroll
-                for (int ky = 0; ky < 3; ++ky) {
+              for (int ky = 0; ky < 3; ++ky) {
 #pragma unroll
-                  for (int k16 = 0; k16 < KC / 16; ++k16) {
-                    // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
-                    // the two K chunks a_chunk apart
-                    const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
-                    const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
-                    tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
-                  }
+                for (int k16 = 0; k16 < KC / 16; ++k16) {
+                  // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
+                  // the two K chunks a_chunk apart
+                  const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
+                  const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
+                  tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
                 }
-                if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);                         // accumulator of M-tile m complete
-                if (h == P.halves - 1 && m == (h + 1) * mh - 1) tc_commit(bar_empty + 8 * s); // box free once every M-tile read it
               }
-              __syncwarp();
+              if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);                           // accumulator of M-tile m complete
             }
-            if (++s == S) { s = 0; ph ^= 1; }
+            __syncwarp();
+            if (lane == 0 && kb == P.kbn - 1) UB_TR(1, it + m, 2);
           }
+          // hand the box back once this warp's MMAs have read it (plain arrive if it had no M-tile in this group)
+          if (elect_one()) {
+            if (mine) tc_commit(bar_empty + 8 * s);
+            else mbar_arrive(bar_empty + 8 * s);
+          }
+          __syncwarp();
+          if (++s == S) { s = 0; ph ^= 1; }
         }
-        s0 = s; ph0 = ph;
       }
     }
   } else {
     // ===================== epilogue (warps 0-15) =====================
     const int wq = warp & 3;                                   // TMEM lane quarter = tile row
-    const int grp = warp >> 2;
-    const int my_buf = C::SPLIT ? (grp >> 1) : grp;
-    const int ch0 = C::SPLIT ? (grp & 1) * 32 : 0;             // first of this warp's 32 channels
+    const int grp_w = warp >> 2;                               // epilogue warpgroup
+    const int my_buf = C::SPLIT ? (grp_w >> 1) : grp_w;
+    const int ch0 = C::SPLIT ? (grp_w & 1) * 32 : 0;             // first of this warp's 32 channels
     constexpr int NCHUNK = COUT / 8;
+    // The 16 epilogue warps share four issue ports with ~360 instructions per warp and tile: per-tile index
+    // arithmetic is kept out of the loop.  (b, tgy, tx) of the CTA's next group = current + gridDim.x items, carried
+    // digit by digit; the divisions happen once here.
+    const int step_b = (int)gridDim.x / tiles_per_img, step_r = (int)gridDim.x - step_b * tiles_per_img;
+    const int step_y = step_r / P.tiles_x, step_x = step_r - step_y * P.tiles_x;
+    int b = (int)blockIdx.x / tiles_per_img, tgy, tx;
+    {
+      const int t = (int)blockIdx.x - b * tiles_per_img;
+      tgy = t / P.tiles_x; tx = t - tgy * P.tiles_x;
+    }
+    const size_t plane = (size_t)L.Ppl * 8;
     int it = 0;
-    for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x)
+    for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
+    if (lane == 0 && wq == 0) UB_TR(2 + grp_w, it / C::NBUF, 4);
+    const int x = tx * T_VALID - 1 + lane;
+    const bool valid = lane >= 1 && lane <= T_VALID && x < L.W;
+    const bool edge = x == -1 || x == L.W;                     // left / right zero border of the PP plane
+    act_t* const o_grp = P.out + ((size_t)b * NCHUNK + (ch0 >> 3)) * plane + (size_t)(L.G + x + 1) * 8;
     for (int m = 0; m < P.mt; ++m, ++it) {
       if (it % C::NBUF != my_buf) continue;
       const int use = it / C::NBUF;
-      const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
-      const int tgy = t / P.tiles_x, tx = t - tgy * P.tiles_x;
       const int ty = tgy * P.mt + m;                           // 4-row M-tile index inside the image
-      const int y = ty * T_ROWS + wq, x = tx * T_VALID - 1 + lane;
-      const bool valid = lane >= 1 && lane <= T_VALID && x < L.W;
-      const bool edge = x == -1 || x == L.W;                   // left / right zero border of the PP plane
-      const int q = (y + 1) * L.pitch + (x + 1);               // position relative to G
+      const int y = ty * T_ROWS + wq;
+      const int q = (y + 1) * L.pitch;                         // row offset relative to G
+      if (lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 0);
       mbar_wait(bar_tfull + 8 * my_buf, use & 1);
       tc_fence_after();
+      if (lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 1);
       const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + my_buf * C::T_STRIDE;
       constexpr bool head = NCLS > 0;
       constexpr int NL = head ? NCLS : 1;
@@ -235,10 +281,12 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
         TMEM_LD16(taddr + COUT + c0, k1);
         TMEM_LD16(taddr + 2 * COUT + c0, k2);
         tmem_ld_wait();
+        if (half == 0 && lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 5);
         if (half == 1) {                                       // accumulator fully read: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_tempty + 8 * my_buf);
+          if (lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 2);
         }
         uint32_t hv[8];
 #pragma unroll
@@ -261,14 +309,14 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
           }
         }
         if (!head && (valid || edge)) {
-          act_t* o = P.out + (((size_t)b * NCHUNK + (c0 >> 3)) * L.Ppl + L.G + q) * 8;
+          act_t* o = o_grp + (size_t)(half * 2) * plane + (size_t)q * 8;
           *reinterpret_cast<uint4*>(o) = make_uint4(hv[0], hv[1], hv[2], hv[3]);
-          *reinterpret_cast<uint4*>(o + (size_t)L.Ppl * 8) = make_uint4(hv[4], hv[5], hv[6], hv[7]);
+          *reinterpret_cast<uint4*>(o + plane) = make_uint4(hv[4], hv[5], hv[6], hv[7]);
           // top / bottom zero border rows of the plane
           if ((ty == 0 && wq == 0) || (ty == P.tiles_y * P.mt - 1 && wq == T_ROWS - 1)) {
             act_t* z = wq == 0 ? o - (size_t)L.pitch * 8 : o + (size_t)L.pitch * 8;
             *reinterpret_cast<uint4*>(z) = make_uint4(0, 0, 0, 0);
-            *reinterpret_cast<uint4*>(z + (size_t)L.Ppl * 8) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(z + plane) = make_uint4(0, 0, 0, 0);
           }
         }
       }
@@ -284,6 +332,13 @@ __global__ void __launch_bounds__(576, 1) k_conv_rows(const __grid_constant__ Ro
           }
         if (P.pred) P.pred[(size_t)b * hw + pix] = (uint8_t)best;
       }
+      if (lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 3);
+    }
+    tx += step_x;
+    if (tx >= P.tiles_x) { tx -= P.tiles_x; ++tgy; }
+    tgy += step_y;
+    if (tgy >= P.tiles_y) { tgy -= P.tiles_y; ++b; }
+    b += step_b;
     }
   }
 
@@ -325,10 +380,6 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: COUT=%d KC=%d does not fit 2 stages", COUT, KC);
   P.num_stages = stages;
   P.mt = mt;
-  // measured: 5748 frames/s with 1, 5680 with 2 (same box) -- the tensor pipe, not the accumulator hand-over, paces
-  // these layers; the two-pass walk stays available for experiments
-  static const int halves_env = getenv("UB_ROWS_HALVES") ? atoi(getenv("UB_ROWS_HALVES")) : 1;
-  P.halves = (halves_env == 2 && P.kbn > 1 && mt >= 2 && stages >= P.kbn + 1) ? 2 : 1;
   P.a_chunk = (T_ROWS * mt + 2) * SEG_BYTES;
   P.a_stage = C::CPK * P.a_chunk;
   P.tiles_y = a.H / (T_ROWS * mt);
@@ -339,8 +390,30 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   if (r != UB_OK) return r;
   const int smem = C::HDR + stages * P.a_stage + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
-  kern<<<(unsigned)grid, 576, smem, st>>>(P);
+#ifdef UB_ROWS_TRACE
+  static long long* d_trace = nullptr;
+  const size_t tr_bytes = sizeof(long long) * 6 * TR_N * 8;
+  if (!d_trace) UB_CUDA(ctx, cudaMalloc(&d_trace, tr_bytes));
+  UB_CUDA(ctx, cudaMemsetAsync(d_trace, 0, tr_bytes, st));
+  P.trace = d_trace;
+#endif
+  kern<<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   UB_CHECK_LAUNCH(ctx);
+#ifdef UB_ROWS_TRACE
+  if (const char* dir = getenv("UB_ROWS_TRACE_DIR")) {
+    std::vector<long long> h(6 * TR_N * 8);
+    UB_CUDA(ctx, cudaStreamSynchronize(st));
+    UB_CUDA(ctx, cudaMemcpy(h.data(), d_trace, tr_bytes, cudaMemcpyDeviceToHost));
+    char path[512];
+    snprintf(path, sizeof path, "%s/rows_trace_%02d.bin", dir, g_trace_dump++);
+    if (FILE* f = fopen(path, "wb")) {
+      const long long hdr[8] = {COUT, KC, NCLS, P.kbn, P.mt, P.num_stages, P.total_items, grid};
+      fwrite(hdr, sizeof hdr, 1, f);
+      fwrite(h.data(), tr_bytes, 1, f);
+      fclose(f);
+    }
+  }
+#endif
   return UB_OK;
 }
 
