@@ -96,6 +96,22 @@ def test_forward_vs_fp32_oracle(ctx, sd, hw, golden_net):
     assert agree >= 0.998
 
 
+@pytest.mark.parametrize("hw", [(64, 64), (128, 160), (48, 80)])
+def test_fused_pool_equals_maxpool_of_layer_output(ctx, hw):
+    """MaxPool2d(2,2) (src/models/unetpp.py:75,105-108) is written by the epilogue of conv0_0.conv2 / conv1_0.conv2.
+    The pooled planes (activation slots 3, 6) must equal the max-pool of the layer outputs (slots 2, 5) bit for bit,
+    including the ragged last 30-column tile (160, 80, 64 are not multiples of 30)."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(2, 3, hw[0], hw[1], generator=g)
+    ctx.forward(x.cuda())
+    for lvl, (full, pooled, c) in enumerate([(2, 3, 32), (5, 6, 64)]):
+        h, w = hw[0] >> lvl, hw[1] >> lvl
+        a = ctx.debug_activation(full, 2, c, h, w)
+        p = ctx.debug_activation(pooled, 2, c, h // 2, w // 2)
+        assert float(a.max()) > 0
+        assert torch.equal(p, F.max_pool2d(a, 2)), f"level {lvl}"
+
+
 @pytest.mark.parametrize("ncls", [2, 5, 8])
 def test_forward_other_class_counts(ncls):
     """The fused 1x1 head has a 3-class fast path; other class counts take the generic one."""

@@ -115,6 +115,7 @@ struct ub_ctx {
   float head_host[8 * 33] = {0};     // host mirror: [num_classes][32] weights then [num_classes] biases
   // activation arena (PP layout, sized for max_batch at net_h x net_w)
   act_t* act[24] = {nullptr};
+  int pool_border_hw[2][2] = {{0, 0}, {0, 0}};   // (H, W) for which the zero borders of A_P0 / A_P1 were last set (fused pool)
   // pre/post + stage-2 scratch
   uint8_t* d_frames = nullptr;       // [B,fh,fw,3]   (ub_pipeline_host staging)
   uint8_t* d_gray = nullptr;         // [B,fh,fw]
@@ -174,12 +175,14 @@ struct ConvArgs {
   int B, H, W;
   const float* head_w; const float* head_b; int num_classes;
   float* logits; uint8_t* pred;
+  act_t* pool_out;             // non-null: also write MaxPool2d(2,2) of the output into this PP plane (conv_rows only)
 };
 int conv3x3_simt(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_tc_init(ub_ctx* ctx);
 int conv3x3_rows(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_rows_init(ub_ctx* ctx);
+bool conv_rows_can_pool(const ub_ctx* ctx, const ConvLayer& L);   // the layer's kernel has a fused-pool variant
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // activation buffers (ub_ctx::act): channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu

@@ -48,6 +48,7 @@ struct RowsParams {
   long long total_items;
   PPLayout L;
   int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
+  act_t* pool_out; PPLayout Lp; int pool_smem;  // fused MaxPool2d(2,2) (POOL kernels): pooled PP plane, its layout, staging offset
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
 #ifdef UB_ROWS_TRACE
   long long* trace;                            // [6 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
@@ -108,7 +109,15 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
 // class count <= 8.  The class count must be a compile-time constant on the hot configuration: with the run-time
 // bound the head cost 8x32 predicated FFMAs plus local-memory traffic per pixel and made the last layer issue-bound
 // (845 instructions per warp and tile instead of ~300, profiles/r01_conv.md).
-template <int COUT, int KC, int NCLS>
+//
+// POOL: the epilogue also writes MaxPool2d(2,2) of its output (src/models/unetpp.py:75,105-108) into a second PP plane,
+// so the next level's input never costs a re-read of this layer's output.  Columns pair up inside a warp (one shuffle),
+// rows pair up across the two warps that hold tile rows 2r / 2r+1: they swap column-pooled halves through a 16 KB
+// double-buffered staging area and a 64-thread named barrier, then each stores 16 of the 32 channels.  Only the
+// interior of the pooled plane is written; its zero border is set once by the host (net_glue.cu).
+constexpr int POOL_SMEM = 16 * 1024;      // 16 warps x 2 buffers x [2 x 16 slots] x 16 B
+
+template <int COUT, int KC, int NCLS, bool POOL>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
   using C = RCfg<COUT, KC>;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -247,6 +256,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
       tgy = t / P.tiles_x; tx = t - tgy * P.tiles_x;
     }
     const size_t plane = (size_t)L.Ppl * 8;
+    [[maybe_unused]] uint32_t pbuf = 0;                        // POOL: staging buffer of this tile
+    [[maybe_unused]] const uint32_t stage_mine = smem_u32(smem) + P.pool_smem + warp * 1024 + (lane >> 1) * 16;
+    [[maybe_unused]] const uint32_t stage_peer = smem_u32(smem) + P.pool_smem + (warp ^ 1) * 1024 + (lane >> 1) * 16;
     int it = 0;
     for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
     if (lane == 0 && wq == 0) UB_TR(2 + grp_w, it / C::NBUF, 4);
@@ -269,6 +281,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
       constexpr int NL = head ? NCLS : 1;
       const int ncls = NCLS == 8 ? P.ncls : NCLS;
       float lg[NL];
+      [[maybe_unused]] uint32_t mine[8];                       // POOL: column-pooled channels this warp will store
       if (head) {
 #pragma unroll
         for (int c = 0; c < NL; ++c) lg[c] = c < ncls ? P.head[ncls * 32 + c] : 0.f;
@@ -319,6 +332,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
             *reinterpret_cast<uint4*>(z + plane) = make_uint4(0, 0, 0, 0);
           }
         }
+        if constexpr (POOL) {
+          // column pairs (x, x+1), x even = odd lanes; activations are >= 0, so the 16-bit integer maximum is the maximum
+          uint32_t cp[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cp[j] = __vmaxu2(hv[j], __shfl_down_sync(0xffffffffu, hv[j], 1));
+          if (half == (wq & 1)) {                                // even tile rows keep channels 0-15, odd rows 16-31
+#pragma unroll
+            for (int j = 0; j < 8; ++j) mine[j] = cp[j];
+          } else if (lane & 1) {
+            st_shared_v4(stage_mine + pbuf * 512, cp[0], cp[1], cp[2], cp[3]);
+            st_shared_v4(stage_mine + pbuf * 512 + 256, cp[4], cp[5], cp[6], cp[7]);
+          }
+        }
+      }
+      if constexpr (POOL) {
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp >> 1)) : "memory");       // the two warps of rows 2r / 2r+1
+        if ((lane & 1) && valid) {
+          uint32_t o0, o1, o2, o3, o4, o5, o6, o7;
+          ld_shared_v4(stage_peer + pbuf * 512, o0, o1, o2, o3);
+          ld_shared_v4(stage_peer + pbuf * 512 + 256, o4, o5, o6, o7);
+          const int py = y >> 1, px = tx * (T_VALID / 2) + (lane >> 1);
+          act_t* po = P.pool_out + (((size_t)b * NCHUNK + (ch0 >> 3) + (wq & 1) * 2) * P.Lp.Ppl + P.Lp.G +
+                                    (size_t)(py + 1) * P.Lp.pitch + px + 1) * 8;
+          *reinterpret_cast<uint4*>(po) = make_uint4(__vmaxu2(mine[0], o0), __vmaxu2(mine[1], o1), __vmaxu2(mine[2], o2), __vmaxu2(mine[3], o3));
+          *reinterpret_cast<uint4*>(po + (size_t)P.Lp.Ppl * 8) =
+              make_uint4(__vmaxu2(mine[4], o4), __vmaxu2(mine[5], o5), __vmaxu2(mine[6], o6), __vmaxu2(mine[7], o7));
+        }
+        pbuf ^= 1;
       }
       if (head && valid) {
         const size_t hw = (size_t)L.H * L.W, pix = (size_t)y * L.W + x;
@@ -352,10 +393,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 
-template <int COUT, int KC, int NCLS>
+template <int COUT, int KC, int NCLS, bool POOL = false>
 int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
   using C = RCfg<COUT, KC>;
-  auto kern = k_conv_rows<COUT, KC, NCLS>;
+  auto kern = k_conv_rows<COUT, KC, NCLS, POOL>;
+  constexpr int BUDGET = SMEM_BUDGET - (POOL ? POOL_SMEM : 0);
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
@@ -372,8 +414,8 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
     if (a.H % (T_ROWS * cand)) continue;
     const int a_stage = C::CPK * (T_ROWS * cand + 2) * SEG_BYTES;
     int st_n;
-    if (C::HDR + resident_bytes + 2 * a_stage <= SMEM_BUDGET) { P.b_resident = 1; st_n = (SMEM_BUDGET - C::HDR - resident_bytes) / a_stage; }
-    else { P.b_resident = 0; st_n = (SMEM_BUDGET - C::HDR) / (a_stage + C::B_STAGE); }
+    if (C::HDR + resident_bytes + 2 * a_stage <= BUDGET) { P.b_resident = 1; st_n = (BUDGET - C::HDR - resident_bytes) / a_stage; }
+    else { P.b_resident = 0; st_n = (BUDGET - C::HDR) / (a_stage + C::B_STAGE); }
     if (st_n >= 2 || cand == 1) { mt = cand; stages = st_n; break; }
   }
   if (stages > 8) stages = 8;
@@ -388,7 +430,8 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   if (r == UB_OK) r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK)
                               : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
   if (r != UB_OK) return r;
-  const int smem = C::HDR + stages * P.a_stage + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  int smem = C::HDR + stages * P.a_stage + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  if (POOL) { P.pool_smem = (smem + 1023) & ~1023; smem = P.pool_smem + POOL_SMEM; }
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
 #ifdef UB_ROWS_TRACE
   static long long* d_trace = nullptr;
@@ -422,6 +465,11 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& 
     if (cout != 32 || kc != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs COUT=32 KC=32 (got %d, %d)", cout, kc);
     return P.ncls == 3 ? launch_rows<32, 32, 3>(ctx, P, a, Lr, st, init_only) : launch_rows<32, 32, 8>(ctx, P, a, Lr, st, init_only);
   }
+  if (P.pool_out) {
+    if (cout == 32 && kc == 32) return launch_rows<32, 32, 0, true>(ctx, P, a, Lr, st, init_only);
+    if (cout == 64 && kc == 64) return launch_rows<64, 64, 0, true>(ctx, P, a, Lr, st, init_only);
+    return ub_fail(ctx, UB_ERR_ARG, "conv_rows: no fused pool for COUT=%d KC=%d", cout, kc);
+  }
   if (cout == 32 && kc == 16) return launch_rows<32, 16, 0>(ctx, P, a, Lr, st, init_only);
   if (cout == 32 && kc == 32) return launch_rows<32, 32, 0>(ctx, P, a, Lr, st, init_only);
   if (cout == 64 && kc == 32) return launch_rows<64, 32, 0>(ctx, P, a, Lr, st, init_only);
@@ -433,14 +481,21 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& 
 
 int conv_rows_init(ub_ctx* ctx) {
   static RowsParams P{};
-  const int cfgs[6][3] = {{32, 16, 0}, {32, 32, 0}, {64, 32, 0}, {64, 64, 0}, {32, 32, 3}, {32, 32, 8}};
+  const int cfgs[8][4] = {{32, 16, 0, 0}, {32, 32, 0, 0}, {64, 32, 0, 0}, {64, 64, 0, 0}, {32, 32, 3, 0}, {32, 32, 8, 0},
+                          {32, 32, 0, 1}, {64, 64, 0, 1}};
   ConvArgs a{}; ConvLayer Lr{};
   for (auto& c : cfgs) {
     P.ncls = c[2];
+    P.pool_out = c[3] ? reinterpret_cast<act_t*>(&P) : nullptr;     // any non-null value: selects the POOL instantiation
     int r = dispatch_rows(ctx, c[0], c[1], P, a, Lr, nullptr, true);
     if (r != UB_OK) return r;
   }
   return UB_OK;
+}
+
+bool conv_rows_can_pool(const ub_ctx* ctx, const ConvLayer& L) {
+  static const bool off = getenv("UB_FUSE_POOL") && atoi(getenv("UB_FUSE_POOL")) == 0;
+  return !off && ctx->conv_impl != 1 && L.fold && L.cin1 == 0 && ((L.cout == 32 && L.kc == 32) || (L.cout == 64 && L.kc == 64));
 }
 
 int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t st) {
@@ -451,6 +506,10 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
   P.L = pp_layout(a.H, a.W);
   P.tiles_x = cdiv(a.W, T_VALID);
   P.ncls = 0; P.logits = a.logits; P.pred = a.pred;
+  if (a.pool_out) {
+    if (a.head_w || (a.H & 1) || (a.W & 1)) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: fused pool needs even H, W and no head");
+    P.pool_out = a.pool_out; P.Lp = pp_layout(a.H / 2, a.W / 2);
+  }
   if (a.head_w) {
     if (Lr.cout != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == 32");
     P.ncls = a.num_classes;

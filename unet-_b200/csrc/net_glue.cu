@@ -206,9 +206,9 @@ int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStrea
 
 static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
                     act_t* out, int B, int H, int W, cudaStream_t st,
-                    float* logits = nullptr, uint8_t* pred = nullptr, bool head = false) {
+                    float* logits = nullptr, uint8_t* pred = nullptr, bool head = false, act_t* pool_out = nullptr) {
   ConvArgs a{};
-  a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W;
+  a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W; a.pool_out = pool_out;
   if (head) {
     a.head_w = ctx->head_w; a.head_b = ctx->head_b; a.num_classes = ctx->num_classes;
     a.logits = logits; a.pred = pred;
@@ -217,6 +217,23 @@ static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
 }
 
 #define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
+
+// conv2 of an encoder block followed by MaxPool2d(2,2) (unetpp.py:105-108).  Where the layer's kernel has the fused
+// variant the pool is written from the conv epilogue (interior only: the pooled plane's zero border and over-read tail
+// are set here, once per shape -- the P buffers have no other writer); otherwise the pool kernel runs.
+static int run_conv_pool(ub_ctx* ctx, int li, int pslot, const act_t* src, act_t* out, act_t* pooled, int C,
+                         int B, int H, int W, cudaStream_t st) {
+  if (!conv_rows_can_pool(ctx, ctx->conv[li])) {
+    RUN(run_conv(ctx, li, src, nullptr, out, B, H, W, st));
+    return maxpool2_pp(ctx, out, B, C, H, W, pooled, st);
+  }
+  int* hw = ctx->pool_border_hw[pslot];
+  if (hw[0] != H || hw[1] != W) {
+    UB_CUDA(ctx, cudaMemsetAsync(pooled, 0, pp_bytes(ctx->max_batch, C, ctx->net_h >> (pslot + 1), ctx->net_w >> (pslot + 1)), st));
+    hw[0] = H; hw[1] = W;
+  }
+  return run_conv(ctx, li, src, nullptr, out, B, H, W, st, nullptr, nullptr, false, pooled);
+}
 
 // The network input comes from exactly one of x_nchw / frames; with frames the preprocess kernel writes the PP input.
 int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const uint8_t* frames, int fh, int fw,
@@ -229,11 +246,9 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const 
   else RUN(nchw_to_pp(ctx, x_nchw, B, 3, H, W, A[A_XIN], 16, st));
   // encoder (unetpp.py:104-108)
   RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));
-  RUN(run_conv(ctx, 1, A[A_T0], nullptr, A[A_X00], B, H, W, st));
-  RUN(maxpool2_pp(ctx, A[A_X00], B, 32, H, W, A[A_P0], st));
+  RUN(run_conv_pool(ctx, 1, 0, A[A_T0], A[A_X00], A[A_P0], 32, B, H, W, st));
   RUN(run_conv(ctx, 2, A[A_P0], nullptr, A[A_T1], B, h1, w1, st));
-  RUN(run_conv(ctx, 3, A[A_T1], nullptr, A[A_X10], B, h1, w1, st));
-  RUN(maxpool2_pp(ctx, A[A_X10], B, 64, h1, w1, A[A_P1], st));
+  RUN(run_conv_pool(ctx, 3, 1, A[A_T1], A[A_X10], A[A_P1], 64, B, h1, w1, st));
   RUN(run_conv(ctx, 4, A[A_P1], nullptr, A[A_T2], B, h2, w2, st));
   RUN(run_conv(ctx, 5, A[A_T2], nullptr, A[A_X20], B, h2, w2, st));
   RUN(maxpool2_pp(ctx, A[A_X20], B, 128, h2, w2, A[A_P2], st));
