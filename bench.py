@@ -29,7 +29,7 @@ FRAME_HW = (448, 800)
 NET_HW = (512, 512)
 GFLOP_PER_FRAME = 111.636          # 18 conv3x3 + final at 512x512, 2*MACs
 METRIC = "frames/sec (800x448 UNet++ + burr)"
-CONV_DRAM_BYTES_PER_FRAME = (11.633741e9 + 6.644805e9) / 64     # measured, see roofline.traffic
+CONV_DRAM_BYTES_PER_FRAME = (11.661369e9 + 7.043801e9) / 64     # measured, see roofline.traffic
 
 
 def load_peaks():
@@ -278,8 +278,8 @@ def run_ours(args):
                 "frac": tflops / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16_tflops_sustained",
                 "frac_of_burst": tflops / peaks["tf"],
                 # dram__bytes_read.sum + dram__bytes_write.sum over the 18 conv launches of one 64-frame step
-                # (ncu --set full, profiles/r01g_conv_ncu_full.csv): 11.63 GB read + 6.64 GB written
-                "traffic": CONV_DRAM_BYTES_PER_FRAME * B, "traffic_unit": "bytes per step (18 launches), from profiles/r01g_conv_ncu_full.csv",
+                # (ncu --set full, profiles/r01i_conv_ncu_full.csv): 11.66 GB read + 7.04 GB written
+                "traffic": CONV_DRAM_BYTES_PER_FRAME * B, "traffic_unit": "bytes per step (18 launches), from profiles/r01i_conv_ncu_full.csv",
                 "algorithmic": f"{GFLOP_PER_FRAME} GFLOP/frame x {B} frames per step over the 18 conv launches",
                 "ms_per_step_by_class": {k: v[0] / args.steps for k, v in tm.items()},
                 "ms_per_step_by_class_note": "CUDA-event brackets per kernel class; gray/edge-map classes run on a second stream "
