@@ -108,6 +108,8 @@ int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, in
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */
+/* GaussianBlur((5,5),1.0) followed by Canny(low, high) in one fused pass (:85-86; infer_enhanced_burr.py:89-90). */
+int ub_blur_canny(ub_ctx* ctx, const uint8_t* gray_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream);
 /* op: 0 dilate, 1 erode, 2 close, 3 open with cv2 MORPH_ELLIPSE(k,k), k <= 25, on binary images:
  * any non-zero input is foreground, the output is {0, value}. */
 int ub_morph(ub_ctx* ctx, int op, int k, const uint8_t* src_dev, int B, int H, int W, int value, uint8_t* dst_dev, void* stream); /* :78-80,:92-97 */

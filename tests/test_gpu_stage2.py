@@ -83,7 +83,7 @@ def test_masks_from_logits(ctx):
         same("tape", tape[i], t)
 
 
-@pytest.mark.parametrize("hw", [(448, 800), (37, 53), (64, 96)])
+@pytest.mark.parametrize("hw", [(448, 800), (37, 53), (64, 96), (36, 164), (100, 324), (33, 160), (31, 4), (70, 484)])
 def test_gauss_canny_edges(ctx, hw):
     h, w = hw
     fr = np.concatenate([S.frames_cable(1, h, w, seed=1), S.frames_noise(1, h, w, seed=2)])
@@ -94,6 +94,7 @@ def test_gauss_canny_edges(ctx, hw):
     for lo, hi in ((50, 150), (30, 100)):
         e = ctx.canny(dev(ref_blur), lo, hi)
         same(f"canny{lo}", e, np.stack([cv2.Canny(b, lo, hi) for b in ref_blur]))
+        same(f"blur_canny{lo}", ctx.blur_canny(dev(gray), lo, hi), np.stack([cv2.Canny(b, lo, hi) for b in ref_blur]))
     same("sobel", ctx.sobel_edges(dev(gray)), np.stack([cvnp.sobel_edges(g) for g in gray]))
     same("lap", ctx.laplacian_edges(dev(gray)), np.stack([cvnp.laplacian_edges(g) for g in gray]))
 

@@ -57,6 +57,7 @@ SIGNATURES = {
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_morph": (_I, [_P, _I, _I, _P, _I, _I, _I, _I, _P, _P]),
     "ub_ccl": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _P, _P]),
     "ub_sobel_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
@@ -231,6 +232,9 @@ class Context:
 
     def canny(self, src, low, high):
         return self._u8op(lib().ub_canny, src, low, high)
+
+    def blur_canny(self, gray, low, high):
+        return self._u8op(lib().ub_blur_canny, gray, low, high)
 
     def sobel_edges(self, gray, thresh=50):
         return self._u8op(lib().ub_sobel_edges, gray, thresh)

@@ -43,6 +43,7 @@ int normalize_frames_impl(ub_ctx*, const uint8_t*, int, int, int, int, uint8_t*,
 int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t);
 int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
 int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
+int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t);
 int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
 int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
 
@@ -296,6 +297,12 @@ int ub_canny(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int low, int 
   NEED_CTX(ctx);
   RUN(check_frame_shape(ctx, B, H, W));
   return canny(ctx, src, dst, ctx->d_tmp[3], ctx->d_lab[0], B, H, W, low, high, as_stream(stream));
+}
+
+int ub_blur_canny(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int low, int high, uint8_t* dst, void* stream) {
+  NEED_CTX(ctx);
+  RUN(check_frame_shape(ctx, B, H, W));
+  return blur_canny(ctx, gray, dst, B, H, W, low, high, as_stream(stream));
 }
 
 int ub_morph(ub_ctx* ctx, int op, int k, const uint8_t* src, int B, int H, int W, int value, uint8_t* dst, void* stream) {

@@ -190,6 +190,10 @@ __device__ __forceinline__ int run_start_of(uint32_t u, int i) {
   return i == 0 ? 0 : i - __clz(~(u << (32 - i)));
 }
 
+}  // namespace s2
+#include "edge_fused.cuh"
+namespace s2 {
+
 // pack + one union-find entry per run.  strong (nullable): bits of pixels == 2 (Canny strong candidates)
 __global__ void __launch_bounds__(256) k_cclb_init(const uint8_t* __restrict__ src, uint32_t* __restrict__ bits, uint32_t* __restrict__ strong,
                                                    int* __restrict__ lab, int H, int W, int Wd) {
@@ -492,15 +496,52 @@ static int cclb_label(ub_ctx* ctx, const uint8_t* src, uint32_t* bits, uint32_t*
   return UB_OK;
 }
 
+// The fused four-pixel kernels need word-aligned rows (edge_fused.cuh); UB_EDGE_FUSED=0 keeps the per-pixel kernels.
+static bool edge_fused_ok(const void* a, const void* b, int W) {
+  static const int env = getenv("UB_EDGE_FUSED") ? atoi(getenv("UB_EDGE_FUSED")) : 1;
+  return env && W % 4 == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 3) == 0;
+}
+static dim3 edge_fused_grid(int B, int H, int W) { return dim3(cdiv(W, EF_TW), cdiv(H, EF_TH), B); }
+
 int gaussian5(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_STENCIL, st);
+  if (edge_fused_ok(src, dst, W)) {
+    k_edge_fused<2><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, dst, nullptr, nullptr, nullptr, H, W, (W + 31) / 32, 0, 0);
+    UB_CHECK_LAUNCH(ctx);
+    return UB_OK;
+  }
   k_gauss5<<<dim3(cdiv(W, GT_W), cdiv(H, GT_H), B), dim3(GT_W, 4), 0, st>>>(src, dst, H, W);
   UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
 
 // cv2.Canny: candidates (stencil) then hysteresis (union-find).  cand: u8 scratch, lab: i32 scratch.
+// blur != 0: src is the gray plane and the 5x5 blur is done inside the fused kernel (GaussianBlur + Canny of the burr stage).
+static int canny_fused(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int* lab, int B, int H, int W, int low, int high, int blur, cudaStream_t st) {
+  const int Wd = (W + 31) / 32;
+  const size_t nwords = (size_t)B * H * Wd;
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  uint32_t* strong = bits + nwords;
+  uint8_t* flag = reinterpret_cast<uint8_t*>(ctx->d_comp);
+  {
+    TimeScope ts(ctx, UB_T_STENCIL, st);
+    if (blur) k_edge_fused<1><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, nullptr, bits, strong, lab, H, W, Wd, low, high);
+    else k_edge_fused<0><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, nullptr, bits, strong, lab, H, W, Wd, low, high);
+    UB_CHECK_LAUNCH(ctx);
+  }
+  TimeScope ts(ctx, UB_T_CCL, st);
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  k_cclb_merge<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd);
+  k_cclb_flatten<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, nullptr, 0);
+  UB_CUDA(ctx, cudaMemsetAsync(flag, 0, (size_t)B * H * W, st));
+  k_cclb_hyst_mark<<<g, dim3(32, 8), 0, st>>>(bits, strong, lab, flag, H, W, Wd);
+  k_cclb_hyst_final<<<g, dim3(32, 8), 0, st>>>(bits, lab, flag, dst, H, W, Wd);
+  UB_CHECK_LAUNCH_N(ctx, 4);
+  return UB_OK;
+}
+
 int canny(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, uint8_t* cand, int* lab, int B, int H, int W, int low, int high, cudaStream_t st) {
+  if (edge_fused_ok(src, src, W)) return canny_fused(ctx, src, dst, lab, B, H, W, low, high, 0, st);
   dim3 gpix(cdiv(W, 256), H, B);
   {
     TimeScope ts(ctx, UB_T_STENCIL, st);
@@ -529,6 +570,13 @@ int canny(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, uint8_t* cand, int* lab
   k_hyst_final<<<gpix, 256, 0, st>>>(lab, dst, H, W);
   UB_CHECK_LAUNCH_N(ctx, 2);
   return UB_OK;
+}
+
+// GaussianBlur((5,5),1.0) -> Canny(low, high); scratch: d_tmp[0] (blurred plane), d_tmp[2], d_lab[0..1], d_comp
+int blur_canny(ub_ctx* ctx, const uint8_t* gray, uint8_t* dst, int B, int H, int W, int low, int high, cudaStream_t st) {
+  if (edge_fused_ok(gray, gray, W)) return canny_fused(ctx, gray, dst, ctx->d_lab[0], B, H, W, low, high, 1, st);
+  RUN(gaussian5(ctx, gray, ctx->d_tmp[0], B, H, W, st));
+  return canny(ctx, ctx->d_tmp[0], dst, ctx->d_tmp[2], ctx->d_lab[0], B, H, W, low, high, st);
 }
 
 int enh_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int mode, int sobel_t, int lap_t,
@@ -570,10 +618,9 @@ int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels
 // First half of the burr stage: the edge map, which depends on the gray frame only (not on the net's masks), so
 // ub_pipeline runs it on a second stream beside the network.  Result in ctx->d_tmp[1].
 int burr_edges(ub_ctx* ctx, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& P, cudaStream_t st) {
-  uint8_t *t0 = ctx->d_tmp[0], *t1 = ctx->d_tmp[1], *t2 = ctx->d_tmp[2];
+  uint8_t* t1 = ctx->d_tmp[1];
   // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
-  RUN(gaussian5(ctx, gray, t0, B, H, W, st));
-  RUN(canny(ctx, t0, t1, t2, ctx->d_lab[0], B, H, W, P.canny_low, P.canny_high, st));
+  RUN(blur_canny(ctx, gray, t1, B, H, W, P.canny_low, P.canny_high, st));
   if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
   return UB_OK;
 }
