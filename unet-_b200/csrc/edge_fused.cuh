@@ -25,6 +25,7 @@ namespace s2 {
 
 constexpr int EF_TW = 160, EF_TH = 32;
 constexpr int EF_CW = EF_TW / 4 + 2;            // 42 column words (one word of halo each side)
+constexpr int EF_TR = 256 / EF_CW;               // 6 row lanes
 constexpr int EF_CWP = EF_CW + 2;               // + one pad word each side (read by the neighbours' taps, never used)
 constexpr int EF_SMEM_A = (EF_TH + 4) * EF_CWP * 8;   // vv; later gx
 constexpr int EF_SMEM_G = (EF_TH + 8) * EF_CW * 4;    // g (6720 B, a multiple of 16)
@@ -57,23 +58,34 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
   const int x0 = blockIdx.x * EF_TW, y0 = blockIdx.y * EF_TH;
   const size_t fbase = (size_t)blockIdx.z * H * W;
   const uint8_t* img = src + fbase;
+  // (tr, cw): a thread keeps its column word and walks rows with stride EF_TR -- no divisions, column terms once
+  const int tr = tid / EF_CW, cw = tid - tr * EF_CW;         // tr < EF_TR for tid < 252
+  const bool act = tr < EF_TR;
+  const int xw = x0 - 4 + 4 * cw;                            // image x of the word's first pixel
+  const bool xin = xw >= 0 && xw + 3 < W;
 
   if (MODE != 0) {
     // ---- L: gray words, REFLECT_101 ----
-    for (int i = tid; i < (EF_TH + 8) * EF_CW; i += 256) {
-      const int r = i / EF_CW, cw = i - r * EF_CW;
-      const uint8_t* row = img + (size_t)reflect101(y0 - 4 + r, H) * W;
-      const int x = x0 - 4 + 4 * cw;
-      uint32_t w;
-      if (x >= 0 && x + 3 < W) w = *reinterpret_cast<const uint32_t*>(row + x);
-      else w = (uint32_t)row[reflect101(x, W)] | ((uint32_t)row[reflect101(x + 1, W)] << 8) |
-               ((uint32_t)row[reflect101(x + 2, W)] << 16) | ((uint32_t)row[reflect101(x + 3, W)] << 24);
-      g[r][cw] = w;
+    if (act && xin) {                                // interior words: one aligned 32-bit load per row
+      const uint8_t* p = img + xw;
+      if (y0 >= 4 && y0 + EF_TH + 3 < H) {
+        p += (y0 - 4) * W;
+        for (int r = tr; r < EF_TH + 8; r += EF_TR) g[r][cw] = *reinterpret_cast<const uint32_t*>(p + r * W);
+      } else {
+        for (int r = tr; r < EF_TH + 8; r += EF_TR) g[r][cw] = *reinterpret_cast<const uint32_t*>(p + reflect101(y0 - 4 + r, H) * W);
+      }
+    } else if (act) {                                // words that straddle the left / right image border
+      int xs[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) xs[k] = reflect101(xw + k, W);
+      for (int r = tr; r < EF_TH + 8; r += EF_TR) {
+        const uint8_t* row = img + reflect101(y0 - 4 + r, H) * W;
+        g[r][cw] = (uint32_t)row[xs[0]] | ((uint32_t)row[xs[1]] << 8) | ((uint32_t)row[xs[2]] << 16) | ((uint32_t)row[xs[3]] << 24);
+      }
     }
     __syncthreads();
     // ---- V: vertical taps, four output rows per thread (eight input rows in registers) ----
-    for (int i = tid; i < ((EF_TH + 4) / 4) * EF_CW; i += 256) {
-      const int grp = i / EF_CW, cw = i - grp * EF_CW;
+    for (int grp = tr; grp < (EF_TH + 4) / 4 && act; grp += EF_TR) {
       uint32_t lo[8], hi[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
@@ -91,8 +103,7 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
     }
     __syncthreads();
     // ---- H: horizontal taps as 16-bit x 8-bit dot products; pixel j of the word needs v[j-2..j+2] ----
-    for (int i = tid; i < (EF_TH + 4) * EF_CW; i += 256) {
-      const int r = i / EF_CW, cw = i - r * EF_CW;
+    for (int r = tr; r < EF_TH + 4 && act; r += EF_TR) {
       const uint32_t a = vv[r][cw].y;                // v[-2], v[-1]   (pad words hold garbage: only unused outputs see it)
       const uint2 m = vv[r][cw + 1];                 // v[0..1], v[2..3]
       const uint32_t n = vv[r][cw + 2].x;            // v[4], v[5]
@@ -106,11 +117,9 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
     }
     __syncthreads();
     if (MODE == 2) {
-      for (int i = tid; i < EF_TH * (EF_TW / 4); i += 256) {
-        const int r = i / (EF_TW / 4), c = i - r * (EF_TW / 4);
-        const int y = y0 + r, x = x0 + 4 * c;
-        if (y < H && x < W) *reinterpret_cast<uint32_t*>(blur_out + fbase + (size_t)y * W + x) = bb[r + 2][c + 2];
-      }
+      if (act && cw >= 1 && cw <= EF_TW / 4 && xw < W)
+        for (int r = tr; r < EF_TH && y0 + r < H; r += EF_TR)
+          *reinterpret_cast<uint32_t*>(blur_out + fbase + (uint32_t)((y0 + r) * W + xw)) = bb[r + 2][cw + 1];
       return;
     }
     // ---- F: Sobel wants BORDER_REPLICATE of the BLURRED plane (block-uniform conditions) ----
@@ -134,22 +143,23 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
     }
   } else {
     // ---- MODE 0: the plane as given, BORDER_REPLICATE ----
-    for (int i = tid; i < (EF_TH + 4) * EF_CW; i += 256) {
-      const int r = i / EF_CW, cw = i - r * EF_CW;
-      const uint8_t* row = img + (size_t)clampi(y0 - 2 + r, H) * W;
-      const int x = x0 - 4 + 4 * cw;
-      uint32_t w;
-      if (x >= 0 && x + 3 < W) w = *reinterpret_cast<const uint32_t*>(row + x);
-      else w = (uint32_t)row[clampi(x, W)] | ((uint32_t)row[clampi(x + 1, W)] << 8) |
-               ((uint32_t)row[clampi(x + 2, W)] << 16) | ((uint32_t)row[clampi(x + 3, W)] << 24);
-      bb[r][cw + 1] = w;
+    if (act && xin) {
+      const uint8_t* p = img + xw;
+      for (int r = tr; r < EF_TH + 4; r += EF_TR) bb[r][cw + 1] = *reinterpret_cast<const uint32_t*>(p + clampi(y0 - 2 + r, H) * W);
+    } else if (act) {
+      int xs[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) xs[k] = clampi(xw + k, W);
+      for (int r = tr; r < EF_TH + 4; r += EF_TR) {
+        const uint8_t* row = img + clampi(y0 - 2 + r, H) * W;
+        bb[r][cw + 1] = (uint32_t)row[xs[0]] | ((uint32_t)row[xs[1]] << 8) | ((uint32_t)row[xs[2]] << 16) | ((uint32_t)row[xs[3]] << 24);
+      }
     }
     __syncthreads();
   }
 
   // ---- S: Sobel, two magnitude rows per thread.  Lanes: E = (p0, p2), O = (p1, p3). ----
-  for (int i = tid; i < ((EF_TH + 2) / 2) * EF_CW; i += 256) {
-    const int grp = i / EF_CW, cw = i - grp * EF_CW;
+  for (int grp = tr; grp < (EF_TH + 2) / 2 && act; grp += EF_TR) {
     uint32_t w0[4], w1[4], w2[4], w3[4], rse[4], rso[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -161,8 +171,6 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
       rse[k] = w0[k] + 2u * w1[k] + w2[k];                     // horizontal smooth, lanes <= 1020
       rso[k] = w1[k] + 2u * w2[k] + w3[k];
     }
-    const int x = x0 - 4 + 4 * cw;
-    const bool xin = x >= 0 && x < W;
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const int mr = 2 * grp + k, y = y0 - 1 + mr;
@@ -181,9 +189,8 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
   __syncthreads();
 
   // ---- N: non-maximum suppression -> 0 none / 1 weak / 2 strong, one byte per pixel in cc ----
-  for (int i = tid; i < EF_TH * (EF_TW / 4); i += 256) {
-    const int r = i / (EF_TW / 4), c = i - r * (EF_TW / 4);
-    const int mr = r + 1, cw = c + 1;
+  for (int r = tr; r < EF_TH && act && cw >= 1 && cw <= EF_TW / 4; r += EF_TR) {
+    const int mr = r + 1, c = cw - 1;
     const uint2 own = mm[mr][cw];
     uint32_t out = 0u;
     const uint32_t mx = __vmaxu2(own.x, own.y);
