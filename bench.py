@@ -318,6 +318,14 @@ def main():
     args = ap.parse_args()
     if args.workload == "enhanced" and args.batch == 64:
         args.batch = 16
+    # The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner
+    # from C), so fd 1 is pointed at stderr for the run and the JSON line goes to the saved descriptor.
+    sys.stdout.flush()
+    real_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    global print
+    _print = print
+    print = lambda *a, **k: _print(*a, **{**k, "file": real_out})      # noqa: A001  (both JSON prints below)
     if args.impl == "reference":
         run_reference(args)
     else:

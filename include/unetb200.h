@@ -105,6 +105,13 @@ int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, in
                          int H, int W, const ub_roi* roi, uint8_t* pred_dev,
                          uint8_t* mask_cable_dev, uint8_t* mask_tape_dev, void* stream);
 
+/* Visualisation blend of visualize_two_stage (infer_two_stage_burr.py:134-154; infer_enhanced_burr.py:157-175):
+ * the four cv2.addWeighted steps -- dim outside the ROI (0.7/0.3), tint cable (0,255,0) and tape (255,0,0) at
+ * 0.6/0.4 and burr (255,0,255) at 0.5/0.5 -- in one pass, bit-exact with OpenCV's binary32 fma + round-half-even.
+ * frames / out u8 [B,H,W,3] BGR, masks u8 [B,H,W] (non-zero = set).  Boxes, contours and text stay with the caller. */
+int ub_overlay(ub_ctx* ctx, const uint8_t* frames_bgr_dev, const uint8_t* mask_cable_dev, const uint8_t* mask_tape_dev,
+               const uint8_t* mask_burr_dev, int B, int H, int W, const ub_roi* roi, uint8_t* out_bgr_dev, void* stream);
+
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */

@@ -361,3 +361,36 @@ def sharpen3(bgr: np.ndarray) -> np.ndarray:
                 acc = acc - p[dy:dy + h, dx:dx + w]
         out[..., c] = np.clip(acc, 0, 255).astype(np.uint8)
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# cv2.addWeighted on uint8 (visualize_two_stage, infer_two_stage_burr.py:141,152-154): OpenCV's SIMD
+# kernel is fma(a, alpha, fma(b, beta, gamma)) in binary32, then round-half-even and saturate.
+# With gamma = 0 the inner fma is the rounded product b*beta.  Pinned on all 256x256 operand pairs
+# for the three weight pairs the reference uses (tests/test_oracle_cvnp.py).
+# ----------------------------------------------------------------------------------------------
+def add_weighted_u8(a: np.ndarray, alpha: float, b: np.ndarray, beta: float) -> np.ndarray:
+    al, be = np.float32(alpha), np.float32(beta)
+    inner = (b.astype(np.float64) * np.float64(be)).astype(np.float32)            # fma(b, beta, 0)
+    v = (a.astype(np.float64) * np.float64(al) + inner.astype(np.float64)).astype(np.float32)   # one rounding = fma
+    return np.clip(np.rint(v), 0, 255).astype(np.uint8)
+
+
+OVERLAY_COLORS = ((0, 255, 0), (255, 0, 0), (255, 0, 255))     # cable, tape, burr in BGR (CLASS_COLORS[1..3], :22-26)
+
+
+def overlay_blend(frame: np.ndarray, mask_cable, mask_tape, mask_burr, roi) -> np.ndarray:
+    """The four addWeighted steps of visualize_two_stage (infer_two_stage_burr.py:134-154; the same lines in
+    infer_enhanced_burr.py:157-175): dim outside the ROI, then tint cable / tape / burr."""
+    x1, y1, x2, y2 = roi
+    dimmed = frame.copy()
+    outside = np.ones(frame.shape[:2], bool)
+    outside[y1:y2, x1:x2] = False
+    dimmed[outside] = 0
+    out = add_weighted_u8(frame, 0.7, dimmed, 0.3)
+    for mask, colour, a, b in ((mask_cable, OVERLAY_COLORS[0], 0.6, 0.4), (mask_tape, OVERLAY_COLORS[1], 0.6, 0.4),
+                               (mask_burr, OVERLAY_COLORS[2], 0.5, 0.5)):
+        tint = np.zeros_like(out)
+        tint[mask > 0] = colour
+        out = add_weighted_u8(out, a, tint, b)
+    return out

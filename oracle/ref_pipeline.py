@@ -247,3 +247,18 @@ def stats_line(idx, frame_no, total, cable_px, tape_px, burr_px, roi):
     status = "[BURR!]" if burr_px > 0 else "[OK]"
     return (f"[{idx:4d}] Frame {frame_no}/{total} {status} | "
             f"Cable:{r[0]:5.1f}% Tape:{r[1]:5.1f}% Burr:{r[2]:5.1f}%")
+
+
+def visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
+    """visualize_two_stage (infer_two_stage_burr.py:130-170) = visualize_detection (infer_enhanced_burr.py:150-192):
+    the addWeighted chain restated in oracle/cvnp.py (overlay_blend), then cv2's own drawing calls."""
+    from . import cvnp
+    x1, y1, x2, y2 = roi
+    out = np.ascontiguousarray(cvnp.overlay_blend(frame, mask_cable, mask_tape, mask_burr, roi))
+    if draw_roi_box:
+        cv2.rectangle(out, (x1, y1), (x2, y2), (0, 255, 255), 2)
+        cv2.putText(out, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, (0, 255, 255), 2)
+    for mask, colour, thick in ((mask_cable, (0, 255, 0), 2), (mask_tape, (255, 0, 0), 2), (mask_burr, (255, 0, 255), 3)):
+        contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
+        cv2.drawContours(out, contours, -1, colour, thick)
+    return out

@@ -38,3 +38,23 @@ def golden_frames(golden_stage2):
         assert zlib.crc32(fr.tobytes()) == int(g[f"{k}_crc"]), \
             f"synthetic frame '{k}' no longer matches the golden fixture; rerun tests/golden/make_golden.py"
     return frames
+
+
+@pytest.fixture(scope="session")
+def golden_viz():
+    return np.load(os.path.join(GOLDEN, "viz.npz"))
+
+
+def viz_inputs(tag):
+    """Inputs behind tests/golden/viz.npz (same construction as make_golden.viz_inputs; the crc pins them)."""
+    import unet_b200.synth as S
+    from oracle import ref_pipeline as R
+    if tag == "full":
+        fr, (h, w) = S.frames_cable(1, 448, 800, seed=6)[0], (448, 800)
+    else:
+        fr, (h, w) = S.frames_noise(1, 90, 158, seed=7)[0], (90, 158)
+    roi = R.map_roi((w, h))
+    mc = S.mask_cable_synth(h, w, roi)
+    mt = (S.mask_blobs(h, w, seed=8, fill=0.02) & (1 - mc)).astype(np.uint8)
+    mb = S.mask_blobs(h, w, seed=9, fill=0.004)
+    return fr, mc, mt, mb, roi

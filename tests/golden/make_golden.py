@@ -149,13 +149,50 @@ def enhance():
     np.savez_compressed(os.path.join(HERE, "enhance.npz"), **out)
 
 
+def viz_inputs(tag):
+    """Seeded frames + masks for the visualisation vectors (regenerated identically in the tests)."""
+    if tag == "full":
+        fr = S.frames_cable(1, 448, 800, seed=6)[0]
+        h, w = 448, 800
+    else:
+        fr = S.frames_noise(1, 90, 158, seed=7)[0]
+        h, w = 90, 158
+    roi = T.map_roi_to_original((w, h), (512, 512))
+    mc = S.mask_cable_synth(h, w, roi)
+    mt = (S.mask_blobs(h, w, seed=8, fill=0.02) & (1 - mc)).astype(np.uint8)
+    mb = S.mask_blobs(h, w, seed=9, fill=0.004)
+    return fr, mc, mt, mb, roi
+
+
+def viz():
+    """visualize_two_stage (infer_two_stage_burr.py:130-170) and visualize_detection (infer_enhanced_burr.py:150-192)."""
+    import zlib
+    out = {"versions": VERS}
+    for tag in ("full", "small"):
+        fr, mc, mt, mb, roi = viz_inputs(tag)
+        a = T.visualize_two_stage(fr, mc, mt, mb, roi, draw_roi_box=True)
+        b = T.visualize_two_stage(fr, mc, mt, mb, roi, draw_roi_box=False)
+        e = E.visualize_detection(fr, mc, mt, mb, dict(zip(("x1", "y1", "x2", "y2"), roi)))
+        assert np.array_equal(a, e)
+        out[f"{tag}_in_crc"] = np.array(zlib.crc32(fr.tobytes() + mc.tobytes() + mt.tobytes() + mb.tobytes()), np.uint32)
+        out[f"{tag}_box_crc"] = np.array(zlib.crc32(a.tobytes()), np.uint32)
+        out[f"{tag}_nobox_crc"] = np.array(zlib.crc32(b.tobytes()), np.uint32)
+        if tag == "small":
+            out["small_box"] = a
+        else:
+            out["full_box_crop"] = a[160:224, 200:296].copy()
+    np.savez_compressed(os.path.join(HERE, "viz.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["stage2", "net", "enhance"]
+    which = sys.argv[1:] or ["stage2", "net", "enhance", "viz"]
     if "stage2" in which:
         stage2()
     if "net" in which:
         net()
     if "enhance" in which:
         enhance()
-    for f in ("stage2.npz", "net.npz", "enhance.npz"):
+    if "viz" in which:
+        viz()
+    for f in ("stage2.npz", "net.npz", "enhance.npz", "viz.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)))

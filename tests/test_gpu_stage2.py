@@ -174,3 +174,38 @@ def test_function_contract():
     same("preprocess_image", x.numpy(), R.preprocess(fr).numpy())
     assert U.map_roi_to_original((800, 448)) == (218, 0, 421, 448)
     same("bgr2gray", U.bgr2gray(fr), gray)
+
+
+@pytest.mark.parametrize("hw", [(448, 800), (90, 158), (33, 67)])
+def test_overlay_blend_vs_oracle(ctx, hw):
+    """ub_overlay == the four cv2.addWeighted steps of visualize_two_stage (oracle: cvnp.overlay_blend, which
+    tests/test_oracle_cvnp.py pins against cv2 on every operand pair)."""
+    h, w = hw
+    fr = np.concatenate([S.frames_cable(1, h, w, seed=3), S.frames_noise(2, h, w, seed=4)])
+    roi = R.map_roi((w, h))
+    mc = np.stack([S.mask_cable_synth(h, w, roi)] * 3)
+    mt = np.stack([S.mask_blobs(h, w, seed=8 + i, fill=0.3) for i in range(3)])
+    mb = np.stack([S.mask_blobs(h, w, seed=20 + i, fill=0.1) * 255 for i in range(3)]).astype(np.uint8)
+    got = ctx.overlay(dev(fr), dev(mc), dev(mt), dev(mb), roi)
+    want = np.stack([cvnp.overlay_blend(fr[i], mc[i], mt[i], mb[i], roi) for i in range(3)])
+    same("overlay", got, want)
+    for i in range(3):       # and the oracle is cv2 itself
+        dimmed = fr[i].copy(); outside = np.ones((h, w), bool); outside[roi[1]:roi[3], roi[0]:roi[2]] = False; dimmed[outside] = 0
+        ref = cv2.addWeighted(fr[i], 0.7, dimmed, 0.3, 0)
+        for m, col, a, b in ((mc[i], (0, 255, 0), .6, .4), (mt[i], (255, 0, 0), .6, .4), (mb[i], (255, 0, 255), .5, .5)):
+            tint = np.zeros_like(ref); tint[m > 0] = col
+            ref = cv2.addWeighted(ref, a, tint, b, 0)
+        same("overlay_cv2", got[i], ref)
+
+
+@pytest.mark.parametrize("tag", ["full", "small"])
+def test_visualize_two_stage_golden(golden_viz, tag):
+    """ops.visualize_two_stage (device blend + cv2 drawing) == the real reference's output, byte for byte."""
+    import zlib
+    from conftest import viz_inputs
+    from unet_b200 import ops as U
+    fr, mc, mt, mb, roi = viz_inputs(tag)
+    box = U.visualize_two_stage(fr, mc, mt, mb, roi, True)
+    nobox = U.visualize_two_stage(fr, mc, mt, mb, roi, False)
+    assert zlib.crc32(box.tobytes()) == int(golden_viz[f"{tag}_box_crc"])
+    assert zlib.crc32(nobox.tobytes()) == int(golden_viz[f"{tag}_nobox_crc"])

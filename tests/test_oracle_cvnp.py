@@ -85,3 +85,16 @@ def test_filter_integer_form():
         w, h = int(rng.integers(1, 60)), int(rng.integers(1, 60))
         for r in (5, 6):
             assert (max(w, h) / (min(w, h) + 1e-6) < float(r)) == (max(w, h) <= r * min(w, h))
+
+
+@pytest.mark.parametrize("alpha,beta", [(0.7, 0.3), (0.6, 0.4), (0.5, 0.5)])
+def test_add_weighted_all_operand_pairs(alpha, beta):
+    """cv2.addWeighted on u8 for the reference's three weight pairs, all 256 x 256 operand pairs, and a frame-sized
+    3-channel array (OpenCV's SIMD body)."""
+    a = np.repeat(np.arange(256, dtype=np.uint8)[:, None], 256, 1)
+    b = np.ascontiguousarray(a.T)
+    assert np.array_equal(cvnp.add_weighted_u8(a, alpha, b, beta), cv2.addWeighted(a, alpha, b, beta, 0))
+    rng = np.random.default_rng(0)
+    x = rng.integers(0, 256, (120, 203, 3), dtype=np.uint8)
+    y = rng.integers(0, 256, (120, 203, 3), dtype=np.uint8)
+    assert np.array_equal(cvnp.add_weighted_u8(x, alpha, y, beta), cv2.addWeighted(x, alpha, y, beta, 0))

@@ -76,3 +76,21 @@ def test_frame_step_matches_reference(golden_net):
         assert np.array_equal(res["mask_tape"], g["step_mask_tape"])
         assert np.array_equal(res["mask_burr"], g["step_mask_burr"])
         assert [res["cable_px"], res["tape_px"], res["burr_px"]] == list(g["step_counts"])
+
+
+@pytest.mark.parametrize("tag", ["full", "small"])
+def test_visualisation_matches_reference(golden_viz, tag):
+    """oracle visualize_two_stage == the real reference's visualize_two_stage / visualize_detection."""
+    import zlib
+    from conftest import viz_inputs
+    fr, mc, mt, mb, roi = viz_inputs(tag)
+    g = golden_viz
+    assert zlib.crc32(fr.tobytes() + mc.tobytes() + mt.tobytes() + mb.tobytes()) == int(g[f"{tag}_in_crc"])
+    box = R.visualize_two_stage(fr, mc, mt, mb, roi, True)
+    nobox = R.visualize_two_stage(fr, mc, mt, mb, roi, False)
+    assert zlib.crc32(box.tobytes()) == int(g[f"{tag}_box_crc"])
+    assert zlib.crc32(nobox.tobytes()) == int(g[f"{tag}_nobox_crc"])
+    if tag == "small":
+        assert np.array_equal(box, g["small_box"])
+    else:
+        assert np.array_equal(box[160:224, 200:296], g["full_box_crop"])

@@ -40,7 +40,13 @@ def timed(fn):
     return e0.elapsed_time(e1) / reps
 
 
+frames3 = torch.from_numpy(np.concatenate([base] * (B // 16))).cuda()
+mask_t = torch.from_numpy(np.stack([S.mask_blobs(H, W, seed=3, fill=0.02)] * B)).cuda()
+mask_b = torch.from_numpy(np.stack([S.mask_blobs(H, W, seed=4, fill=0.004)] * B)).cuda()
+roi = (218, 0, 421, 448)
 rows = [
+    ("overlay blend (4 x addWeighted, ub_overlay)", lambda: ctx.overlay(frames3, mask, mask_t, mask_b, roi), 9 * P),
+    ("gray (ub_preprocess, gray only)", lambda: ctx.preprocess(frames3, want_x=False, want_gray=True), 4 * P),
     ("gaussian5 (k_edge_fused<2>)", lambda: ctx.gaussian5(gray), 2 * P),
     ("blur_canny, hysteresis included", lambda: ctx.blur_canny(gray, 50, 150), 2 * P),
     ("burr stage (edges + band + morphology + CCL + filter)", lambda: ctx.burr(gray, mask), 3 * P),

@@ -55,6 +55,7 @@ SIGNATURES = {
     "ub_preprocess": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "ub_normalize_frames": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P]),
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
+    "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -221,6 +222,16 @@ class Context:
         return pred, cable, tape
 
     # -- stage 2 operators
+    def overlay(self, frames, mask_cable, mask_tape, mask_burr, roi):
+        """Blend chain of visualize_two_stage: frames u8 [B,H,W,3], masks u8 [B,H,W] -> u8 [B,H,W,3]."""
+        b, h, w, _ = frames.shape
+        out = torch.empty_like(frames)
+        r = Roi(*[int(v) for v in roi])
+        self._check(lib().ub_overlay(self._h, self._dev(frames, torch.uint8), self._dev(mask_cable, torch.uint8),
+                                     self._dev(mask_tape, torch.uint8), self._dev(mask_burr, torch.uint8), b, h, w,
+                                     C.byref(r), out.data_ptr(), self.stream))
+        return out
+
     def _u8op(self, fn, src, *args):
         b, h, w = src.shape
         dst = torch.empty_like(src)

@@ -89,30 +89,11 @@ def load_state_dict(path):
 
 
 # ------------------------------------------------------------------------------------- drawing
-def draw_overlay(frame, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
-    """The reference's visualisation (infer_two_stage_burr.py:130-170, infer_enhanced_burr.py:150-192):
-    dim outside the ROI, tint the three masks, ROI box, contours.  Host-side presentation only."""
-    import cv2
-    x1, y1, x2, y2 = roi
-    out = frame.copy()
-    dimmed = out.copy()
-    outside = np.ones(frame.shape[:2], bool)
-    outside[y1:y2, x1:x2] = False
-    dimmed[outside] = 0
-    out = cv2.addWeighted(out, 0.7, dimmed, 0.3, 0)
-    layers = ((mask_cable, CLASS_COLORS[1], 0.6, 0.4), (mask_tape, CLASS_COLORS[2], 0.6, 0.4),
-              (mask_burr, CLASS_COLORS[3], 0.5, 0.5))
-    for mask, colour, a, b in layers:
-        tint = np.zeros_like(out)
-        tint[mask > 0] = colour
-        out = cv2.addWeighted(out, a, tint, b, 0)
-    if draw_roi_box:
-        cv2.rectangle(out, (x1, y1), (x2, y2), (0, 255, 255), 2)
-        cv2.putText(out, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, (0, 255, 255), 2)
-    for mask, colour, thick in ((mask_cable, (0, 255, 0), 2), (mask_tape, (255, 0, 0), 2), (mask_burr, (255, 0, 255), 3)):
-        contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
-        cv2.drawContours(out, contours, -1, colour, thick)
-    return out
+def draw_overlay(blended, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
+    """Second half of the reference's visualisation (infer_two_stage_burr.py:156-170, infer_enhanced_burr.py:177-190):
+    ROI box and contours over the frame the device already blended (ub_overlay: ROI dimming + the three tints)."""
+    from .ops import draw_annotations
+    return draw_annotations(np.ascontiguousarray(blended), mask_cable, mask_tape, mask_burr, roi, draw_roi_box)
 
 
 def draw_text(img, info_text, defect_text):
@@ -167,7 +148,7 @@ class DeviceStep:
 
     def __call__(self, frames_np):
         """frames_np: list of [h,w,3] uint8 host frames (source resolution).
-        -> stats int32 [n,4] (numpy), and if want_masks (frames [n,H,W,3], masks [n,3,H,W]) on the host."""
+        -> stats int32 [n,4] (numpy), and if want_masks (blended frames [n,H,W,3], masks [n,3,H,W]) on the host."""
         torch = self.torch
         n = len(frames_np)
         for i, f in enumerate(frames_np):
@@ -180,8 +161,10 @@ class DeviceStep:
                 d = self.pipe.ctx.enhance(d)
             stats, masks = self.pipe.run(d, want_masks=self.want_masks)
             stats = stats.cpu().numpy()
-            if self.want_masks:
-                return stats, d.cpu().numpy(), masks.cpu().numpy()
+            if self.want_masks:          # blended frames for the result video: the addWeighted chain runs on the device
+                blend = self.pipe.ctx.overlay(d, masks[:, 0].contiguous(), masks[:, 1].contiguous(), masks[:, 2].contiguous(),
+                                              self.pipe.roi)
+                return stats, blend.cpu().numpy(), masks.cpu().numpy()
         return stats, None, None
 
 

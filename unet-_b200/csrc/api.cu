@@ -40,6 +40,7 @@ TimeScope::~TimeScope() {
 // forward declarations of functions defined in other translation units
 void resize_cache_free(ub_ctx* ctx);
 int normalize_frames_impl(ub_ctx*, const uint8_t*, int, int, int, int, uint8_t*, int, int, cudaStream_t);
+int overlay_impl(ub_ctx*, const uint8_t*, const uint8_t*, const uint8_t*, const uint8_t*, int, int, int, ub_roi, uint8_t*, cudaStream_t);
 int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t);
 int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
 int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
@@ -285,6 +286,13 @@ static int check_frame_shape(ub_ctx* ctx, int B, int H, int W) {
   if (B < 1 || B > ctx->max_batch || H < 1 || W < 1 || (size_t)H * W > (size_t)ctx->frame_h * ctx->frame_w)
     return ub_fail(ctx, UB_ERR_ARG, "frames %dx%dx%d exceed the context (%d x %dx%d)", B, H, W, ctx->max_batch, ctx->frame_h, ctx->frame_w);
   return UB_OK;
+}
+
+int ub_overlay(ub_ctx* ctx, const uint8_t* frames, const uint8_t* mc, const uint8_t* mt, const uint8_t* mb, int B, int H, int W,
+               const ub_roi* roi, uint8_t* out, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || !mc || !mt || !mb || !out || !roi || B < 1 || H < 1 || W < 1) return ub_fail(ctx, UB_ERR_ARG, "ub_overlay: null pointer or empty shape");
+  return overlay_impl(ctx, frames, mc, mt, mb, B, H, W, *roi, out, as_stream(stream));
 }
 
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {

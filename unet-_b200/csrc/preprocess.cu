@@ -135,6 +135,65 @@ __global__ void k_gray(const uint8_t* __restrict__ frames, uint8_t* __restrict__
   }
 }
 
+// One cv2.addWeighted step on a u8 sample: fma(a, alpha, b*beta) in binary32, round-half-even (oracle/cvnp.py: add_weighted_u8)
+__device__ __forceinline__ float aw_step(float a, float alpha, float b, float beta) {
+  return rintf(__fmaf_rn(a, alpha, __fmul_rn(b, beta)));
+}
+// The blend chain of visualize_two_stage (infer_two_stage_burr.py:134-154).  The four steps only depend on the sample,
+// its channel and four flags (inside the ROI, cable, tape, burr), so a CTA first tabulates the whole chain --
+// 16 flag sets x 3 channels x 256 values = 12 KB of shared memory, 48 chain evaluations per thread -- and then
+// maps OV_ROWS image rows through it, four pixels (12 B of BGR + 3 mask words) per thread and step.
+constexpr int OV_ROWS = 64;
+__device__ __forceinline__ uint8_t ov_chain(float v, int ch, int flags) {
+  v = aw_step(v, 0.7f, (flags & 1) ? v : 0.f, 0.3f);
+  v = aw_step(v, 0.6f, ((flags & 2) && ch == 1) ? 255.f : 0.f, 0.4f);      // cable (0,255,0)
+  v = aw_step(v, 0.6f, ((flags & 4) && ch == 0) ? 255.f : 0.f, 0.4f);      // tape  (255,0,0)
+  v = aw_step(v, 0.5f, ((flags & 8) && ch != 1) ? 255.f : 0.f, 0.5f);      // burr  (255,0,255)
+  return (uint8_t)fminf(fmaxf(v, 0.f), 255.f);
+}
+__global__ void __launch_bounds__(256) k_overlay(const uint8_t* __restrict__ frames, const uint8_t* __restrict__ mc,
+                                                 const uint8_t* __restrict__ mt, const uint8_t* __restrict__ mb,
+                                                 uint8_t* __restrict__ out, int H, int W, ub_roi roi) {
+  __shared__ uint8_t lut[16 * 3 * 256];
+  for (int t = 0; t < 48; ++t) lut[t * 256 + threadIdx.x] = ov_chain((float)threadIdx.x, t % 3, t / 3);
+  __syncthreads();
+  const int y0 = blockIdx.x * OV_ROWS, y1 = min(y0 + OV_ROWS, H);
+  const size_t fbase = (size_t)blockIdx.y * H * W;
+  const int wq = (W + 3) / 4;
+  const bool vec = (W & 3) == 0;                       // rows (and frames) start on word boundaries
+  for (int i = threadIdx.x; i < (y1 - y0) * wq; i += 256) {
+    const int r = i / wq, x = 4 * (i - r * wq), y = y0 + r;
+    const size_t pix = fbase + (size_t)y * W + x;
+    const bool yin = y >= roi.y1 && y < roi.y2;
+    if (vec) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(frames + pix * 3);
+      const uint32_t w[3] = {p[0], p[1], p[2]};
+      const uint32_t c4 = *reinterpret_cast<const uint32_t*>(mc + pix), t4 = *reinterpret_cast<const uint32_t*>(mt + pix),
+                     b4 = *reinterpret_cast<const uint32_t*>(mb + pix);
+      uint32_t o[3] = {0u, 0u, 0u};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int flags = (yin && x + k >= roi.x1 && x + k < roi.x2 ? 1 : 0) | (((c4 >> (8 * k)) & 0xffu) ? 2 : 0) |
+                          (((t4 >> (8 * k)) & 0xffu) ? 4 : 0) | (((b4 >> (8 * k)) & 0xffu) ? 8 : 0);
+        const uint8_t* l = lut + flags * 768;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+          const int bi = 3 * k + ch;
+          o[bi >> 2] |= (uint32_t)l[ch * 256 + ((w[bi >> 2] >> (8 * (bi & 3))) & 0xffu)] << (8 * (bi & 3));
+        }
+      }
+      uint32_t* q = reinterpret_cast<uint32_t*>(out + pix * 3);
+      q[0] = o[0]; q[1] = o[1]; q[2] = o[2];
+    } else {
+      for (int k = 0; k < 4 && x + k < W; ++k) {
+        const int flags = (yin && x + k >= roi.x1 && x + k < roi.x2 ? 1 : 0) | (mc[pix + k] ? 2 : 0) | (mt[pix + k] ? 4 : 0) |
+                          (mb[pix + k] ? 8 : 0);
+        for (int ch = 0; ch < 3; ++ch) out[(pix + k) * 3 + ch] = lut[flags * 768 + ch * 256 + frames[(pix + k) * 3 + ch]];
+      }
+    }
+  }
+}
+
 // rotate + resize (infer_two_stage_burr.py:275-280)
 template <class Src>
 __global__ void k_resize3(Src S0, size_t src_stride, uint8_t* __restrict__ dst, int dh, int dw,
@@ -231,6 +290,14 @@ int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, i
     k_gray<<<(unsigned)((npix / 4 + 255) / 256 + 1), 256, 0, st>>>(frames, gray, npix);
     UB_CHECK_LAUNCH(ctx);
   }
+  return UB_OK;
+}
+
+int overlay_impl(ub_ctx* ctx, const uint8_t* frames, const uint8_t* mc, const uint8_t* mt, const uint8_t* mb, int B, int H, int W,
+                 ub_roi roi, uint8_t* out, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_PREPOST, st);
+  k_overlay<<<dim3(cdiv(H, OV_ROWS), B), 256, 0, st>>>(frames, mc, mt, mb, out, H, W, roi);
+  UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
 

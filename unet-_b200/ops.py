@@ -7,6 +7,7 @@ Same names, argument meaning and results as the reference functions:
   detect_burrs_enhanced   infer_enhanced_burr.py:69-138
   enhance_image           infer_enhanced_burr.py:38-66
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
+  visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
 without touching the host.  All arithmetic runs in the CUDA library; there is no CPU path.
@@ -132,3 +133,37 @@ def enhance_image(frame):
     with torch.cuda.device(f.device):
         out = c.enhance(f)
     return _unbatch(out, was_np, single)
+
+
+def overlay_blend(frame, mask_cable, mask_tape, mask_burr, roi):
+    """The four cv2.addWeighted steps of visualize_two_stage (infer_two_stage_burr.py:134-154): dim outside
+    the ROI, tint cable / tape / burr -- one device pass, bit-exact with cv2.  numpy in -> numpy out; CUDA
+    tensors ([H,W,3] / [B,H,W,3] and [H,W] / [B,H,W]) stay on the GPU."""
+    f, was_np, single = _batched(frame, 3)
+    ms = [_batched(m, 2)[0].to(f.device) for m in (mask_cable, mask_tape, mask_burr)]
+    c = _ctx(f.device, f.shape[0], tuple(f.shape[1:3]))
+    with torch.cuda.device(f.device):
+        out = c.overlay(f, ms[0], ms[1], ms[2], roi)
+    return _unbatch(out, was_np, single)
+
+
+def draw_annotations(img, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
+    """The vector part of visualize_two_stage (infer_two_stage_burr.py:156-170): ROI box + label and the three
+    contour sets, drawn by cv2 on the host over the device-blended frame (in place)."""
+    import cv2
+    x1, y1, x2, y2 = roi
+    if draw_roi_box:
+        cv2.rectangle(img, (x1, y1), (x2, y2), (0, 255, 255), 2)
+        cv2.putText(img, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, (0, 255, 255), 2)
+    for mask, colour, thick in ((mask_cable, (0, 255, 0), 2), (mask_tape, (255, 0, 0), 2), (mask_burr, (255, 0, 255), 3)):
+        contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
+        cv2.drawContours(img, contours, -1, colour, thick)
+    return img
+
+
+def visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box=True):
+    """Drop-in for visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box)
+    (infer_two_stage_burr.py:130-170; visualize_detection of infer_enhanced_burr.py:150-192 with the ROI as a
+    tuple): numpy in, numpy out."""
+    out = overlay_blend(frame, mask_cable, mask_tape, mask_burr, roi_orig)
+    return draw_annotations(np.ascontiguousarray(out), mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box)
