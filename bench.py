@@ -298,6 +298,12 @@ def run_ours(args):
             fps_cpu, cores, dt = cpu_reference_fps(frames_np, sd, args.cpu_frames, workload=args.workload)
             line["cpu_baseline"] = {"value": fps_cpu, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{args.cpu_frames} frames of the same batch, batch 1, fp32 ({dt:.1f} s)"}
+        if world == 1 and not args.no_hbm_kernels and args.workload == "two_stage":
+            # the HBM-bound side of the path, one entry point at a time on 512 resident frames (planes > L2)
+            torch.cuda.empty_cache()
+            sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
+            import bench_stage2
+            line["hbm_kernels"] = bench_stage2.measure(512, 10)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -313,6 +319,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=24)
     ap.add_argument("--ref-frames-per-step", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hbm-kernels", action="store_true", help="skip the per-entry-point stage-2 HBM table")
     ap.add_argument("--workload", default="two_stage", choices=["two_stage", "enhanced"],
                     help="two_stage: BASELINE metric config (default); enhanced: config 4 (1080p rotate+resize, enhance_image, multi-scale detector)")
     args = ap.parse_args()

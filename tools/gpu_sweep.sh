@@ -3,7 +3,7 @@
 TAG=$1; VAR=$2; shift 2
 mkdir -p gpurun_out
 for v in "$@"; do
-  env $VAR=$v python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_$v.json 2> gpurun_out/${TAG}_$v.err
+  env $VAR=$v python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-hbm-kernels > gpurun_out/${TAG}_$v.json 2> gpurun_out/${TAG}_$v.err
   python - <<PY
 import json
 d=json.load(open("gpurun_out/${TAG}_$v.json"))

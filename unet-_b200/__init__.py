@@ -2,13 +2,13 @@
 
 Host-side mirror of the reference's Python contracts over libunetb200.so:
   NestedUNet                      (src/models/unetpp.py)
-  preprocess_image, map_roi_to_original, detect_burrs_on_cable   (infer_two_stage_burr.py)
+  preprocess_image, map_roi_to_original, detect_burrs_on_cable, visualize_two_stage   (infer_two_stage_burr.py)
   detect_burrs_enhanced, enhance_image                           (infer_enhanced_burr.py)
   InspectionPipeline              batched body of the inference loop + multi-GPU sharding
 """
 __all__ = ["NestedUNet", "InspectionPipeline", "preprocess_image", "map_roi_to_original",
            "detect_burrs_on_cable", "detect_burrs_enhanced", "enhance_image", "bgr2gray",
-           "normalize_frame", "synth"]
+           "normalize_frame", "visualize_two_stage", "overlay_blend", "synth"]
 
 
 def __getattr__(name):          # lazy: importing the package must not need torch.cuda
@@ -19,7 +19,7 @@ def __getattr__(name):          # lazy: importing the package must not need torc
         from .pipeline import InspectionPipeline
         return InspectionPipeline
     if name in ("preprocess_image", "map_roi_to_original", "detect_burrs_on_cable", "detect_burrs_enhanced",
-                "enhance_image", "bgr2gray", "normalize_frame"):
+                "enhance_image", "bgr2gray", "normalize_frame", "visualize_two_stage", "overlay_blend"):
         from . import ops
         return getattr(ops, name)
     raise AttributeError(name)
