@@ -57,6 +57,10 @@ typedef struct ub_burr_params {
 
 enum { UB_VARIANT_STANDARD = 0,   /* detect_burrs_on_cable, infer_two_stage_burr.py:50-119 */
        UB_VARIANT_ENHANCED = 1,   /* detect_burrs_enhanced, infer_enhanced_burr.py:69-138  */
+       /* get_burr_mask_rulebased, src/refactor/burr_detector.py:11-66 (ub_burr only): edges = wrapped |Laplacian| >
+        * canny_low (the field holds BurrConfig.laplacian_threshold; canny_high unused), band_k = 2*band_out+1,
+        * close_k = open_k = 1 (no morphology), area filter only (max_aspect large, min_side 0); output {0,1} */
+       UB_VARIANT_LAPLACIAN = 2,
        /* OR-ed into `variant` of ub_pipeline / ub_pipeline_host: run enhance_image on every frame
         * before the net and the gray conversion (--enhance, infer_enhanced_burr.py:279-280) */
        UB_FLAG_ENHANCE_IMAGE = 0x100 };

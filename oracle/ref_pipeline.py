@@ -262,3 +262,21 @@ def visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi, draw_roi_b
         contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
         cv2.drawContours(out, contours, -1, colour, thick)
     return out
+
+
+def burrs_rulebased(gray, mask_cable, band_out=10, laplacian_threshold=30, min_area=20, max_area=500):
+    """get_burr_mask_rulebased, src/refactor/burr_detector.py:11-66 (BurrConfig defaults, src/refactor/config.py:98-103)."""
+    if mask_cable.max() == 0:                                                        # :23-24
+        return np.zeros_like(mask_cable)
+    k = 2 * band_out + 1
+    dil = cv2.dilate(mask_cable, _ellipse(k), iterations=1)                          # :37-38
+    band = cv2.subtract(dil, mask_cable)                                             # :41
+    lap8 = np.abs(cv2.Laplacian(gray, cv2.CV_64F)).astype(np.uint8)                  # :44-45 (wraps mod 256)
+    lap_band = cv2.bitwise_and(lap8, lap8, mask=band)                                # :48
+    burr = cv2.threshold(lap_band, laplacian_threshold, 255, cv2.THRESH_BINARY)[1]   # :51
+    n, labels, stats, _ = cv2.connectedComponentsWithStats(burr.astype(np.uint8), connectivity=8)   # :54-56
+    out = np.zeros_like(burr)
+    for i in range(1, n):                                                            # :60-64
+        if min_area <= stats[i, cv2.CC_STAT_AREA] <= max_area:
+            out[labels == i] = 255
+    return out

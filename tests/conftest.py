@@ -58,3 +58,21 @@ def viz_inputs(tag):
     mt = (S.mask_blobs(h, w, seed=8, fill=0.02) & (1 - mc)).astype(np.uint8)
     mb = S.mask_blobs(h, w, seed=9, fill=0.004)
     return fr, mc, mt, mb, roi
+
+
+@pytest.fixture(scope="session")
+def golden_rulebased():
+    return np.load(os.path.join(GOLDEN, "rulebased.npz"))
+
+
+def rulebased_cases():
+    """(tag, gray, mask) behind tests/golden/rulebased.npz."""
+    import cv2
+    import unet_b200.synth as S
+    for tag, fr, mask in (("speckle", S.frames_speckle(1, 448, 800, seed=5, n_blobs=400)[0], S.mask_cable_synth(448, 800, None)),
+                          ("noise", S.frames_noise(1, 120, 184, seed=1)[0], S.mask_cable_synth(120, 184, None))):
+        yield tag, cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY), mask
+
+
+RULEBASED_CFGS = {"default": dict(band_out=10, laplacian_threshold=30, min_area=20, max_area=500),
+                  "wide": dict(band_out=12, laplacian_threshold=20, min_area=5, max_area=2000)}

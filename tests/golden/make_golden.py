@@ -149,6 +149,21 @@ def enhance():
     np.savez_compressed(os.path.join(HERE, "enhance.npz"), **out)
 
 
+def rulebased():
+    """get_burr_mask_rulebased of the refactored library (src/refactor/burr_detector.py:11-66)."""
+    from src.refactor.burr_detector import get_burr_mask_rulebased
+    from src.refactor.config import BurrConfig
+    out = {"versions": VERS}
+    for tag, fr, mask in (("speckle", S.frames_speckle(1, 448, 800, seed=5, n_blobs=400)[0], S.mask_cable_synth(448, 800, None)),
+                          ("noise", S.frames_noise(1, 120, 184, seed=1)[0], S.mask_cable_synth(120, 184, None))):
+        gray = cv2.cvtColor(fr, cv2.COLOR_BGR2GRAY)
+        for name, cfg in (("default", BurrConfig()), ("wide", BurrConfig(band_out=12, laplacian_threshold=20, min_area=5, max_area=2000))):
+            out[f"{tag}_{name}"] = np.packbits(get_burr_mask_rulebased(gray, mask, cfg) > 0)
+            out[f"{tag}_{name}_vals"] = np.unique(get_burr_mask_rulebased(gray, mask, cfg))
+        out[f"{tag}_empty"] = get_burr_mask_rulebased(gray, np.zeros_like(mask), BurrConfig()).max()
+    np.savez_compressed(os.path.join(HERE, "rulebased.npz"), **out)
+
+
 def viz_inputs(tag):
     """Seeded frames + masks for the visualisation vectors (regenerated identically in the tests)."""
     if tag == "full":
@@ -185,7 +200,7 @@ def viz():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["stage2", "net", "enhance", "viz"]
+    which = sys.argv[1:] or ["stage2", "net", "enhance", "viz", "rulebased"]
     if "stage2" in which:
         stage2()
     if "net" in which:
@@ -194,5 +209,7 @@ if __name__ == "__main__":
         enhance()
     if "viz" in which:
         viz()
-    for f in ("stage2.npz", "net.npz", "enhance.npz", "viz.npz"):
+    if "rulebased" in which:
+        rulebased()
+    for f in ("stage2.npz", "net.npz", "enhance.npz", "viz.npz", "rulebased.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -209,3 +209,20 @@ def test_visualize_two_stage_golden(golden_viz, tag):
     nobox = U.visualize_two_stage(fr, mc, mt, mb, roi, False)
     assert zlib.crc32(box.tobytes()) == int(golden_viz[f"{tag}_box_crc"])
     assert zlib.crc32(nobox.tobytes()) == int(golden_viz[f"{tag}_nobox_crc"])
+
+
+def test_rulebased_detector_golden_and_oracle(golden_rulebased):
+    """ops.get_burr_mask_rulebased (ub_burr, UB_VARIANT_LAPLACIAN) == the real reference's output (golden) and the oracle
+    on other masks / thresholds."""
+    from conftest import rulebased_cases, RULEBASED_CFGS
+    from unet_b200 import ops as U
+    for tag, gray, mask in rulebased_cases():
+        for name, cfg in RULEBASED_CFGS.items():
+            out = U.get_burr_mask_rulebased(gray, mask, cfg)
+            assert out.dtype == np.uint8 and set(np.unique(out)) <= {0, 255}
+            assert np.array_equal(np.packbits(out > 0), golden_rulebased[f"{tag}_{name}"]), (tag, name)
+        assert U.get_burr_mask_rulebased(gray, np.zeros_like(mask)).max() == 0
+        h, w = gray.shape
+        blobs = (S.mask_blobs(h, w, seed=11, fill=0.0008) * 255).astype(np.uint8)          # {0,255} mask, many small seeds
+        for cfg in (dict(band_out=3, laplacian_threshold=10, min_area=1, max_area=100000), dict(band_out=7, laplacian_threshold=60, min_area=3, max_area=40)):
+            same(f"rulebased_{tag}", U.get_burr_mask_rulebased(gray, blobs, cfg), R.burrs_rulebased(gray, blobs, **cfg))

@@ -94,3 +94,14 @@ def test_visualisation_matches_reference(golden_viz, tag):
         assert np.array_equal(box, g["small_box"])
     else:
         assert np.array_equal(box[160:224, 200:296], g["full_box_crop"])
+
+
+def test_rulebased_detector_matches_reference(golden_rulebased):
+    """oracle burrs_rulebased == the real get_burr_mask_rulebased (src/refactor/burr_detector.py:11-66)."""
+    from conftest import rulebased_cases, RULEBASED_CFGS
+    for tag, gray, mask in rulebased_cases():
+        for name, cfg in RULEBASED_CFGS.items():
+            out = R.burrs_rulebased(gray, mask, **cfg)
+            assert set(np.unique(out)) <= {0, 255}
+            assert np.array_equal(np.packbits(out > 0), golden_rulebased[f"{tag}_{name}"]), (tag, name)
+        assert R.burrs_rulebased(gray, np.zeros_like(mask)).max() == 0

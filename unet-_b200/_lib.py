@@ -18,7 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("UNETB200_LIB") or os.path.join(_HERE, "libunetb200.so")
 _lib = None
 
-VARIANT_STANDARD, VARIANT_ENHANCED = 0, 1
+VARIANT_STANDARD, VARIANT_ENHANCED, VARIANT_LAPLACIAN = 0, 1, 2
 FLAG_ENHANCE_IMAGE = 0x100
 CVT_BGR2LAB, CVT_LBGR2LAB, CVT_LAB2BGR, CVT_LAB2LBGR = 0, 1, 2, 3
 T_CLASSES = ("conv3x3", "net_glue", "prepost", "stencil_morph", "ccl", "enhance")
@@ -131,6 +131,11 @@ def standard_params(min_area=30, max_area=800) -> BurrParams:
 def enhanced_params(min_area=50, max_area=500) -> BurrParams:
     """detect_burrs_enhanced constants (infer_enhanced_burr.py:82-136)."""
     return BurrParams(min_area, max_area, 6, 5, 30, 100, 25, 5, 3)
+
+
+def rulebased_params(band_out=10, laplacian_threshold=30, min_area=20, max_area=500) -> BurrParams:
+    """get_burr_mask_rulebased / BurrConfig (src/refactor/burr_detector.py:11-66, src/refactor/config.py:98-103)."""
+    return BurrParams(min_area, max_area, 1 << 20, 0, laplacian_threshold, 0, 2 * band_out + 1, 1, 1)
 
 
 class Context:
@@ -273,7 +278,7 @@ class Context:
         b, h, w = gray.shape
         out = torch.empty_like(gray)
         px = torch.empty((b,), dtype=torch.int32, device=gray.device)
-        p = params if params is not None else (enhanced_params() if variant else standard_params())
+        p = params if params is not None else (standard_params(), enhanced_params(), rulebased_params())[variant]
         self._check(lib().ub_burr(self._h, variant, self._dev(gray, torch.uint8), self._dev(mask, torch.uint8), b, h, w,
                                   C.byref(p), out.data_ptr(), px.data_ptr(), self.stream))
         return out, px

@@ -340,6 +340,7 @@ int ub_laplacian_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, in
 static ub_burr_params default_params(int variant) {
   ub_burr_params p;
   if (variant == UB_VARIANT_ENHANCED) p = {50, 500, 6, 5, 30, 100, 25, 5, 3};
+  else if (variant == UB_VARIANT_LAPLACIAN) p = {20, 500, 1 << 20, 0, 30, 0, 21, 1, 1};       // BurrConfig defaults, src/refactor/config.py:98-103
   else p = {30, 800, 5, 4, 50, 150, 8, 3, 2};
   return p;
 }
@@ -348,6 +349,7 @@ int ub_burr(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, 
             const ub_burr_params* params, uint8_t* burr, int32_t* burr_px, void* stream) {
   NEED_CTX(ctx);
   if (!gray || !mask || !burr) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (variant < UB_VARIANT_STANDARD || variant > UB_VARIANT_LAPLACIAN) return ub_fail(ctx, UB_ERR_ARG, "variant %d", variant);
   RUN(check_frame_shape(ctx, B, H, W));
   cudaStream_t st = as_stream(stream);
   ub_burr_params p = params ? *params : default_params(variant);

@@ -619,6 +619,8 @@ int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels
 // ub_pipeline runs it on a second stream beside the network.  Result in ctx->d_tmp[1].
 int burr_edges(ub_ctx* ctx, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& P, cudaStream_t st) {
   uint8_t* t1 = ctx->d_tmp[1];
+  if (variant == UB_VARIANT_LAPLACIAN)        // src/refactor/burr_detector.py:44-51: wrapped |Laplacian| > threshold, nothing else
+    return enh_edges(ctx, gray, B, H, W, 2, 0, P.canny_low, nullptr, t1, st);
   // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
   RUN(blur_canny(ctx, gray, t1, B, H, W, P.canny_low, P.canny_high, st));
   if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));

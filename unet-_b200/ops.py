@@ -7,6 +7,7 @@ Same names, argument meaning and results as the reference functions:
   detect_burrs_enhanced   infer_enhanced_burr.py:69-138
   enhance_image           infer_enhanced_burr.py:38-66
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
+  get_burr_mask_rulebased src/refactor/burr_detector.py:11-66 (the Laplacian-band detector of the refactored library)
   visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
@@ -121,6 +122,19 @@ def detect_burrs_on_cable(frame_gray, mask_cable, config=None):
 def detect_burrs_enhanced(frame_gray, mask_cable, config):
     return _detect(_lib.VARIANT_ENHANCED, frame_gray, mask_cable,
                    _lib.enhanced_params(config["min_area"], config["max_area"]))
+
+
+def get_burr_mask_rulebased(frame_gray, mask_cable, cfg=None):
+    """get_burr_mask_rulebased(frame_gray, mask_cable, cfg: BurrConfig) (src/refactor/burr_detector.py:11-66):
+    band = dilate(mask, ELLIPSE(2*band_out+1)) - mask, wrapped |Laplacian| > laplacian_threshold inside the band,
+    components with min_area <= area <= max_area -> {0, 255}.  `cfg` is the reference's BurrConfig, any object with
+    the same four attributes, a dict, or None (BurrConfig defaults 10 / 30 / 20 / 500).  band_out <= 12."""
+    get = (lambda k, d: cfg.get(k, d)) if isinstance(cfg, dict) else (lambda k, d: getattr(cfg, k, d))
+    p = _lib.rulebased_params(get("band_out", 10), get("laplacian_threshold", 30), get("min_area", 20), get("max_area", 500))
+    if isinstance(frame_gray, np.ndarray) and frame_gray.ndim == 3 and frame_gray.shape[2] == 3:
+        frame_gray = bgr2gray(frame_gray)                     # :26-27
+    out = _detect(_lib.VARIANT_LAPLACIAN, frame_gray, mask_cable, p)
+    return out * 255
 
 
 def enhance_image(frame):
