@@ -116,6 +116,14 @@ int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, in
 int ub_overlay(ub_ctx* ctx, const uint8_t* frames_bgr_dev, const uint8_t* mask_cable_dev, const uint8_t* mask_tape_dev,
                const uint8_t* mask_burr_dev, int B, int H, int W, const ub_roi* roi, uint8_t* out_bgr_dev, void* stream);
 
+/* compute_diameter_metrics (src/utils/geometry_enhanced.py:113-187): pred u8 [B,H,W] class ids -> out int32 [B][8] =
+ * { dc_px, dt_px (binary32 bit patterns: medians of the Gaussian-smoothed row widths of the largest cable / tape
+ * component over the rows where both are > 0; 0 when valid_rows < min_valid_rows), valid_rows, cable_area, tape_area
+ * (pixels of the kept components: coverage numerators), 0, 0, 0 }.  min_area: the reference passes 50 (:143-144).
+ * 16 <= H <= 2048, W >= 16.  The mm values and the differences are scalar host arithmetic (ops.compute_diameter_metrics). */
+int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
+                        int min_area, int min_valid_rows, int32_t* out_dev, void* stream);
+
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */

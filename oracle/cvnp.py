@@ -394,3 +394,28 @@ def overlay_blend(frame: np.ndarray, mask_cable, mask_tape, mask_burr, roi) -> n
         tint[mask > 0] = colour
         out = add_weighted_u8(out, a, tint, b)
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# cv2.GaussianBlur(v.reshape(-1,1), (1,31), sigmaX=0) on float32 (src/utils/geometry_enhanced.py:70-76): kernel =
+# float32(getGaussianKernel(31, sigma=5)), BORDER_REFLECT_101, and OpenCV's symmetric column filter order
+#   s = k0*c;  s += kj * (p[+j] + p[-j])  for j = 1..15,   every product and sum rounded to binary32 (no FMA).
+# ----------------------------------------------------------------------------------------------
+def gauss31_kernel_f32() -> np.ndarray:
+    x = np.arange(31, dtype=np.float64) - 15.0
+    t = np.exp(-0.5 / 25.0 * x * x)
+    return (t / t.sum()).astype(np.float32)
+
+
+def gauss31_f32(v: np.ndarray) -> np.ndarray:
+    v = np.asarray(v, np.float32)
+    n = len(v)
+    k = gauss31_kernel_f32()
+    idx = np.abs(np.arange(-15, n + 15))
+    idx = np.where(idx >= n, 2 * (n - 1) - idx, idx)
+    p = v[idx]
+    s = (k[15] * p[15:15 + n]).astype(np.float32)
+    for j in range(1, 16):
+        pair = (p[15 + j:15 + j + n] + p[15 - j:15 - j + n]).astype(np.float32)
+        s = (s + (k[15 + j] * pair).astype(np.float32)).astype(np.float32)
+    return s

@@ -280,3 +280,46 @@ def burrs_rulebased(gray, mask_cable, band_out=10, laplacian_threshold=30, min_a
         if min_area <= stats[i, cv2.CC_STAT_AREA] <= max_area:
             out[labels == i] = 255
     return out
+
+
+def _largest_cc(mask, min_area):
+    """_largest_connected_component, src/utils/geometry_enhanced.py:79-110."""
+    n, labels, stats, _ = cv2.connectedComponentsWithStats(mask, connectivity=8)
+    if n <= 1:
+        return mask
+    areas = stats[1:, cv2.CC_STAT_AREA]
+    ok = np.where(areas >= min_area)[0]
+    if len(ok) == 0:
+        return np.zeros_like(mask)
+    return (labels == 1 + int(ok[np.argmax(areas[ok])])).astype(np.uint8)
+
+
+def _row_widths(mask, use_cv2=True):
+    """_compute_width_per_row(mask, smooth=True, kernel_size=31), src/utils/geometry_enhanced.py:45-76."""
+    from . import cvnp
+    h = mask.shape[0]
+    w = np.zeros(h, np.float32)
+    for y in range(h):
+        xs = np.where(mask[y] > 0)[0]
+        if xs.size:
+            w[y] = float(xs.max() - xs.min() + 1)
+    if use_cv2:
+        return cv2.GaussianBlur(w.reshape(-1, 1), (1, 31), sigmaX=0).reshape(-1)
+    return cvnp.gauss31_f32(w)
+
+
+def diameter_metrics(pred, cable_cls=1, tape_cls=2, mm_per_px=0.05, min_valid_rows=20, use_cv2=True):
+    """compute_diameter_metrics, src/utils/geometry_enhanced.py:113-187 -> dict with the dataclass's fields."""
+    h, w = pred.shape
+    cable = _largest_cc((pred == cable_cls).astype(np.uint8), 50)
+    tape = _largest_cc((pred == tape_cls).astype(np.uint8), 50)
+    cw, tw = _row_widths(cable, use_cv2), _row_widths(tape, use_cv2)
+    valid = (cw > 0) & (tw > 0)
+    out = dict(valid_rows=int(valid.sum()), cable_coverage=cable.sum() / (h * w), tape_coverage=tape.sum() / (h * w))
+    if out["valid_rows"] < min_valid_rows:
+        out.update(dc_px=0.0, dt_px=0.0, delta_d_px=0.0, dc_mm=0.0, dt_mm=0.0, delta_d_mm=0.0)
+        return out
+    dc, dt = float(np.median(cw[valid])), float(np.median(tw[valid]))
+    out.update(dc_px=dc, dt_px=dt, delta_d_px=dt - dc, dc_mm=dc * mm_per_px, dt_mm=dt * mm_per_px,
+               delta_d_mm=dt * mm_per_px - dc * mm_per_px)
+    return out

@@ -76,3 +76,20 @@ def rulebased_cases():
 
 RULEBASED_CFGS = {"default": dict(band_out=10, laplacian_threshold=30, min_area=20, max_area=500),
                   "wide": dict(band_out=12, laplacian_threshold=20, min_area=5, max_area=2000)}
+
+
+GEOM_FIELDS = ("dc_px", "dt_px", "delta_d_px", "dc_mm", "dt_mm", "delta_d_mm", "valid_rows", "cable_coverage", "tape_coverage")
+
+
+@pytest.fixture(scope="session")
+def golden_geometry():
+    return np.load(os.path.join(GOLDEN, "geometry.npz"))
+
+
+def geometry_cases(g):
+    """(pred, golden row with defaults, golden row of the not-enough-rows call) behind tests/golden/geometry.npz."""
+    import unet_b200.synth as S
+    for i, (h, w, seed, tape) in enumerate(g["cases"]):
+        p = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape))
+        assert zlib.crc32(p.tobytes()) == int(g["pred_crc"][i]), "synth.pred_classes changed; rerun tests/golden/make_golden.py geometry"
+        yield p, g["metrics"][2 * i], g["metrics"][2 * i + 1]

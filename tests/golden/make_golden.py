@@ -164,6 +164,28 @@ def rulebased():
     np.savez_compressed(os.path.join(HERE, "rulebased.npz"), **out)
 
 
+GEOM_CASES = (((512, 512), 0, True), ((448, 800), 1, True), ((512, 512), 2, False), ((96, 160), 3, True), ((130, 75), 4, True))
+GEOM_FIELDS = ("dc_px", "dt_px", "delta_d_px", "dc_mm", "dt_mm", "delta_d_mm", "valid_rows", "cable_coverage", "tape_coverage")
+
+
+def geometry():
+    """compute_diameter_metrics of the real reference (src/utils/geometry_enhanced.py:113-187) on unet_b200.synth.pred_classes."""
+    import zlib
+    from src.utils.geometry_enhanced import compute_diameter_metrics
+    out = {"versions": VERS, "cases": np.array([[h, w, seed, int(t)] for (h, w), seed, t in GEOM_CASES])}
+    rows, crcs = [], []
+    for (h, w), seed, tape in GEOM_CASES:
+        p = S.pred_classes(h, w, seed=seed, tape=tape)
+        crcs.append(zlib.crc32(p.tobytes()))
+        m = compute_diameter_metrics(p)
+        rows.append([float(getattr(m, f)) for f in GEOM_FIELDS])
+        m2 = compute_diameter_metrics(p, mm_per_px=0.1, min_valid_rows=1000)       # the "not enough rows" branch
+        rows.append([float(getattr(m2, f)) for f in GEOM_FIELDS])
+    out["metrics"] = np.array(rows, np.float64)
+    out["pred_crc"] = np.array(crcs, np.uint32)
+    np.savez_compressed(os.path.join(HERE, "geometry.npz"), **out)
+
+
 def viz_inputs(tag):
     """Seeded frames + masks for the visualisation vectors (regenerated identically in the tests)."""
     if tag == "full":
@@ -200,7 +222,7 @@ def viz():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["stage2", "net", "enhance", "viz", "rulebased"]
+    which = sys.argv[1:] or ["stage2", "net", "enhance", "viz", "rulebased", "geometry"]
     if "stage2" in which:
         stage2()
     if "net" in which:
@@ -211,5 +233,7 @@ if __name__ == "__main__":
         viz()
     if "rulebased" in which:
         rulebased()
-    for f in ("stage2.npz", "net.npz", "enhance.npz", "viz.npz", "rulebased.npz"):
+    if "geometry" in which:
+        geometry()
+    for f in ("stage2.npz", "net.npz", "enhance.npz", "viz.npz", "rulebased.npz", "geometry.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -226,3 +226,28 @@ def test_rulebased_detector_golden_and_oracle(golden_rulebased):
         blobs = (S.mask_blobs(h, w, seed=11, fill=0.0008) * 255).astype(np.uint8)          # {0,255} mask, many small seeds
         for cfg in (dict(band_out=3, laplacian_threshold=10, min_area=1, max_area=100000), dict(band_out=7, laplacian_threshold=60, min_area=3, max_area=40)):
             same(f"rulebased_{tag}", U.get_burr_mask_rulebased(gray, blobs, cfg), R.burrs_rulebased(gray, blobs, **cfg))
+
+
+def test_diameter_metrics_golden_and_oracle(golden_geometry):
+    """ops.compute_diameter_metrics (ub_diameter_metrics) == the real reference's numbers, every field exactly; batched
+    device call == oracle on other class maps, incl. two equal-area components (OpenCV label order breaks the tie)."""
+    from conftest import geometry_cases, GEOM_FIELDS
+    from unet_b200 import ops as U
+    for pred, want, want_short in geometry_cases(golden_geometry):
+        m = U.compute_diameter_metrics(pred)
+        assert [float(getattr(m, f)) for f in GEOM_FIELDS] == list(want), (pred.shape, m)
+        m = U.compute_diameter_metrics(pred, mm_per_px=0.1, min_valid_rows=1000)
+        assert [float(getattr(m, f)) for f in GEOM_FIELDS] == list(want_short), (pred.shape, m)
+    preds = np.stack([S.pred_classes(448, 800, seed=10 + i, tape=i != 2) for i in range(4)])
+    preds[3][:] = 0                                   # tie: two cable blocks of equal area; tape only beside the second
+    preds[3][300:360, 100:200] = 1
+    preds[3][20:80, 500:600] = 1
+    preds[3][295:365, 60:100] = 2
+    preds[3][10:90, 460:500] = 2
+    preds[3][10:90, 330:400] = 2
+    got = U.compute_diameter_metrics(dev(preds))
+    for i in range(4):
+        want = R.diameter_metrics(preds[i])
+        assert [float(getattr(got[i], f)) for f in GEOM_FIELDS] == [float(want[f]) for f in GEOM_FIELDS], (i, got[i], want)
+    empty = U.compute_diameter_metrics(np.zeros((64, 64), np.uint8))
+    assert empty.valid_rows == 0 and empty.dc_px == 0.0 and empty.cable_coverage == 0.0

@@ -98,3 +98,25 @@ def test_add_weighted_all_operand_pairs(alpha, beta):
     x = rng.integers(0, 256, (120, 203, 3), dtype=np.uint8)
     y = rng.integers(0, 256, (120, 203, 3), dtype=np.uint8)
     assert np.array_equal(cvnp.add_weighted_u8(x, alpha, y, beta), cv2.addWeighted(x, alpha, y, beta, 0))
+
+
+@pytest.mark.parametrize("n", [448, 512, 96, 33, 1000])
+def test_gauss31_float_profile_filter(n):
+    """cv2.GaussianBlur(v.reshape(-1,1), (1,31), 0) on float32 (geometry_enhanced.py:70-76): kernel and operation order."""
+    assert np.array_equal(cvnp.gauss31_kernel_f32(), cv2.getGaussianKernel(31, 0, cv2.CV_32F).reshape(-1))
+    rng = np.random.default_rng(n)
+    for trial in range(4):
+        v = rng.integers(0, 800, n).astype(np.float32)
+        if trial % 2:
+            v[rng.random(n) < 0.4] = 0
+        assert np.array_equal(cvnp.gauss31_f32(v), cv2.GaussianBlur(v.reshape(-1, 1), (1, 31), sigmaX=0).reshape(-1))
+
+
+def test_gauss31_table_in_the_kernel_source():
+    """The 16 hex-float constants of c_gauss31 (csrc/stage2.cu) are float32(cv2.getGaussianKernel(31, 0)), centre first."""
+    import os, re
+    src = open(os.path.join(os.path.dirname(__file__), "..", "unet-_b200", "csrc", "stage2.cu")).read()
+    body = re.search(r"c_gauss31\[16\] = \{(.*?)\};", src, re.S).group(1)
+    vals = np.array([float.fromhex(t.strip().rstrip("f")) for t in body.split(",")], np.float64)
+    k = cv2.getGaussianKernel(31, 0, cv2.CV_32F).reshape(-1)
+    assert np.array_equal(vals.astype(np.float32), k[15:]) and np.array_equal(vals, k[15:].astype(np.float64))

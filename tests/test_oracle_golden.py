@@ -105,3 +105,14 @@ def test_rulebased_detector_matches_reference(golden_rulebased):
             assert set(np.unique(out)) <= {0, 255}
             assert np.array_equal(np.packbits(out > 0), golden_rulebased[f"{tag}_{name}"]), (tag, name)
         assert R.burrs_rulebased(gray, np.zeros_like(mask)).max() == 0
+
+
+@pytest.mark.parametrize("use_cv2", [True, False])
+def test_diameter_metrics_match_reference(golden_geometry, use_cv2):
+    """oracle diameter_metrics (cv2 filter / numpy restatement of it) == the real compute_diameter_metrics, every field."""
+    from conftest import geometry_cases, GEOM_FIELDS
+    for pred, want, want_short in geometry_cases(golden_geometry):
+        got = R.diameter_metrics(pred, use_cv2=use_cv2)
+        assert [float(got[f]) for f in GEOM_FIELDS] == list(want), (pred.shape, got)
+        got = R.diameter_metrics(pred, mm_per_px=0.1, min_valid_rows=1000, use_cv2=use_cv2)
+        assert [float(got[f]) for f in GEOM_FIELDS] == list(want_short)

@@ -56,6 +56,7 @@ SIGNATURES = {
     "ub_normalize_frames": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P]),
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
     "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
+    "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -235,6 +236,14 @@ class Context:
         self._check(lib().ub_overlay(self._h, self._dev(frames, torch.uint8), self._dev(mask_cable, torch.uint8),
                                      self._dev(mask_tape, torch.uint8), self._dev(mask_burr, torch.uint8), b, h, w,
                                      C.byref(r), out.data_ptr(), self.stream))
+        return out
+
+    def diameter_metrics(self, pred, cable_cls=1, tape_cls=2, min_area=50, min_valid_rows=20):
+        """pred u8 [B,H,W] class ids -> int32 [B,8] (dc_px / dt_px as float32 bit patterns, valid_rows, cable_area, tape_area)."""
+        b, h, w = pred.shape
+        out = torch.empty((b, 8), dtype=torch.int32, device=pred.device)
+        self._check(lib().ub_diameter_metrics(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, min_area,
+                                              min_valid_rows, out.data_ptr(), self.stream))
         return out
 
     def _u8op(self, fn, src, *args):

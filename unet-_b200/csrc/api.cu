@@ -45,6 +45,7 @@ int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* 
 int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
 int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
 int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t);
+int diameter_metrics(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
 int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
 
@@ -293,6 +294,14 @@ int ub_overlay(ub_ctx* ctx, const uint8_t* frames, const uint8_t* mc, const uint
   NEED_CTX(ctx);
   if (!frames || !mc || !mt || !mb || !out || !roi || B < 1 || H < 1 || W < 1) return ub_fail(ctx, UB_ERR_ARG, "ub_overlay: null pointer or empty shape");
   return overlay_impl(ctx, frames, mc, mt, mb, B, H, W, *roi, out, as_stream(stream));
+}
+
+int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int min_area,
+                        int min_valid_rows, int32_t* out, void* stream) {
+  NEED_CTX(ctx);
+  if (!pred || !out) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return diameter_metrics(ctx, pred, B, H, W, cable_cls, tape_cls, min_area, min_valid_rows, out, as_stream(stream));
 }
 
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {

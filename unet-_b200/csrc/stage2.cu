@@ -310,6 +310,7 @@ __global__ void __launch_bounds__(256) k_cclb_hyst_final(const uint32_t* __restr
 }
 
 // component statistics, one atomic set per run (flattened labels)
+template <bool KEY>
 __global__ void __launch_bounds__(256) k_cclb_stats(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
                                                     int* __restrict__ comp, size_t plane) {
   const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
@@ -324,6 +325,8 @@ __global__ void __launch_bounds__(256) k_cclb_stats(const uint32_t* __restrict__
     atomicAdd(k, len);
     atomicMin(k + plane, x); atomicMax(k + 2 * plane, xe);
     atomicMin(k + 3 * plane, y); atomicMax(k + 4 * plane, y);
+    // first appearance in cv2's 2x2-block raster scan (the component's OpenCV label order), as in k_ccl_stats
+    if (KEY) atomicMin(k + 5 * plane, ((((y >> 1) * ((W + 1) >> 1)) + (x >> 1)) << 2) | ((y & 1) << 1) | (x & 1));
   }
 }
 
@@ -672,7 +675,7 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
     uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
     RUN(cclb_label(ctx, t2, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
     dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
-    k_cclb_stats<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
     k_cclb_filter<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, P, burr, burr_px, px_stride);
     UB_CHECK_LAUNCH_N(ctx, 2);
     return UB_OK;
@@ -681,5 +684,172 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
   k_ccl_stats<<<gseg, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, nullptr);
   k_ccl_filter<<<gpix, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, P, burr, burr_px, px_stride);
   UB_CHECK_LAUNCH_N(ctx, 2);
+  return UB_OK;
+}
+
+// =====================================================================================================
+// compute_diameter_metrics (src/utils/geometry_enhanced.py:113-187): for the cable and the tape class keep
+// the largest 8-connected component of area >= min_area (_largest_connected_component, :79-110), take every
+// row's width max_x - min_x + 1 (:64-67), smooth the two width profiles with cv2.GaussianBlur((1,31), 0) on
+// float32 (:70-76), and report the medians over the rows where both are > 0 (:150-171).
+// Device form: run-based labelling (above) -> best component per frame by a 64-bit atomicMax on
+// (area, OpenCV label order) -> one warp per row for the extent -> one block per frame for the float32
+// smoothing (cv2's exact operation order, oracle/cvnp.py: gauss31_f32), compaction, bitonic sort, medians.
+// =====================================================================================================
+namespace s2 {
+
+__global__ void k_class_mask(const uint8_t* __restrict__ pred, uint8_t* __restrict__ out, size_t n, int cls) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 4 <= n && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out)) & 3) == 0) {
+    const uint32_t v = *reinterpret_cast<const uint32_t*>(pred + i) ^ (0x01010101u * (uint32_t)cls);   // zero byte where pred == cls
+    const uint32_t nz = (((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v) & 0x80808080u;                          // 0x80 where byte != 0
+    *reinterpret_cast<uint32_t*>(out + i) = (nz >> 7) ^ 0x01010101u;
+  } else {
+    for (size_t k = i; k < n && k < i + 4; ++k) out[k] = pred[k] == cls;
+  }
+}
+
+// best[b] = max over components with area >= min_area of (area << 32 | INT_MAX - first-appearance key)
+__global__ void __launch_bounds__(256) k_diam_select(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                     const int* __restrict__ comp, size_t plane, int min_area,
+                                                     unsigned long long* __restrict__ best) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int p = y * W + 32 * w + a;
+    if (lab_all[base + p] != p) continue;                       // roots only
+    const int area = comp[base + p];
+    if (area >= min_area)
+      atomicMax(best + blockIdx.z, ((unsigned long long)(uint32_t)area << 32) | (uint32_t)(INT_MAX - comp[5 * plane + base + p]));
+  }
+}
+
+// one warp per (frame, row): extent of the best component in the row -> width (0 when absent)
+__global__ void __launch_bounds__(256) k_diam_rows(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                   const int* __restrict__ comp, size_t plane,
+                                                   const unsigned long long* __restrict__ best, float* __restrict__ widths) {
+  const int y = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (y >= H) return;
+  const unsigned long long b = best[blockIdx.z];
+  const int b_area = (int)(b >> 32), b_key = INT_MAX - (int)(uint32_t)b;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  int lo = INT_MAX, hi = -1;
+  if (b)
+    for (int w = lane; w < Wd; w += 32) {
+      uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+      while (c) {
+        int a, len;
+        c &= ~first_run(c, a, len);
+        const int x = 32 * w + a, r = lab_all[base + y * W + x];
+        if (comp[base + r] == b_area && comp[5 * plane + base + r] == b_key) { lo = min(lo, x); hi = max(hi, x + len - 1); }
+      }
+    }
+  for (int o = 16; o; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+  if (lane == 0) widths[(size_t)blockIdx.z * H + y] = hi >= 0 ? (float)(hi - lo + 1) : 0.f;
+}
+
+// float32(cv2.getGaussianKernel(31, 0)) -- sigma = 0.3*((31-1)*0.5-1)+0.8 = 5; centre first (tests pin the table against cv2)
+__constant__ float c_gauss31[16] = {0x1.476facp-4f, 0x1.40f3dap-4f, 0x1.2e43p-4f, 0x1.117f6ap-4f, 0x1.db88f4p-5f, 0x1.8d334p-5f,
+                                    0x1.3ec2b8p-5f, 0x1.eb8fdp-6f, 0x1.6c286ep-6f, 0x1.033262p-6f, 0x1.628266p-7f, 0x1.d1dbc8p-8f,
+                                    0x1.2616cp-8f, 0x1.64bf72p-9f, 0x1.9fc9dp-10f, 0x1.d19932p-11f};
+
+constexpr int DM_MAXH = 2048;
+// one block per frame: smooth both profiles, valid rows, medians.  out[b] = {dc, dt (float bits), valid_rows, cable_area, tape_area, 0, 0, 0}
+__global__ void __launch_bounds__(1024) k_diam_finish(const float* __restrict__ wc_all, const float* __restrict__ wt_all, int H,
+                                                      const unsigned long long* __restrict__ best_c, const unsigned long long* __restrict__ best_t,
+                                                      int min_valid_rows, int32_t* __restrict__ out) {
+  __shared__ float s_c[DM_MAXH], s_t[DM_MAXH];
+  __shared__ int s_n;
+  const float* wc = wc_all + (size_t)blockIdx.x * H;
+  const float* wt = wt_all + (size_t)blockIdx.x * H;
+  if (threadIdx.x == 0) s_n = 0;
+  float sc[DM_MAXH / 1024], st[DM_MAXH / 1024];
+#pragma unroll
+  for (int q = 0; q < DM_MAXH / 1024; ++q) {
+    const int y = threadIdx.x + q * 1024;
+    sc[q] = st[q] = 0.f;
+    if (y < H) {
+      // cv2's symmetric column filter: s = k0*c; s += kj*(p[+j] + p[-j]), every product and sum rounded to binary32, no FMA
+      float a = __fmul_rn(c_gauss31[0], wc[y]), b = __fmul_rn(c_gauss31[0], wt[y]);
+      for (int j = 1; j < 16; ++j) {
+        const int yp = reflect101(y + j, H), ym = reflect101(y - j, H);
+        a = __fadd_rn(a, __fmul_rn(c_gauss31[j], __fadd_rn(wc[yp], wc[ym])));
+        b = __fadd_rn(b, __fmul_rn(c_gauss31[j], __fadd_rn(wt[yp], wt[ym])));
+      }
+      sc[q] = a; st[q] = b;
+    }
+  }
+  __syncthreads();
+  // compaction of the valid rows (order is irrelevant for a median), padding with +inf for the sort
+  for (int i = threadIdx.x; i < DM_MAXH; i += 1024) s_c[i] = s_t[i] = __int_as_float(0x7f800000);
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < DM_MAXH / 1024; ++q) {
+    const int y = threadIdx.x + q * 1024;
+    if (y < H && sc[q] > 0.f && st[q] > 0.f) { const int k = atomicAdd(&s_n, 1); s_c[k] = sc[q]; s_t[k] = st[q]; }
+  }
+  __syncthreads();
+  const int n = s_n;
+  int np2 = 1;
+  while (np2 < n) np2 <<= 1;
+  for (int size = 2; size <= np2; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = threadIdx.x; i < np2; i += 1024) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool up = (i & size) == 0;
+          float x = s_c[i], y2 = s_c[j];
+          if ((x > y2) == up) { s_c[i] = y2; s_c[j] = x; }
+          x = s_t[i]; y2 = s_t[j];
+          if ((x > y2) == up) { s_t[i] = y2; s_t[j] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  if (threadIdx.x == 0) {
+    float dc = 0.f, dt = 0.f;
+    if (n >= min_valid_rows && n > 0) {       // np.median on float32: middle element, or float32 mean of the two middle ones
+      dc = (n & 1) ? s_c[n >> 1] : __fmul_rn(__fadd_rn(s_c[(n >> 1) - 1], s_c[n >> 1]), 0.5f);
+      dt = (n & 1) ? s_t[n >> 1] : __fmul_rn(__fadd_rn(s_t[(n >> 1) - 1], s_t[n >> 1]), 0.5f);
+    }
+    int32_t* o = out + (size_t)blockIdx.x * 8;
+    o[0] = __float_as_int(dc); o[1] = __float_as_int(dt); o[2] = n;
+    o[3] = (int)(best_c[blockIdx.x] >> 32); o[4] = (int)(best_t[blockIdx.x] >> 32); o[5] = o[6] = o[7] = 0;
+  }
+}
+
+}  // namespace s2
+
+// pred: class ids u8 [B,H,W]; out: int32 [B,8] (see k_diam_finish).  Scratch: d_tmp[0], d_lab[0..1], d_comp, d_counts.
+int diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int min_area,
+                     int min_valid_rows, int32_t* out, cudaStream_t st) {
+  if (H > DM_MAXH) return ub_fail(ctx, UB_ERR_ARG, "ub_diameter_metrics: H = %d > %d", H, DM_MAXH);
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const size_t n = (size_t)B * H * W, plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
+  const int Wd = (W + 31) / 32;
+  uint8_t* m = ctx->d_tmp[0];
+  int* lab = ctx->d_lab[0];
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  // widths: 2 x [B,H] float in d_tmp[1] (B*H*W bytes), best[2][B] in d_tmp[2]
+  if (W < 16 || H < 16) return ub_fail(ctx, UB_ERR_ARG, "ub_diameter_metrics: %dx%d smaller than 16x16", H, W);
+  float* widths = reinterpret_cast<float*>(ctx->d_tmp[1]);
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(ctx->d_tmp[2]);
+  UB_CUDA(ctx, cudaMemsetAsync(best, 0, sizeof(unsigned long long) * 2 * B, st));
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  for (int k = 0; k < 2; ++k) {
+    k_class_mask<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
+    RUN(cclb_label(ctx, m, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+    k_cclb_stats<true><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_diam_select<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, min_area, best + (size_t)k * B);
+    k_diam_rows<<<dim3(cdiv(H, 8), 1, B), 256, 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, best + (size_t)k * B,
+                                                       widths + (size_t)k * B * H);
+    UB_CHECK_LAUNCH_N(ctx, 4);
+  }
+  k_diam_finish<<<B, 1024, 0, st>>>(widths, widths + (size_t)B * H, H, best, best + B, min_valid_rows, out);
+  UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }

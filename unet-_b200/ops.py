@@ -8,6 +8,7 @@ Same names, argument meaning and results as the reference functions:
   enhance_image           infer_enhanced_burr.py:38-66
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
   get_burr_mask_rulebased src/refactor/burr_detector.py:11-66 (the Laplacian-band detector of the refactored library)
+  compute_diameter_metrics src/utils/geometry_enhanced.py:113-187 (Dc / Dt / delta-D of the refactored library)
   visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
@@ -135,6 +136,41 @@ def get_burr_mask_rulebased(frame_gray, mask_cable, cfg=None):
         frame_gray = bgr2gray(frame_gray)                     # :26-27
     out = _detect(_lib.VARIANT_LAPLACIAN, frame_gray, mask_cable, p)
     return out * 255
+
+
+class DiameterMetrics:
+    """Same fields as the reference's dataclass (src/utils/geometry_enhanced.py:18-34)."""
+    __slots__ = ("dc_px", "dt_px", "delta_d_px", "dc_mm", "dt_mm", "delta_d_mm", "valid_rows", "cable_coverage", "tape_coverage")
+
+    def __init__(self, **kw):
+        for k in self.__slots__:
+            setattr(self, k, kw[k])
+
+    def __repr__(self):
+        return "DiameterMetrics(" + ", ".join(f"{k}={getattr(self, k)!r}" for k in self.__slots__) + ")"
+
+
+def compute_diameter_metrics(pred_mask, cable_cls=1, tape_cls=2, mm_per_px=0.05, min_valid_rows=20):
+    """compute_diameter_metrics(pred_mask, cable_cls, tape_cls, mm_per_px, min_valid_rows)
+    (src/utils/geometry_enhanced.py:113-187).  pred_mask: class ids u8 [H,W] (numpy -> one DiameterMetrics) or a
+    CUDA tensor [B,H,W] (-> list).  Labelling, row extents, float32 smoothing and medians run on the device; the
+    scalar conversions to millimetres are the reference's own float arithmetic on the host."""
+    f, was_np, single = _batched(pred_mask, 2)
+    b, h, w = f.shape
+    c = _ctx(f.device, b, (h, w), (16, 16))
+    with torch.cuda.device(f.device):
+        raw = c.diameter_metrics(f, cable_cls, tape_cls, 50, min_valid_rows).cpu().numpy()
+    res = []
+    for r in raw:
+        dc_px, dt_px = (float(v) for v in r[:2].view(np.float32))
+        valid_rows = int(r[2])
+        if valid_rows < min_valid_rows:
+            dc_px = dt_px = 0.0
+        dc_mm, dt_mm = dc_px * mm_per_px, dt_px * mm_per_px
+        res.append(DiameterMetrics(dc_px=dc_px, dt_px=dt_px, delta_d_px=dt_px - dc_px, dc_mm=dc_mm, dt_mm=dt_mm,
+                                   delta_d_mm=dt_mm - dc_mm, valid_rows=valid_rows, cable_coverage=int(r[3]) / (h * w),
+                                   tape_coverage=int(r[4]) / (h * w)))
+    return res[0] if single else res
 
 
 def enhance_image(frame):

@@ -63,6 +63,38 @@ def mask_blobs(h: int, w: int, seed: int = 0, fill: float = 0.3) -> np.ndarray:
     return (rng.random((h, w)) < fill).astype(np.uint8)
 
 
+def pred_classes(h: int = 512, w: int = 512, seed: int = 0, tape: bool = True) -> np.ndarray:
+    """Synthetic class-id map (0 background, 1 cable, 2 tape) for the geometry measurements: a wobbling cable
+    band with ragged edges, a tape wrap that covers it over a range of rows and hugs it on both sides elsewhere,
+    plus stray blobs and single-pixel specks of both classes."""
+    rng = np.random.default_rng(seed)
+    p = np.zeros((h, w), np.uint8)
+    phase = rng.uniform(0, 2 * np.pi)
+    y = np.arange(h)
+    cx = 0.5 * w + 0.03 * w * np.sin(2 * np.pi * y / max(h / 3.0, 8.0) + phase)
+    half = 0.08 * w + rng.integers(-2, 3, h)
+    xs = np.arange(w)[None, :]
+    cable = np.abs(xs - cx[:, None]) <= half[:, None]
+    cable[: h // 12] = False
+    p[cable] = 1
+    if tape:
+        t_half = half + 0.04 * w + rng.integers(-3, 4, h)
+        wrap = np.abs(xs - cx[:, None]) <= t_half[:, None]
+        rows = (y > h // 4) & (y < (3 * h) // 4)
+        p[wrap & ~cable & rows[:, None]] = 2                      # tape beside the cable
+        full = (y > (2 * h) // 5) & (y < h // 2)
+        p[wrap & full[:, None]] = 2                               # tape over the cable: the cable splits in two
+    for cls, n in ((1, 6), (2, 6)):                               # stray blobs (some above the 50 px area gate)
+        for _ in range(n):
+            by, bx = rng.integers(0, h - 12), rng.integers(0, w - 12)
+            bh, bw = rng.integers(2, 12, 2)
+            p[by:by + bh, bx:bx + bw] = cls
+    specks = rng.random((h, w))
+    p[specks < 0.002] = 1
+    p[specks > 0.998] = 2
+    return p
+
+
 def make_state_dict(seed: int = 0, num_classes: int = 3, input_channels: int = 3,
                     head_gain: float = 1.0):
     """Random-init checkpoint "W0" with the reference's 134-key layout
