@@ -124,6 +124,13 @@ int ub_overlay(ub_ctx* ctx, const uint8_t* frames_bgr_dev, const uint8_t* mask_c
 int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
                         int min_area, int min_valid_rows, int32_t* out_dev, void* stream);
 
+/* analyze_defects (src/utils/geometry_enhanced.py:236-330): pred u8 [B,H,W] class ids (< 8) -> out int32 [B][16] =
+ * { tape_px, tape_components, tape_largest_area, holes, hole_px, cable_components, 0, 0, pixel count of class 0..7 } where
+ * holes are the 8-connected components of CLOSE(tape, ELLIPSE 5x5) - tape with area >= hole_min_size.  The ratios
+ * (coverage, hole ratio, largest-area ratio) are scalar host arithmetic (ops.analyze_defects). */
+int ub_analyze_defects(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
+                       int hole_min_size, int32_t* out_dev, void* stream);
+
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */

@@ -323,3 +323,21 @@ def diameter_metrics(pred, cable_cls=1, tape_cls=2, mm_per_px=0.05, min_valid_ro
     out.update(dc_px=dc, dt_px=dt, delta_d_px=dt - dc, dc_mm=dc * mm_per_px, dt_mm=dt * mm_per_px,
                delta_d_mm=dt * mm_per_px - dc * mm_per_px)
     return out
+
+
+def analyze_defects(pred, cable_cls=1, tape_cls=2, defect_classes=(3, 4, 5, 6), hole_min_size=10):
+    """analyze_defects, src/utils/geometry_enhanced.py:236-330 -> dict with the dataclass's fields."""
+    h, w = pred.shape
+    tape = (pred == tape_cls).astype(np.uint8)
+    n_tape, _, tstats, _ = cv2.connectedComponentsWithStats(tape, connectivity=8)                    # :267-269
+    closed = cv2.morphologyEx(tape, cv2.MORPH_CLOSE, _ellipse(5))                                    # :273-274
+    holes = ((closed.astype(np.int16) - tape.astype(np.int16)) > 0).astype(np.uint8)                 # :275-276
+    n_h, _, hstats, _ = cv2.connectedComponentsWithStats(holes, connectivity=8)                      # :279-281
+    ok = [int(a) for a in (hstats[1:, cv2.CC_STAT_AREA] if n_h > 1 else []) if a >= hole_min_size]   # :283-285
+    n_cable = cv2.connectedComponentsWithStats((pred == cable_cls).astype(np.uint8), connectivity=8)[0]
+    areas = {int(c): int((pred == c).sum()) for c in defect_classes}                                 # :308-314
+    n_tape = max(0, n_tape - 1)
+    return dict(tape_hole_ratio=sum(ok) / max(int(tape.sum()), 1), tape_num_holes=len(ok), tape_coverage=tape.sum() / (h * w),
+                cable_num_components=max(0, n_cable - 1), tape_num_components=n_tape,
+                tape_largest_area_ratio=(tstats[1:, cv2.CC_STAT_AREA].max() / tape.sum()) if n_tape > 0 else 0.0,
+                defect_areas=areas, total_defect_area=sum(areas.values()))

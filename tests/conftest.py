@@ -93,3 +93,19 @@ def geometry_cases(g):
         p = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape))
         assert zlib.crc32(p.tobytes()) == int(g["pred_crc"][i]), "synth.pred_classes changed; rerun tests/golden/make_golden.py geometry"
         yield p, g["metrics"][2 * i], g["metrics"][2 * i + 1]
+
+
+def defect_cases(g):
+    """(pred, hole_min_size, golden row) behind tests/golden/geometry.npz['defects']."""
+    import unet_b200.synth as S
+    for i, (h, w, seed, tape) in enumerate(g["cases"]):
+        p = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape), defects=True)
+        assert zlib.crc32(p.tobytes()) == int(g["defects_crc"][i])
+        for j, hole_min in enumerate((10, 2)):
+            yield p, hole_min, g["defects"][2 * i + j]
+
+
+def defect_row(d):
+    get = (lambda k: d[k]) if isinstance(d, dict) else (lambda k: getattr(d, k))
+    return [float(get("tape_hole_ratio")), get("tape_num_holes"), float(get("tape_coverage")), get("cable_num_components"),
+            get("tape_num_components"), float(get("tape_largest_area_ratio")), get("total_defect_area")] + [get("defect_areas")[c] for c in (3, 4, 5, 6)]

@@ -183,6 +183,19 @@ def geometry():
         rows.append([float(getattr(m2, f)) for f in GEOM_FIELDS])
     out["metrics"] = np.array(rows, np.float64)
     out["pred_crc"] = np.array(crcs, np.uint32)
+    # analyze_defects (:236-330) on the same maps with defect classes and pin-holes added
+    from src.utils.geometry_enhanced import analyze_defects
+    drows, dcrc = [], []
+    for (h, w), seed, tape in GEOM_CASES:
+        p = S.pred_classes(h, w, seed=seed, tape=tape, defects=True)
+        dcrc.append(zlib.crc32(p.tobytes()))
+        for hole_min in (10, 2):
+            d = analyze_defects(p, hole_min_size=hole_min)
+            drows.append([float(d.tape_hole_ratio), d.tape_num_holes, float(d.tape_coverage), d.cable_num_components,
+                          d.tape_num_components, float(d.tape_largest_area_ratio), d.total_defect_area] +
+                         [d.defect_areas[c] for c in (3, 4, 5, 6)])
+    out["defects"] = np.array(drows, np.float64)
+    out["defects_crc"] = np.array(dcrc, np.uint32)
     np.savez_compressed(os.path.join(HERE, "geometry.npz"), **out)
 
 

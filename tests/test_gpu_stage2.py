@@ -251,3 +251,17 @@ def test_diameter_metrics_golden_and_oracle(golden_geometry):
         assert [float(getattr(got[i], f)) for f in GEOM_FIELDS] == [float(want[f]) for f in GEOM_FIELDS], (i, got[i], want)
     empty = U.compute_diameter_metrics(np.zeros((64, 64), np.uint8))
     assert empty.valid_rows == 0 and empty.dc_px == 0.0 and empty.cable_coverage == 0.0
+
+
+def test_analyze_defects_golden_and_oracle(golden_geometry):
+    """ops.analyze_defects (ub_analyze_defects) == the real reference's fields exactly; batched device call == oracle."""
+    from conftest import defect_cases, defect_row
+    from unet_b200 import ops as U
+    for pred, hole_min, want in defect_cases(golden_geometry):
+        assert defect_row(U.analyze_defects(pred, hole_min_size=hole_min)) == list(want), (pred.shape, hole_min)
+    preds = np.stack([S.pred_classes(448, 800, seed=30 + i, tape=i != 1, defects=True) for i in range(3)])
+    got = U.analyze_defects(dev(preds), hole_min_size=4)
+    for i in range(3):
+        assert defect_row(got[i]) == defect_row(R.analyze_defects(preds[i], hole_min_size=4)), i
+    z = U.analyze_defects(np.zeros((48, 64), np.uint8))
+    assert z.tape_num_components == 0 and z.tape_largest_area_ratio == 0.0 and z.tape_hole_ratio == 0.0 and z.total_defect_area == 0

@@ -116,3 +116,10 @@ def test_diameter_metrics_match_reference(golden_geometry, use_cv2):
         assert [float(got[f]) for f in GEOM_FIELDS] == list(want), (pred.shape, got)
         got = R.diameter_metrics(pred, mm_per_px=0.1, min_valid_rows=1000, use_cv2=use_cv2)
         assert [float(got[f]) for f in GEOM_FIELDS] == list(want_short)
+
+
+def test_analyze_defects_matches_reference(golden_geometry):
+    """oracle analyze_defects == the real analyze_defects (src/utils/geometry_enhanced.py:236-330), every field."""
+    from conftest import defect_cases, defect_row
+    for pred, hole_min, want in defect_cases(golden_geometry):
+        assert defect_row(R.analyze_defects(pred, hole_min_size=hole_min)) == list(want), (pred.shape, hole_min)

@@ -51,6 +51,7 @@ def measure(B=512, reps=10, log=None):
         ("ub_blur_canny: k_edge_fused<1> + union-find hysteresis", lambda: ctx.blur_canny(gray, 50, 150), 2 * P),
         ("ub_burr: edges + band + morphology + CCL + filter", lambda: ctx.burr(gray, mask), 3 * P),
         ("ub_diameter_metrics: 2 x (CCL + largest component + row extents) + smoothing + medians", lambda: ctx.diameter_metrics(preds), P),
+        ("ub_analyze_defects: 3 x CCL + CLOSE 5x5 + class histogram", lambda: ctx.analyze_defects(preds), P),
         ("ub_morph close 3x3 (per-operator kernel, not on the pipeline path)", lambda: ctx.morph("close", 3, mask), 2 * P),
         ("ub_morph dilate 8x8 (per-operator kernel, not on the pipeline path)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
     ]

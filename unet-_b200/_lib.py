@@ -57,6 +57,7 @@ SIGNATURES = {
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
     "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
     "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_analyze_defects": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -244,6 +245,14 @@ class Context:
         out = torch.empty((b, 8), dtype=torch.int32, device=pred.device)
         self._check(lib().ub_diameter_metrics(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, min_area,
                                               min_valid_rows, out.data_ptr(), self.stream))
+        return out
+
+    def analyze_defects(self, pred, cable_cls=1, tape_cls=2, hole_min_size=10):
+        """pred u8 [B,H,W] class ids -> int32 [B,16] (see ub_analyze_defects)."""
+        b, h, w = pred.shape
+        out = torch.empty((b, 16), dtype=torch.int32, device=pred.device)
+        self._check(lib().ub_analyze_defects(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, hole_min_size,
+                                             out.data_ptr(), self.stream))
         return out
 
     def _u8op(self, fn, src, *args):

@@ -853,3 +853,98 @@ int diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int 
   UB_CHECK_LAUNCH(ctx);
   return UB_OK;
 }
+
+// =====================================================================================================
+// analyze_defects (src/utils/geometry_enhanced.py:236-330): tape coverage, tape / cable component counts, largest
+// tape component, holes = CLOSE(tape, ELLIPSE 5x5) - tape with components of area >= hole_min_size counted and
+// summed, and the pixel count of every class id (defect_areas).
+// out[b] = { tape_px, tape_components, tape_largest_area, holes (>= min size), hole_px (of those), cable_components, 0, 0,
+//            count[class 0..7] }   (int32 [B][16])
+// =====================================================================================================
+namespace s2 {
+
+// per-frame summary of a labelled plane: acc[0] += components, acc[1] = max area, acc[2] += components with area >= min_area,
+// acc[3] += their area, acc[4] += foreground pixels
+__global__ void __launch_bounds__(256) k_comp_summary(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                      const int* __restrict__ comp, int min_area, int* __restrict__ acc_all, int acc_stride) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  if (!c) return;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  int* acc = acc_all + (size_t)blockIdx.z * acc_stride;
+  atomicAdd(acc + 4, __popc(c));
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int p = y * W + 32 * w + a;
+    if (lab_all[base + p] != p) continue;
+    const int area = comp[base + p];
+    atomicAdd(acc, 1);
+    atomicMax(acc + 1, area);
+    if (area >= min_area) { atomicAdd(acc + 2, 1); atomicAdd(acc + 3, area); }
+  }
+}
+
+// holes = closed & ~tape as bytes {0,1};  class histogram (ids 0..7) with one shared-memory histogram per block
+__global__ void __launch_bounds__(256) k_holes_hist(const uint8_t* __restrict__ pred, const uint8_t* __restrict__ closed, const uint8_t* __restrict__ tape,
+                                                    uint8_t* __restrict__ holes, int HW, int* __restrict__ hist_all, int hist_stride) {
+  __shared__ int s_h[8];
+  if (threadIdx.x < 8) s_h[threadIdx.x] = 0;
+  __syncthreads();
+  const size_t base = (size_t)blockIdx.y * HW;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < HW) {
+    holes[base + i] = (closed[base + i] != 0 && tape[base + i] == 0) ? 1 : 0;
+    const int c = pred[base + i];
+    if (c < 8) atomicAdd(&s_h[c], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x < 8 && s_h[threadIdx.x]) atomicAdd(hist_all + (size_t)blockIdx.y * hist_stride + threadIdx.x, s_h[threadIdx.x]);
+}
+
+__global__ void k_defects_pack(const int* __restrict__ acc, int B, int32_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int* a = acc + (size_t)b * 16;
+  int32_t* o = out + (size_t)b * 16;
+  o[0] = a[4]; o[1] = a[0]; o[2] = a[1];           // tape pixels, components, largest area
+  o[3] = a[5 + 2]; o[4] = a[5 + 3];                // holes of area >= hole_min_size, their pixels
+  o[5] = a[10];                                    // cable components
+}
+
+}  // namespace s2
+
+int analyze_defects(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int hole_min_size,
+                    int32_t* out, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const size_t n = (size_t)B * H * W, plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
+  const int Wd = (W + 31) / 32;
+  uint8_t *tape = ctx->d_tmp[0], *other = ctx->d_tmp[1], *closed = ctx->d_tmp[2], *tmp = ctx->d_tmp[3];
+  int* lab = ctx->d_lab[0];
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  int* acc = ctx->d_counts;                        // [B][16]: three 5-int summaries per frame (tape, holes, cable)
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  const unsigned gm = (unsigned)((n / 4 + 255) / 256 + 1);
+  UB_CUDA(ctx, cudaMemsetAsync(acc, 0, sizeof(int) * 16 * B, st));
+  UB_CUDA(ctx, cudaMemsetAsync(out, 0, sizeof(int32_t) * 16 * B, st));
+  // tape: components, largest, pixels
+  k_class_mask<<<gm, 256, 0, st>>>(pred, tape, n, tape_cls);
+  RUN(cclb_label(ctx, tape, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+  k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+  k_comp_summary<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, 0, acc, 16);
+  // holes = CLOSE(tape, 5x5) - tape, class histogram
+  RUN(morph_op(ctx, 2, 5, tape, closed, tmp, B, H, W, 1, st));
+  k_holes_hist<<<dim3(cdiv(H * W, 256), B), 256, 0, st>>>(pred, closed, tape, other, H * W, out + 8, 16);
+  RUN(cclb_label(ctx, other, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+  k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+  k_comp_summary<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, hole_min_size, acc + 5, 16);
+  // cable: component count
+  k_class_mask<<<gm, 256, 0, st>>>(pred, other, n, cable_cls);
+  RUN(cclb_label(ctx, other, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+  k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+  k_comp_summary<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, 0, acc + 10, 16);
+  k_defects_pack<<<cdiv(B, 128), 128, 0, st>>>(acc, B, out);
+  UB_CHECK_LAUNCH_N(ctx, 10);
+  return UB_OK;
+}

@@ -9,6 +9,7 @@ Same names, argument meaning and results as the reference functions:
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
   get_burr_mask_rulebased src/refactor/burr_detector.py:11-66 (the Laplacian-band detector of the refactored library)
   compute_diameter_metrics src/utils/geometry_enhanced.py:113-187 (Dc / Dt / delta-D of the refactored library)
+  analyze_defects         src/utils/geometry_enhanced.py:236-330 (coverage, components, hole ratio, defect areas)
   visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
@@ -170,6 +171,39 @@ def compute_diameter_metrics(pred_mask, cable_cls=1, tape_cls=2, mm_per_px=0.05,
         res.append(DiameterMetrics(dc_px=dc_px, dt_px=dt_px, delta_d_px=dt_px - dc_px, dc_mm=dc_mm, dt_mm=dt_mm,
                                    delta_d_mm=dt_mm - dc_mm, valid_rows=valid_rows, cable_coverage=int(r[3]) / (h * w),
                                    tape_coverage=int(r[4]) / (h * w)))
+    return res[0] if single else res
+
+
+class DefectAnalysis:
+    """Same fields as the reference's dataclass (src/utils/geometry_enhanced.py:216-233)."""
+    __slots__ = ("tape_hole_ratio", "tape_num_holes", "tape_coverage", "cable_num_components", "tape_num_components",
+                 "tape_largest_area_ratio", "defect_areas", "total_defect_area")
+
+    def __init__(self, **kw):
+        for k in self.__slots__:
+            setattr(self, k, kw[k])
+
+    def __repr__(self):
+        return "DefectAnalysis(" + ", ".join(f"{k}={getattr(self, k)!r}" for k in self.__slots__) + ")"
+
+
+def analyze_defects(pred_mask, cable_cls=1, tape_cls=2, defect_classes=(3, 4, 5, 6), hole_min_size=10):
+    """analyze_defects(pred_mask, cable_cls, tape_cls, defect_classes, hole_min_size)
+    (src/utils/geometry_enhanced.py:236-330).  numpy [H,W] -> one DefectAnalysis; CUDA tensor [B,H,W] -> list.
+    Class ids must be < 8.  Labelling, the 5x5 CLOSE, hole components and the class histogram run on the device."""
+    f, was_np, single = _batched(pred_mask, 2)
+    b, h, w = f.shape
+    c = _ctx(f.device, b, (h, w), (16, 16))
+    with torch.cuda.device(f.device):
+        raw = c.analyze_defects(f, cable_cls, tape_cls, hole_min_size).cpu().numpy()
+    res = []
+    for r in raw:
+        tape_px, tape_n, tape_largest, holes, hole_px, cable_n = (int(v) for v in r[:6])
+        areas = {int(cls): int(r[8 + cls]) for cls in defect_classes}
+        res.append(DefectAnalysis(tape_hole_ratio=hole_px / max(tape_px, 1), tape_num_holes=holes, tape_coverage=tape_px / (h * w),
+                                  cable_num_components=cable_n, tape_num_components=tape_n,
+                                  tape_largest_area_ratio=(tape_largest / tape_px) if tape_n > 0 else 0.0,
+                                  defect_areas=areas, total_defect_area=sum(areas.values())))
     return res[0] if single else res
 
 

@@ -63,7 +63,7 @@ def mask_blobs(h: int, w: int, seed: int = 0, fill: float = 0.3) -> np.ndarray:
     return (rng.random((h, w)) < fill).astype(np.uint8)
 
 
-def pred_classes(h: int = 512, w: int = 512, seed: int = 0, tape: bool = True) -> np.ndarray:
+def pred_classes(h: int = 512, w: int = 512, seed: int = 0, tape: bool = True, defects: bool = False) -> np.ndarray:
     """Synthetic class-id map (0 background, 1 cable, 2 tape) for the geometry measurements: a wobbling cable
     band with ragged edges, a tape wrap that covers it over a range of rows and hugs it on both sides elsewhere,
     plus stray blobs and single-pixel specks of both classes."""
@@ -92,6 +92,13 @@ def pred_classes(h: int = 512, w: int = 512, seed: int = 0, tape: bool = True) -
     specks = rng.random((h, w))
     p[specks < 0.002] = 1
     p[specks > 0.998] = 2
+    if defects:                                                   # defect classes 3..6 and pin-holes in the tape
+        for cls in (3, 4, 5, 6):
+            for _ in range(3):
+                by, bx = rng.integers(0, h - 10), rng.integers(0, w - 10)
+                bh, bw = rng.integers(1, 10, 2)
+                p[by:by + bh, bx:bx + bw] = cls
+        p[(p == 2) & (rng.random((h, w)) < 0.03)] = 0
     return p
 
 
