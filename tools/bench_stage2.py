@@ -52,8 +52,8 @@ def measure(B=512, reps=10, log=None):
         ("ub_burr: edges + band + morphology + CCL + filter", lambda: ctx.burr(gray, mask), 3 * P),
         ("ub_diameter_metrics: 2 x (CCL + largest component + row extents) + smoothing + medians", lambda: ctx.diameter_metrics(preds), P),
         ("ub_analyze_defects: 3 x CCL + CLOSE 5x5 + class histogram", lambda: ctx.analyze_defects(preds), P),
-        ("ub_morph close 3x3 (per-operator kernel, not on the pipeline path)", lambda: ctx.morph("close", 3, mask), 2 * P),
-        ("ub_morph dilate 8x8 (per-operator kernel, not on the pipeline path)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
+        ("ub_morph close 3x3 (k_morph_words)", lambda: ctx.morph("close", 3, mask), 2 * P),
+        ("ub_morph dilate 8x8 (k_morph_words)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
     ]
     out = {"frames": B, "hw": [H, W], "hbm_peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(pk) else "fallback",
            "edge_fused": os.environ.get("UB_EDGE_FUSED", "1"), "ops": []}

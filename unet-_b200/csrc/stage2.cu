@@ -463,18 +463,40 @@ static int morph_once(ub_ctx* ctx, bool dil, int k, const uint8_t* src, uint8_t*
 
 #define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
 
-// op: 0 dilate, 1 erode, 2 close (dilate->erode), 3 open (erode->dilate); tmp needed for 2,3
+template <int HALO>
+static void launch_morph_words(int op, dim3 grid, cudaStream_t st, const uint8_t* src, uint8_t* dst, int H, int W, const Footprint& fp, int value) {
+  switch (op) {
+    case 0: k_morph_words<HALO, 0><<<grid, 256, 0, st>>>(src, dst, H, W, fp, (uint32_t)value); break;
+    case 1: k_morph_words<HALO, 1><<<grid, 256, 0, st>>>(src, dst, H, W, fp, (uint32_t)value); break;
+    case 2: k_morph_words<HALO, 2><<<grid, 256, 0, st>>>(src, dst, H, W, fp, (uint32_t)value); break;
+    default: k_morph_words<HALO, 3><<<grid, 256, 0, st>>>(src, dst, H, W, fp, (uint32_t)value); break;
+  }
+}
+
+// op: 0 dilate, 1 erode, 2 close (dilate->erode), 3 open (erode->dilate); tmp only for the per-pixel fallback (UB_MORPH_WORDS=0)
 int morph_op(ub_ctx* ctx, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_STENCIL, st);
+  static const int words_env = getenv("UB_MORPH_WORDS") ? atoi(getenv("UB_MORPH_WORDS")) : 1;
+  if (op < 0 || op > 3) return ub_fail(ctx, UB_ERR_ARG, "bad morph op %d", op);
+  if (words_env) {
+    Footprint fp;
+    if (!make_footprint(k, fp)) return ub_fail(ctx, UB_ERR_ARG, "ellipse size %d unsupported (1..25)", k);
+    const int halo = (op >= 2 ? 2 : 1) * (k / 2);          // rows the operator reaches above / below (anchor k/2)
+    dim3 grid(cdiv(W, FM_W), cdiv(H, FM_TH), B);
+    if (halo <= 4) launch_morph_words<4>(op, grid, st, src, dst, H, W, fp, value);
+    else if (halo <= 12) launch_morph_words<12>(op, grid, st, src, dst, H, W, fp, value);
+    else launch_morph_words<24>(op, grid, st, src, dst, H, W, fp, value);
+    UB_CHECK_LAUNCH(ctx);
+    return UB_OK;
+  }
   switch (op) {
     case 0: return morph_once(ctx, true, k, src, dst, B, H, W, value, nullptr, st);
     case 1: return morph_once(ctx, false, k, src, dst, B, H, W, value, nullptr, st);
     case 2: RUN(morph_once(ctx, true, k, src, tmp, B, H, W, value, nullptr, st));
             return morph_once(ctx, false, k, tmp, dst, B, H, W, value, nullptr, st);
-    case 3: RUN(morph_once(ctx, false, k, src, tmp, B, H, W, value, nullptr, st));
-            return morph_once(ctx, true, k, tmp, dst, B, H, W, value, nullptr, st);
+    default: RUN(morph_once(ctx, false, k, src, tmp, B, H, W, value, nullptr, st));
+             return morph_once(ctx, true, k, tmp, dst, B, H, W, value, nullptr, st);
   }
-  return ub_fail(ctx, UB_ERR_ARG, "bad morph op %d", op);
 }
 
 static int ccl_label(ub_ctx* ctx, const uint8_t* src, int* lab, int B, int H, int W, int* comp, size_t plane, cudaStream_t st) {

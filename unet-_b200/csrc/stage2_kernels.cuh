@@ -279,6 +279,79 @@ __global__ void __launch_bounds__(256) k_burr_morph(const uint8_t* __restrict__ 
   }
 }
 
+// ------------------------------------------------------------------------------
+// One morphology operator (ub_morph: dilate / erode / close / open with a cv2 ellipse) on bit-packed shared-memory
+// rows, one 32-pixel word per thread and stage -- the per-operator form of k_burr_morph.  HALO rows above and below
+// the 32-row tile (template: 4 / 12 / 24 covers one or two passes of footprints up to 25), one word left and right.
+// Out-of-image samples are ignored as cv2 does (0 before a dilation, 1 before an erosion).
+// ------------------------------------------------------------------------------
+template <bool DILATE, int ROWS>
+__device__ __forceinline__ uint32_t fmw_apply(const uint32_t (*in)[FM_WORDS], int r, int w, const Footprint& fp) {
+  const uint32_t ident = DILATE ? 0u : 0xffffffffu;
+  uint32_t acc = ident;
+  for (int j = 0; j < fp.nrows; ++j) {
+    const int rr = r + fp.dy[j];
+    if (rr < 0 || rr >= ROWS) continue;
+    const uint32_t lo = w > 0 ? in[rr][w - 1] : ident, mid = in[rr][w], hi = w + 1 < FM_WORDS ? in[rr][w + 1] : ident;
+    for (int sft = fp.xa[j]; sft <= fp.xb[j]; ++sft) {
+      const uint32_t v = sft >= 0 ? __funnelshift_r(mid, hi, sft) : __funnelshift_r(lo, mid, 32 + sft);
+      acc = DILATE ? (acc | v) : (acc & v);
+    }
+  }
+  return acc;
+}
+
+// OP: 0 dilate, 1 erode, 2 close (dilate -> erode), 3 open (erode -> dilate)
+template <int HALO, int OP>
+__global__ void __launch_bounds__(256) k_morph_words(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int H, int W,
+                                                     Footprint fp, uint32_t value) {
+  constexpr int ROWS = FM_TH + 2 * HALO, NW = ROWS * FM_WORDS;
+  constexpr bool FIRST_DIL = OP == 0 || OP == 2;
+  __shared__ uint32_t s_a[ROWS][FM_WORDS], s_b[OP >= 2 ? ROWS : 1][FM_WORDS], s_in[OP >= 1 ? ROWS : 1][FM_WORDS];
+  const int x0 = blockIdx.x * FM_W, y0 = blockIdx.y * FM_TH;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  for (int i = threadIdx.x; i < NW; i += 256) {
+    const int r = i / FM_WORDS, w = i - r * FM_WORDS;
+    const int y = y0 - HALO + r, x = x0 - 32 + 32 * w;
+    const uint32_t b = pack32(src + base, H, W, y, x);
+    if (OP >= 1) {
+      const uint32_t in = inside32(H, W, y, x);
+      s_in[r][w] = in;
+      s_a[r][w] = FIRST_DIL ? b : (b | ~in);
+    } else {
+      s_a[r][w] = b;
+    }
+  }
+  __syncthreads();
+  if (OP >= 2) {
+    for (int i = threadIdx.x; i < NW; i += 256) {
+      const int r = i / FM_WORDS, w = i - r * FM_WORDS;
+      s_b[r][w] = FIRST_DIL ? (fmw_apply<true, ROWS>(s_a, r, w, fp) | ~s_in[r][w]) : (fmw_apply<false, ROWS>(s_a, r, w, fp) & s_in[r][w]);
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < FM_TH * (FM_W / 32); i += 256) {
+    const int ty = i / (FM_W / 32), tw = i - ty * (FM_W / 32);
+    const int y = y0 + ty, x = x0 + 32 * tw;
+    if (y >= H || x >= W) continue;
+    uint32_t word;
+    if (OP == 0) word = fmw_apply<true, ROWS>(s_a, ty + HALO, tw + 1, fp);
+    else if (OP == 1) word = fmw_apply<false, ROWS>(s_a, ty + HALO, tw + 1, fp);
+    else if (OP == 2) word = fmw_apply<false, ROWS>(s_b, ty + HALO, tw + 1, fp);
+    else word = fmw_apply<true, ROWS>(s_b, ty + HALO, tw + 1, fp);
+    uint8_t* o = dst + base + (size_t)y * W + x;
+    if (x + 32 <= W && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      uint32_t v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = ((((word >> (4 * k)) & 15u) * 0x00204081u) & 0x01010101u) * value;
+      *reinterpret_cast<uint4*>(o) = make_uint4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<uint4*>(o + 16) = make_uint4(v[4], v[5], v[6], v[7]);
+    } else {
+      for (int k = 0; k < 32 && x + k < W; ++k) o[k] = ((word >> k) & 1u) ? (uint8_t)value : 0;
+    }
+  }
+}
+
 // out = (a != 0 && b != 0) ? 1 : 0     (edges & detection_band, infer_two_stage_burr.py:89)
 __global__ void k_and01(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, uint8_t* __restrict__ out, size_t n) {
   size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
