@@ -673,7 +673,9 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
   if (fuse_env && 2 * (P.open_k / 2) + 2 * (P.close_k / 2) + P.band_k / 2 <= FM_HALO) {
     // band, candidates, CLOSE, OPEN in one pass over bit-packed tiles                -> t2
     TimeScope ts(ctx, UB_T_STENCIL, st);
-    k_burr_morph<<<dim3(cdiv(W, FM_W), cdiv(H, FM_TH), B), 256, 0, st>>>(mask, t1, t2, H, W, mc);
+    const dim3 gm(cdiv(W, FM_W), cdiv(H, FM_TH), B);
+    if (2 * (P.open_k / 2) + 2 * (P.close_k / 2) + P.band_k / 2 <= 8) k_burr_morph<8><<<gm, 256, 0, st>>>(mask, t1, t2, H, W, mc);
+    else k_burr_morph<FM_HALO><<<gm, 256, 0, st>>>(mask, t1, t2, H, W, mc);
     UB_CHECK_LAUNCH(ctx);
   } else {
     {

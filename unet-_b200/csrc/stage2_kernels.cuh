@@ -209,28 +209,33 @@ __device__ __forceinline__ uint32_t inside32(int H, int W, int y, int x) {
 }
 
 // out[r][w] = dilate / erode of plane `in` with footprint fp at word (r, w)
-template <bool DILATE>
+template <bool DILATE, int ROWS>
 __device__ __forceinline__ uint32_t fm_apply(const uint32_t (*in)[FM_WORDS], int r, int w, const Footprint& fp) {
   const uint32_t ident = DILATE ? 0u : 0xffffffffu;
   uint32_t acc = ident;
   for (int j = 0; j < fp.nrows; ++j) {
     const int rr = r + fp.dy[j];
-    if (rr < 0 || rr >= FM_ROWS) continue;
+    if (rr < 0 || rr >= ROWS) continue;
     const uint32_t lo = w > 0 ? in[rr][w - 1] : ident, mid = in[rr][w], hi = w + 1 < FM_WORDS ? in[rr][w + 1] : ident;
-    for (int sft = fp.xa[j]; sft <= fp.xb[j]; ++sft) {
-      const uint32_t v = sft >= 0 ? __funnelshift_r(mid, hi, sft) : __funnelshift_r(lo, mid, 32 + sft);
-      acc = DILATE ? (acc | v) : (acc & v);
-    }
+    // the run [xa, xb] in two loops (left of the word, then from the word on): one funnel shift + one logic op per cell
+    const int xa = fp.xa[j], xb = fp.xb[j];
+    int sft = xa;
+#pragma unroll 4
+    for (; sft < 0 && sft <= xb; ++sft) { const uint32_t v = __funnelshift_r(lo, mid, 32 + sft); acc = DILATE ? (acc | v) : (acc & v); }
+#pragma unroll 4
+    for (; sft <= xb; ++sft) { const uint32_t v = __funnelshift_r(mid, hi, sft); acc = DILATE ? (acc | v) : (acc & v); }
   }
   return acc;
 }
 
+template <int HALO>     // rows of halo above / below the 32-row tile: >= 2*(open/2) + 2*(close/2) + band/2 (8 standard, 20 enhanced)
 __global__ void __launch_bounds__(256) k_burr_morph(const uint8_t* __restrict__ mask, const uint8_t* __restrict__ edges,
                                                     uint8_t* __restrict__ out, int H, int W, MorphChain mc) {
-  __shared__ uint32_t s_a[FM_ROWS][FM_WORDS], s_b[FM_ROWS][FM_WORDS], s_in[FM_ROWS][FM_WORDS];
+  constexpr int ROWS = FM_TH + 2 * HALO;
+  __shared__ uint32_t s_a[ROWS][FM_WORDS], s_b[ROWS][FM_WORDS], s_in[ROWS][FM_WORDS];
   const int x0 = blockIdx.x * FM_W, y0 = blockIdx.y * FM_TH;
   const size_t base = (size_t)blockIdx.z * H * W;
-  constexpr int NW = FM_ROWS * FM_WORDS;
+  constexpr int NW = ROWS * FM_WORDS;
   uint32_t e_bits[(NW + 255) / 256], m_bits[(NW + 255) / 256];
   // load: s_a = mask bits, registers keep the edge / mask words of this thread's positions
 #pragma unroll
@@ -238,7 +243,7 @@ __global__ void __launch_bounds__(256) k_burr_morph(const uint8_t* __restrict__ 
     const int i = threadIdx.x + k * 256;
     if (i < NW) {
       const int r = i / FM_WORDS, w = i - r * FM_WORDS;
-      const int y = y0 - FM_HALO + r, x = x0 - 32 + 32 * w;
+      const int y = y0 - HALO + r, x = x0 - 32 + 32 * w;
       m_bits[k] = pack32(mask + base, H, W, y, x);
       e_bits[k] = pack32(edges + base, H, W, y, x);
       s_a[r][w] = m_bits[k];
@@ -250,22 +255,22 @@ __global__ void __launch_bounds__(256) k_burr_morph(const uint8_t* __restrict__ 
 #pragma unroll
   for (int k = 0; k < (NW + 255) / 256; ++k) {
     const int i = threadIdx.x + k * 256;
-    if (i < NW) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<true>(s_a, r, w, mc.band) & ~m_bits[k] & e_bits[k]; }
+    if (i < NW) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<true, ROWS>(s_a, r, w, mc.band) & ~m_bits[k] & e_bits[k]; }
   }
   __syncthreads();
   // CLOSE: dilate -> s_a (forced to 1 outside the image for the erosion that follows), erode -> s_b
-  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<true>(s_b, r, w, mc.close) | ~s_in[r][w]; }
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<true, ROWS>(s_b, r, w, mc.close) | ~s_in[r][w]; }
   __syncthreads();
-  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<false>(s_a, r, w, mc.close) | ~s_in[r][w]; }
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_b[r][w] = fm_apply<false, ROWS>(s_a, r, w, mc.close) | ~s_in[r][w]; }
   __syncthreads();
   // OPEN: erode -> s_a (forced to 0 outside for the dilation), dilate -> output
-  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<false>(s_b, r, w, mc.open) & s_in[r][w]; }
+  for (int i = threadIdx.x; i < NW; i += 256) { const int r = i / FM_WORDS, w = i - r * FM_WORDS; s_a[r][w] = fm_apply<false, ROWS>(s_b, r, w, mc.open) & s_in[r][w]; }
   __syncthreads();
   for (int i = threadIdx.x; i < FM_TH * (FM_W / 32); i += 256) {
     const int ty = i / (FM_W / 32), tw = i - ty * (FM_W / 32);
     const int y = y0 + ty, x = x0 + 32 * tw;
     if (y >= H || x >= W) continue;
-    const uint32_t word = fm_apply<true>(s_a, ty + FM_HALO, tw + 1, mc.open);
+    const uint32_t word = fm_apply<true, ROWS>(s_a, ty + HALO, tw + 1, mc.open);
     uint8_t* o = out + base + (size_t)y * W + x;
     if (x + 32 <= W && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
       uint32_t v[8];
@@ -293,10 +298,13 @@ __device__ __forceinline__ uint32_t fmw_apply(const uint32_t (*in)[FM_WORDS], in
     const int rr = r + fp.dy[j];
     if (rr < 0 || rr >= ROWS) continue;
     const uint32_t lo = w > 0 ? in[rr][w - 1] : ident, mid = in[rr][w], hi = w + 1 < FM_WORDS ? in[rr][w + 1] : ident;
-    for (int sft = fp.xa[j]; sft <= fp.xb[j]; ++sft) {
-      const uint32_t v = sft >= 0 ? __funnelshift_r(mid, hi, sft) : __funnelshift_r(lo, mid, 32 + sft);
-      acc = DILATE ? (acc | v) : (acc & v);
-    }
+    // the run [xa, xb] in two loops (left of the word, then from the word on): one funnel shift + one logic op per cell
+    const int xa = fp.xa[j], xb = fp.xb[j];
+    int sft = xa;
+#pragma unroll 4
+    for (; sft < 0 && sft <= xb; ++sft) { const uint32_t v = __funnelshift_r(lo, mid, 32 + sft); acc = DILATE ? (acc | v) : (acc & v); }
+#pragma unroll 4
+    for (; sft <= xb; ++sft) { const uint32_t v = __funnelshift_r(mid, hi, sft); acc = DILATE ? (acc | v) : (acc & v); }
   }
   return acc;
 }
