@@ -131,6 +131,12 @@ int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int 
 int ub_analyze_defects(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
                        int hole_min_size, int32_t* out_dev, void* stream);
 
+/* _compute_width_per_row(mask, smooth=True, kernel_size=31) (src/utils/geometry_enhanced.py:45-76) for the cable and the
+ * tape class of pred u8 [B,H,W], as compute_thickness_profile uses it (:208-212): out float [B][2][H] = per-row extent
+ * max_x - min_x + 1 of every pixel of the class (0 for empty rows) after cv2's float32 GaussianBlur((1,31), 0). */
+int ub_width_profiles(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
+                      float* out_dev, void* stream);
+
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */

@@ -341,3 +341,10 @@ def analyze_defects(pred, cable_cls=1, tape_cls=2, defect_classes=(3, 4, 5, 6), 
                 cable_num_components=max(0, n_cable - 1), tape_num_components=n_tape,
                 tape_largest_area_ratio=(tstats[1:, cv2.CC_STAT_AREA].max() / tape.sum()) if n_tape > 0 else 0.0,
                 defect_areas=areas, total_defect_area=sum(areas.values()))
+
+
+def thickness_profile(pred, cable_cls=1, tape_cls=2, mm_per_px=0.05, use_cv2=True):
+    """compute_thickness_profile, src/utils/geometry_enhanced.py:190-228 -> (delta_d_mm float32 [H], valid bool [H])."""
+    cw = _row_widths((pred == cable_cls).astype(np.uint8), use_cv2)
+    tw = _row_widths((pred == tape_cls).astype(np.uint8), use_cv2)
+    return (tw - cw) * mm_per_px, (cw > 0) & (tw > 0)

@@ -194,6 +194,12 @@ def geometry():
             drows.append([float(d.tape_hole_ratio), d.tape_num_holes, float(d.tape_coverage), d.cable_num_components,
                           d.tape_num_components, float(d.tape_largest_area_ratio), d.total_defect_area] +
                          [d.defect_areas[c] for c in (3, 4, 5, 6)])
+    from src.utils.geometry_enhanced import compute_thickness_profile
+    for i, ((h, w), seed, tape) in enumerate(GEOM_CASES):
+        t = compute_thickness_profile(S.pred_classes(h, w, seed=seed, tape=tape, defects=True), mm_per_px=0.07)
+        assert np.array_equal(t.y_coords, np.arange(h)) and t.delta_d_mm.dtype == np.float32
+        out[f"profile_{i}"] = t.delta_d_mm
+        out[f"profile_valid_{i}"] = np.packbits(t.valid_mask)
     out["defects"] = np.array(drows, np.float64)
     out["defects_crc"] = np.array(dcrc, np.uint32)
     np.savez_compressed(os.path.join(HERE, "geometry.npz"), **out)

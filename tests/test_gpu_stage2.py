@@ -265,3 +265,19 @@ def test_analyze_defects_golden_and_oracle(golden_geometry):
         assert defect_row(got[i]) == defect_row(R.analyze_defects(preds[i], hole_min_size=4)), i
     z = U.analyze_defects(np.zeros((48, 64), np.uint8))
     assert z.tape_num_components == 0 and z.tape_largest_area_ratio == 0.0 and z.tape_hole_ratio == 0.0 and z.total_defect_area == 0
+
+
+def test_thickness_profile_golden_and_oracle(golden_geometry):
+    """ops.compute_thickness_profile (ub_width_profiles) == the real reference's arrays, bit for bit."""
+    from unet_b200 import ops as U
+    g = golden_geometry
+    for i, (h, w, seed, tape) in enumerate(g["cases"]):
+        pred = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape), defects=True)
+        t = U.compute_thickness_profile(pred, mm_per_px=0.07)
+        assert t.delta_d_mm.dtype == np.float32 and np.array_equal(t.delta_d_mm, g[f"profile_{i}"]), i
+        assert np.array_equal(np.packbits(t.valid_mask), g[f"profile_valid_{i}"]) and np.array_equal(t.y_coords, np.arange(h))
+    preds = np.stack([S.pred_classes(448, 800, seed=40 + i, tape=i != 1, defects=True) for i in range(3)])
+    got = U.compute_thickness_profile(dev(preds))
+    for i in range(3):
+        d, valid = R.thickness_profile(preds[i])
+        assert np.array_equal(got[i].delta_d_mm, d) and np.array_equal(got[i].valid_mask, valid), i

@@ -123,3 +123,15 @@ def test_analyze_defects_matches_reference(golden_geometry):
     from conftest import defect_cases, defect_row
     for pred, hole_min, want in defect_cases(golden_geometry):
         assert defect_row(R.analyze_defects(pred, hole_min_size=hole_min)) == list(want), (pred.shape, hole_min)
+
+
+@pytest.mark.parametrize("use_cv2", [True, False])
+def test_thickness_profile_matches_reference(golden_geometry, use_cv2):
+    """oracle thickness_profile == the real compute_thickness_profile (src/utils/geometry_enhanced.py:190-228)."""
+    import unet_b200.synth as S
+    g = golden_geometry
+    for i, (h, w, seed, tape) in enumerate(g["cases"]):
+        pred = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape), defects=True)
+        d, valid = R.thickness_profile(pred, mm_per_px=0.07, use_cv2=use_cv2)
+        assert d.dtype == np.float32 and np.array_equal(d, g[f"profile_{i}"]), i
+        assert np.array_equal(np.packbits(valid), g[f"profile_valid_{i}"]), i

@@ -58,6 +58,7 @@ SIGNATURES = {
     "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
     "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_analyze_defects": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_width_profiles": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -253,6 +254,13 @@ class Context:
         out = torch.empty((b, 16), dtype=torch.int32, device=pred.device)
         self._check(lib().ub_analyze_defects(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, hole_min_size,
                                              out.data_ptr(), self.stream))
+        return out
+
+    def width_profiles(self, pred, cable_cls=1, tape_cls=2):
+        """pred u8 [B,H,W] -> float32 [B,2,H]: smoothed per-row widths of the cable and the tape class."""
+        b, h, w = pred.shape
+        out = torch.empty((b, 2, h), dtype=torch.float32, device=pred.device)
+        self._check(lib().ub_width_profiles(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, out.data_ptr(), self.stream))
         return out
 
     def _u8op(self, fn, src, *args):

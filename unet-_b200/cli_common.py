@@ -254,4 +254,6 @@ def dist_env():
         dist.all_gather(parts, pad)
         return torch.cat([p[: int(k)] for p, k in zip(parts, sizes)]).cpu().numpy()
 
+    import atexit
+    atexit.register(lambda: dist.is_initialized() and dist.destroy_process_group())
     return rank, world, gather

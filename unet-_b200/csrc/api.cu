@@ -47,6 +47,7 @@ int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int,
 int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t);
 int diameter_metrics(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int analyze_defects(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int32_t*, cudaStream_t);
+int width_profiles(ub_ctx*, const uint8_t*, int, int, int, int, int, float*, cudaStream_t);
 int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
 int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
 
@@ -311,6 +312,13 @@ int ub_analyze_defects(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, in
   if (!pred || !out) return ub_fail(ctx, UB_ERR_ARG, "null argument");
   RUN(check_frame_shape(ctx, B, H, W));
   return analyze_defects(ctx, pred, B, H, W, cable_cls, tape_cls, hole_min_size, out, as_stream(stream));
+}
+
+int ub_width_profiles(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, float* out, void* stream) {
+  NEED_CTX(ctx);
+  if (!pred || !out) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return width_profiles(ctx, pred, B, H, W, cable_cls, tape_cls, out, as_stream(stream));
 }
 
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {

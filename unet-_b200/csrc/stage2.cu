@@ -755,10 +755,11 @@ __global__ void __launch_bounds__(256) k_diam_select(const uint32_t* __restrict_
 // one warp per (frame, row): extent of the best component in the row -> width (0 when absent)
 __global__ void __launch_bounds__(256) k_diam_rows(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
                                                    const int* __restrict__ comp, size_t plane,
-                                                   const unsigned long long* __restrict__ best, float* __restrict__ widths) {
+                                                   const unsigned long long* __restrict__ best, float* __restrict__ widths,
+                                                   int frame_stride) {
   const int y = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (y >= H) return;
-  const unsigned long long b = best[blockIdx.z];
+  const unsigned long long b = best ? best[blockIdx.z] : ~0ull;              // best == nullptr: every run of the plane counts
   const int b_area = (int)(b >> 32), b_key = INT_MAX - (int)(uint32_t)b;
   const size_t base = (size_t)blockIdx.z * H * W;
   int lo = INT_MAX, hi = -1;
@@ -768,12 +769,14 @@ __global__ void __launch_bounds__(256) k_diam_rows(const uint32_t* __restrict__ 
       while (c) {
         int a, len;
         c &= ~first_run(c, a, len);
-        const int x = 32 * w + a, r = lab_all[base + y * W + x];
-        if (comp[base + r] == b_area && comp[5 * plane + base + r] == b_key) { lo = min(lo, x); hi = max(hi, x + len - 1); }
+        const int x = 32 * w + a;
+        bool take = best == nullptr;
+        if (!take) { const int r = lab_all[base + y * W + x]; take = comp[base + r] == b_area && comp[5 * plane + base + r] == b_key; }
+        if (take) { lo = min(lo, x); hi = max(hi, x + len - 1); }
       }
     }
   for (int o = 16; o; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
-  if (lane == 0) widths[(size_t)blockIdx.z * H + y] = hi >= 0 ? (float)(hi - lo + 1) : 0.f;
+  if (lane == 0) widths[(size_t)blockIdx.z * frame_stride + y] = hi >= 0 ? (float)(hi - lo + 1) : 0.f;
 }
 
 // float32(cv2.getGaussianKernel(31, 0)) -- sigma = 0.3*((31-1)*0.5-1)+0.8 = 5; centre first (tests pin the table against cv2)
@@ -846,7 +849,46 @@ __global__ void __launch_bounds__(1024) k_diam_finish(const float* __restrict__ 
   }
 }
 
+// cv2.GaussianBlur(widths.reshape(-1,1), (1,31), 0) for nvec width profiles of H rows each (same arithmetic as k_diam_finish)
+__global__ void __launch_bounds__(256) k_smooth31(const float* __restrict__ in, float* __restrict__ out, int H, int nvec) {
+  const int y = blockIdx.x * 256 + threadIdx.x, v = blockIdx.y;
+  if (y >= H || v >= nvec) return;
+  const float* w = in + (size_t)v * H;
+  float a = __fmul_rn(c_gauss31[0], w[y]);
+  for (int j = 1; j < 16; ++j) a = __fadd_rn(a, __fmul_rn(c_gauss31[j], __fadd_rn(w[reflect101(y + j, H)], w[reflect101(y - j, H)])));
+  out[(size_t)v * H + y] = a;
+}
+
+// pack bits only (no labelling): the thickness profile takes every pixel of the class, not the largest component
+__global__ void __launch_bounds__(256) k_pack_rows(const uint8_t* __restrict__ src, uint32_t* __restrict__ bits, int H, int W, int Wd) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  bits[((size_t)blockIdx.z * H + y) * Wd + w] = pack32(src + (size_t)blockIdx.z * H * W, H, W, y, 32 * w);
+}
+
 }  // namespace s2
+
+// _compute_width_per_row(mask, smooth=True, kernel_size=31) (src/utils/geometry_enhanced.py:45-76) of the cable and the tape
+// class masks, as compute_thickness_profile calls it (:208-212).  out: float [B][2][H] (cable, tape).
+int width_profiles(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, float* out, cudaStream_t st) {
+  if (W < 16 || H < 16) return ub_fail(ctx, UB_ERR_ARG, "ub_width_profiles: %dx%d smaller than 16x16", H, W);
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const size_t n = (size_t)B * H * W;
+  const int Wd = (W + 31) / 32;
+  uint8_t* m = ctx->d_tmp[0];
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  float* raw = reinterpret_cast<float*>(ctx->d_tmp[1]);              // [B][2][H]
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  for (int k = 0; k < 2; ++k) {
+    k_class_mask<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
+    k_pack_rows<<<g, dim3(32, 8), 0, st>>>(m, bits, H, W, Wd);
+    k_diam_rows<<<dim3(cdiv(H, 8), 1, B), 256, 0, st>>>(bits, nullptr, H, W, Wd, nullptr, 0, nullptr, raw + (size_t)k * H, 2 * H);
+    UB_CHECK_LAUNCH_N(ctx, 3);
+  }
+  k_smooth31<<<dim3(cdiv(H, 256), 2 * B), 256, 0, st>>>(raw, out, H, 2 * B);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
 
 // pred: class ids u8 [B,H,W]; out: int32 [B,8] (see k_diam_finish).  Scratch: d_tmp[0], d_lab[0..1], d_comp, d_counts.
 int diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int min_area,
@@ -870,7 +912,7 @@ int diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int 
     k_cclb_stats<true><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
     k_diam_select<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, min_area, best + (size_t)k * B);
     k_diam_rows<<<dim3(cdiv(H, 8), 1, B), 256, 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, best + (size_t)k * B,
-                                                       widths + (size_t)k * B * H);
+                                                       widths + (size_t)k * B * H, H);
     UB_CHECK_LAUNCH_N(ctx, 4);
   }
   k_diam_finish<<<B, 1024, 0, st>>>(widths, widths + (size_t)B * H, H, best, best + B, min_valid_rows, out);

@@ -9,6 +9,7 @@ Same names, argument meaning and results as the reference functions:
   normalize_frame         infer_two_stage_burr.py:275-280 (rotate + resize)
   get_burr_mask_rulebased src/refactor/burr_detector.py:11-66 (the Laplacian-band detector of the refactored library)
   compute_diameter_metrics src/utils/geometry_enhanced.py:113-187 (Dc / Dt / delta-D of the refactored library)
+  compute_thickness_profile src/utils/geometry_enhanced.py:190-228 (per-row delta-D profile)
   analyze_defects         src/utils/geometry_enhanced.py:236-330 (coverage, components, hole ratio, defect areas)
   visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
@@ -171,6 +172,31 @@ def compute_diameter_metrics(pred_mask, cable_cls=1, tape_cls=2, mm_per_px=0.05,
         res.append(DiameterMetrics(dc_px=dc_px, dt_px=dt_px, delta_d_px=dt_px - dc_px, dc_mm=dc_mm, dt_mm=dt_mm,
                                    delta_d_mm=dt_mm - dc_mm, valid_rows=valid_rows, cable_coverage=int(r[3]) / (h * w),
                                    tape_coverage=int(r[4]) / (h * w)))
+    return res[0] if single else res
+
+
+class ThicknessProfile:
+    """Same fields as the reference's dataclass (src/utils/geometry_enhanced.py:37-42)."""
+    __slots__ = ("y_coords", "delta_d_mm", "valid_mask")
+
+    def __init__(self, y_coords, delta_d_mm, valid_mask):
+        self.y_coords, self.delta_d_mm, self.valid_mask = y_coords, delta_d_mm, valid_mask
+
+
+def compute_thickness_profile(pred_mask, cable_cls=1, tape_cls=2, mm_per_px=0.05):
+    """compute_thickness_profile(pred_mask, cable_cls, tape_cls, mm_per_px) (src/utils/geometry_enhanced.py:190-228).
+    numpy [H,W] -> one ThicknessProfile of numpy arrays; CUDA tensor [B,H,W] -> list.  Row extents and the float32
+    smoothing run on the device; the subtraction and the scale are the reference's own numpy expressions."""
+    f, was_np, single = _batched(pred_mask, 2)
+    b, h, w = f.shape
+    c = _ctx(f.device, b, (h, w), (16, 16))
+    with torch.cuda.device(f.device):
+        prof = c.width_profiles(f, cable_cls, tape_cls).cpu().numpy()
+    res = []
+    for p in prof:
+        cw, tw = p[0], p[1]
+        delta_d_px = tw - cw                                          # :215
+        res.append(ThicknessProfile(np.arange(h), delta_d_px * mm_per_px, (cw > 0) & (tw > 0)))   # :216-226
     return res[0] if single else res
 
 
