@@ -137,6 +137,16 @@ int ub_analyze_defects(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W
 int ub_width_profiles(ub_ctx* ctx, const uint8_t* pred_dev, int B, int H, int W, int cable_cls, int tape_cls,
                       float* out_dev, void* stream);
 
+/* filter_cable_by_shape (src/refactor/postprocess.py:12-77): of the 8-connected components of mask (non-zero = set) with
+ * area >= min_area, max(w,h)/(min(w,h)+1e-6) >= min_aspect and |centroid_x - roi_width/2| / roi_width <= max_center_offset,
+ * keep the one with the largest area*aspect*(1-offset) (float64, first label on ties) -> out u8 {0,255}; all zero if none. */
+int ub_filter_cable_by_shape(ub_ctx* ctx, const uint8_t* mask_dev, int B, int H, int W, int min_area, double min_aspect,
+                             double max_center_offset, int roi_width, uint8_t* out_dev, void* stream);
+/* constrain_tape_to_ring (src/refactor/postprocess.py:80-118): ring = dilate(cable, ELLIPSE(dilate_k)) - erode(cable,
+ * ELLIPSE(erode_k)); the largest component of tape & ring -> out u8 {0,255}.  Binary masks ({0,1} or {0,255}). */
+int ub_constrain_tape_to_ring(ub_ctx* ctx, const uint8_t* tape_dev, const uint8_t* cable_dev, int B, int H, int W,
+                              int dilate_k, int erode_k, uint8_t* out_dev, void* stream);
+
 /* ---- stage 2: individual operators (each = one cv2 call of the reference) --------- */
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, uint8_t* dst_dev, void* stream);      /* :85  */
 int ub_canny(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int low, int high, uint8_t* dst_dev, void* stream); /* :86 */

@@ -348,3 +348,40 @@ def thickness_profile(pred, cable_cls=1, tape_cls=2, mm_per_px=0.05, use_cv2=Tru
     cw = _row_widths((pred == cable_cls).astype(np.uint8), use_cv2)
     tw = _row_widths((pred == tape_cls).astype(np.uint8), use_cv2)
     return (tw - cw) * mm_per_px, (cw > 0) & (tw > 0)
+
+
+def filter_cable_by_shape(mask, min_area=1000, min_aspect=1.6, max_center_offset=0.3, roi_width=512):
+    """filter_cable_by_shape, src/refactor/postprocess.py:12-77 (PostprocessConfig defaults, src/refactor/config.py:60-70)."""
+    if mask.max() == 0:
+        return mask
+    n, labels, stats, cent = cv2.connectedComponentsWithStats(mask.astype(np.uint8), connectivity=8)
+    if n <= 1:
+        return np.zeros_like(mask)
+    best_score, best = -1, -1
+    for i in range(1, n):
+        area, w, h = stats[i, cv2.CC_STAT_AREA], stats[i, cv2.CC_STAT_WIDTH], stats[i, cv2.CC_STAT_HEIGHT]
+        if area < min_area:
+            continue
+        aspect = max(w, h) / (min(w, h) + 1e-6)
+        if aspect < min_aspect:
+            continue
+        off = abs(cent[i][0] - roi_width / 2.0) / roi_width
+        if off > max_center_offset:
+            continue
+        score = area * aspect * (1.0 - off)
+        if score > best_score:
+            best_score, best = score, i
+    return (labels == best).astype(np.uint8) * 255 if best > 0 else np.zeros_like(mask)
+
+
+def constrain_tape_to_ring(tape, cable, dilate_k=15, erode_k=5):
+    """constrain_tape_to_ring, src/refactor/postprocess.py:80-118."""
+    if cable.max() == 0 or tape.max() == 0:
+        return np.zeros_like(tape)
+    ring = cv2.subtract(cv2.dilate(cable, _ellipse(dilate_k), iterations=1), cv2.erode(cable, _ellipse(erode_k), iterations=1))
+    con = cv2.bitwise_and(tape, ring)
+    if con.max() > 0:
+        n, labels, stats, _ = cv2.connectedComponentsWithStats(con.astype(np.uint8), connectivity=8)
+        if n > 1:
+            con = (labels == np.argmax(stats[1:, cv2.CC_STAT_AREA]) + 1).astype(np.uint8) * 255
+    return con

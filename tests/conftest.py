@@ -109,3 +109,16 @@ def defect_row(d):
     get = (lambda k: d[k]) if isinstance(d, dict) else (lambda k: getattr(d, k))
     return [float(get("tape_hole_ratio")), get("tape_num_holes"), float(get("tape_coverage")), get("cable_num_components"),
             get("tape_num_components"), float(get("tape_largest_area_ratio")), get("total_defect_area")] + [get("defect_areas")[c] for c in (3, 4, 5, 6)]
+
+
+POST_CFGS = {"default": dict(cable_min_area=1000, cable_min_aspect=1.6, cable_max_center_offset=0.3, tape_ring_dilate=15, tape_ring_erode=5),
+             "loose": dict(cable_min_area=40, cable_min_aspect=1.0, cable_max_center_offset=0.45, tape_ring_dilate=25, tape_ring_erode=3)}
+
+
+def postprocess_cases(g):
+    """(i, name, cfg, cable u8, tape u8, width) behind the cable_* / ring_* entries of tests/golden/geometry.npz."""
+    import unet_b200.synth as S
+    for i, (h, w, seed, tape) in enumerate(g["cases"]):
+        p = S.pred_classes(int(h), int(w), seed=int(seed), tape=bool(tape), defects=True)
+        for name, cfg in POST_CFGS.items():
+            yield i, name, cfg, (p == 1).astype(np.uint8), (p == 2).astype(np.uint8), int(w)

@@ -200,6 +200,19 @@ def geometry():
         assert np.array_equal(t.y_coords, np.arange(h)) and t.delta_d_mm.dtype == np.float32
         out[f"profile_{i}"] = t.delta_d_mm
         out[f"profile_valid_{i}"] = np.packbits(t.valid_mask)
+    # filter_cable_by_shape / constrain_tape_to_ring (src/refactor/postprocess.py) on the class masks of the same maps
+    from src.refactor.postprocess import filter_cable_by_shape, constrain_tape_to_ring
+    from src.refactor.config import PostprocessConfig
+    for i, ((h, w), seed, tape) in enumerate(GEOM_CASES):
+        p = S.pred_classes(h, w, seed=seed, tape=tape, defects=True)
+        cable, tp = (p == 1).astype(np.uint8), (p == 2).astype(np.uint8)
+        for name, cfg in (("default", PostprocessConfig()), ("loose", PostprocessConfig(cable_min_area=40, cable_min_aspect=1.0,
+                                                                                         cable_max_center_offset=0.45, tape_ring_dilate=25, tape_ring_erode=3))):
+            fc = filter_cable_by_shape(cable, cfg, w)
+            out[f"cable_{name}_{i}"] = np.packbits(fc > 0)
+            out[f"cable_{name}_{i}_vals"] = np.unique(fc)
+            out[f"ring_{name}_{i}"] = np.packbits(constrain_tape_to_ring(tp, cable, cfg) > 0)
+            out[f"ring255_{name}_{i}"] = np.packbits(constrain_tape_to_ring(tp * 255, fc, cfg) > 0)
     out["defects"] = np.array(drows, np.float64)
     out["defects_crc"] = np.array(dcrc, np.uint32)
     np.savez_compressed(os.path.join(HERE, "geometry.npz"), **out)

@@ -281,3 +281,29 @@ def test_thickness_profile_golden_and_oracle(golden_geometry):
     for i in range(3):
         d, valid = R.thickness_profile(preds[i])
         assert np.array_equal(got[i].delta_d_mm, d) and np.array_equal(got[i].valid_mask, valid), i
+
+
+def test_postprocess_filters_golden_and_oracle(golden_geometry):
+    """ops.filter_cable_by_shape / ops.constrain_tape_to_ring == the real reference's masks; batched call == oracle."""
+    from conftest import postprocess_cases
+    from unet_b200 import ops as U
+    g = golden_geometry
+    for i, name, cfg, cable, tape, w in postprocess_cases(g):
+        fc = U.filter_cable_by_shape(cable, cfg, w)
+        assert set(np.unique(fc)) <= {0, 255}
+        assert np.array_equal(np.packbits(fc > 0), g[f"cable_{name}_{i}"]), (i, name)
+        ring = U.constrain_tape_to_ring(tape, cable, cfg)
+        assert set(np.unique(ring)) <= {0, 255} and np.array_equal(np.packbits(ring > 0), g[f"ring_{name}_{i}"]), (i, name)
+        assert np.array_equal(np.packbits(U.constrain_tape_to_ring(tape * 255, fc, cfg) > 0), g[f"ring255_{name}_{i}"]), (i, name)
+    preds = np.stack([S.pred_classes(448, 800, seed=50 + i, tape=True, defects=True) for i in range(3)])
+    cable, tape = (preds == 1).astype(np.uint8), (preds == 2).astype(np.uint8)
+    cable[2][:] = 0                                      # two identical blocks: equal score, the first label wins
+    cable[2][300:400, 380:420] = 1
+    cable[2][100:200, 380:420] = 1
+    got = U.filter_cable_by_shape(dev(cable), dict(cable_min_area=100, cable_min_aspect=1.2, cable_max_center_offset=0.4), 800)
+    ring = U.constrain_tape_to_ring(dev(tape), dev(cable))
+    for i in range(3):
+        same("filter_cable", got[i], R.filter_cable_by_shape(cable[i], 100, 1.2, 0.4, 800))
+        same("tape_ring", ring[i], R.constrain_tape_to_ring(tape[i], cable[i]))
+    z = np.zeros((64, 96), np.uint8)
+    assert U.filter_cable_by_shape(z).max() == 0 and U.constrain_tape_to_ring(z, z).max() == 0

@@ -135,3 +135,14 @@ def test_thickness_profile_matches_reference(golden_geometry, use_cv2):
         d, valid = R.thickness_profile(pred, mm_per_px=0.07, use_cv2=use_cv2)
         assert d.dtype == np.float32 and np.array_equal(d, g[f"profile_{i}"]), i
         assert np.array_equal(np.packbits(valid), g[f"profile_valid_{i}"]), i
+
+
+def test_postprocess_filters_match_reference(golden_geometry):
+    """oracle filter_cable_by_shape / constrain_tape_to_ring == the real functions (src/refactor/postprocess.py:12-118)."""
+    from conftest import postprocess_cases
+    g = golden_geometry
+    for i, name, cfg, cable, tape, w in postprocess_cases(g):
+        fc = R.filter_cable_by_shape(cable, cfg["cable_min_area"], cfg["cable_min_aspect"], cfg["cable_max_center_offset"], w)
+        assert np.array_equal(np.packbits(fc > 0), g[f"cable_{name}_{i}"]) and np.array_equal(np.unique(fc), g[f"cable_{name}_{i}_vals"])
+        assert np.array_equal(np.packbits(R.constrain_tape_to_ring(tape, cable, cfg["tape_ring_dilate"], cfg["tape_ring_erode"]) > 0), g[f"ring_{name}_{i}"])
+        assert np.array_equal(np.packbits(R.constrain_tape_to_ring(tape * 255, fc, cfg["tape_ring_dilate"], cfg["tape_ring_erode"]) > 0), g[f"ring255_{name}_{i}"])

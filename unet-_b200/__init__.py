@@ -8,7 +8,7 @@ Host-side mirror of the reference's Python contracts over libunetb200.so:
 """
 __all__ = ["NestedUNet", "InspectionPipeline", "preprocess_image", "map_roi_to_original",
            "detect_burrs_on_cable", "detect_burrs_enhanced", "enhance_image", "bgr2gray",
-           "normalize_frame", "visualize_two_stage", "overlay_blend", "get_burr_mask_rulebased", "compute_diameter_metrics", "analyze_defects", "compute_thickness_profile", "synth"]
+           "normalize_frame", "visualize_two_stage", "overlay_blend", "get_burr_mask_rulebased", "compute_diameter_metrics", "analyze_defects", "compute_thickness_profile", "filter_cable_by_shape", "constrain_tape_to_ring", "synth"]
 
 
 def __getattr__(name):          # lazy: importing the package must not need torch.cuda
@@ -20,7 +20,8 @@ def __getattr__(name):          # lazy: importing the package must not need torc
         return InspectionPipeline
     if name in ("preprocess_image", "map_roi_to_original", "detect_burrs_on_cable", "detect_burrs_enhanced",
                 "enhance_image", "bgr2gray", "normalize_frame", "visualize_two_stage", "overlay_blend",
-                "get_burr_mask_rulebased", "compute_diameter_metrics", "analyze_defects", "compute_thickness_profile"):
+                "get_burr_mask_rulebased", "compute_diameter_metrics", "analyze_defects", "compute_thickness_profile",
+                "filter_cable_by_shape", "constrain_tape_to_ring"):
         from . import ops
         return getattr(ops, name)
     raise AttributeError(name)

@@ -59,6 +59,8 @@ SIGNATURES = {
     "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_analyze_defects": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_width_profiles": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "ub_filter_cable_by_shape": (_I, [_P, _P, _I, _I, _I, _I, C.c_double, C.c_double, _I, _P, _P]),
+    "ub_constrain_tape_to_ring": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_gaussian5": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_blur_canny": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -261,6 +263,20 @@ class Context:
         b, h, w = pred.shape
         out = torch.empty((b, 2, h), dtype=torch.float32, device=pred.device)
         self._check(lib().ub_width_profiles(self._h, self._dev(pred, torch.uint8), b, h, w, cable_cls, tape_cls, out.data_ptr(), self.stream))
+        return out
+
+    def filter_cable_by_shape(self, mask, min_area, min_aspect, max_center_offset, roi_width):
+        b, h, w = mask.shape
+        out = torch.empty_like(mask)
+        self._check(lib().ub_filter_cable_by_shape(self._h, self._dev(mask, torch.uint8), b, h, w, int(min_area), float(min_aspect),
+                                                   float(max_center_offset), int(roi_width), out.data_ptr(), self.stream))
+        return out
+
+    def constrain_tape_to_ring(self, tape, cable, dilate_k, erode_k):
+        b, h, w = tape.shape
+        out = torch.empty_like(tape)
+        self._check(lib().ub_constrain_tape_to_ring(self._h, self._dev(tape, torch.uint8), self._dev(cable, torch.uint8), b, h, w,
+                                                    int(dilate_k), int(erode_k), out.data_ptr(), self.stream))
         return out
 
     def _u8op(self, fn, src, *args):

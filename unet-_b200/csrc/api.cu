@@ -48,6 +48,8 @@ int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaS
 int diameter_metrics(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int analyze_defects(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int width_profiles(ub_ctx*, const uint8_t*, int, int, int, int, int, float*, cudaStream_t);
+int filter_cable_by_shape(ub_ctx*, const uint8_t*, int, int, int, int, double, double, int, uint8_t*, cudaStream_t);
+int constrain_tape_to_ring(ub_ctx*, const uint8_t*, const uint8_t*, int, int, int, int, int, uint8_t*, cudaStream_t);
 int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
 int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
 
@@ -151,7 +153,7 @@ void ub_destroy(ub_ctx* c) {
   for (auto& p : c->d_mask) cudaFree(p);
   for (auto& p : c->d_tmp) cudaFree(p);
   for (auto& p : c->d_lab) cudaFree(p);
-  cudaFree(c->d_comp); cudaFree(c->d_counts); cudaFree(c->d_stats); cudaFree(c->d_logits);
+  cudaFree(c->d_sums); cudaFree(c->d_comp); cudaFree(c->d_counts); cudaFree(c->d_stats); cudaFree(c->d_logits);
   resize_cache_free(c);
   enhance_free(c);
   for (auto& r : c->tm.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -319,6 +321,22 @@ int ub_width_profiles(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int
   if (!pred || !out) return ub_fail(ctx, UB_ERR_ARG, "null argument");
   RUN(check_frame_shape(ctx, B, H, W));
   return width_profiles(ctx, pred, B, H, W, cable_cls, tape_cls, out, as_stream(stream));
+}
+
+int ub_filter_cable_by_shape(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, int min_area, double min_aspect,
+                             double max_center_offset, int roi_width, uint8_t* out, void* stream) {
+  NEED_CTX(ctx);
+  if (!mask || !out || roi_width < 1) return ub_fail(ctx, UB_ERR_ARG, "null argument or roi_width < 1");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return filter_cable_by_shape(ctx, mask, B, H, W, min_area, min_aspect, max_center_offset, roi_width, out, as_stream(stream));
+}
+
+int ub_constrain_tape_to_ring(ub_ctx* ctx, const uint8_t* tape, const uint8_t* cable, int B, int H, int W, int dilate_k, int erode_k,
+                              uint8_t* out, void* stream) {
+  NEED_CTX(ctx);
+  if (!tape || !cable || !out) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return constrain_tape_to_ring(ctx, tape, cable, B, H, W, dilate_k, erode_k, out, as_stream(stream));
 }
 
 int ub_gaussian5(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, uint8_t* dst, void* stream) {

@@ -124,6 +124,7 @@ struct ub_ctx {
   uint8_t* d_tmp[4] = {nullptr};     // u8 planes [B,fh,fw]
   int32_t* d_lab[2] = {nullptr};     // i32 planes [B,fh,fw]
   int32_t* d_comp = nullptr;         // per-pixel component accumulators
+  uint32_t* d_sums = nullptr;        // [B*H*W] per-root x sums (ub_filter_cable_by_shape; allocated on first use)
   int32_t* d_counts = nullptr;       // small per-frame counters
   int32_t* d_stats = nullptr;        // [B,4]
   float* d_logits = nullptr;         // [B,C,nh,nw] fp32 (module path / debug)

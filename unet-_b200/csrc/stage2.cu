@@ -1014,3 +1014,158 @@ int analyze_defects(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int c
   UB_CHECK_LAUNCH_N(ctx, 10);
   return UB_OK;
 }
+
+// =====================================================================================================
+// src/refactor/postprocess.py: filter_cable_by_shape (:12-77) and constrain_tape_to_ring (:80-118).
+// Both end in "keep one component": the first by a float64 score over (area, bounding box, centroid), the second by
+// area; ties go to the smaller OpenCV label (the loop's strict '>' / np.argmax), i.e. the smaller first-appearance key.
+// =====================================================================================================
+namespace s2 {
+
+// sums[root] += sum of x over the run: exact integers, like cv2's double accumulation of m10 (the host checks that
+// H*W*W/2 fits 32 bits)
+__global__ void __launch_bounds__(256) k_cclb_sumx(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                   uint32_t* __restrict__ sums) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int x = 32 * w + a;
+    atomicAdd(sums + base + lab_all[base + y * W + x], (uint32_t)(len * (2 * x + len - 1) / 2));
+  }
+}
+
+// score of a root as filter_cable_by_shape computes it (:41-66), or a negative value when a gate rejects it
+__device__ __forceinline__ double cable_score(const int* __restrict__ comp, size_t plane, size_t idx, const uint32_t* __restrict__ sums,
+                                              int min_area, double min_aspect, double max_offset, int roi_width) {
+  const int area = comp[idx];
+  if (area < min_area) return -1.0;
+  const int w = comp[2 * plane + idx] - comp[plane + idx] + 1, h = comp[4 * plane + idx] - comp[3 * plane + idx] + 1;
+  const double aspect = __ddiv_rn((double)max(w, h), __dadd_rn((double)min(w, h), 1e-6));
+  if (aspect < min_aspect) return -1.0;
+  const double cx = __ddiv_rn((double)sums[idx], (double)area);                     // cv2 centroid x = m10 / m00
+  const double off = __ddiv_rn(fabs(__dsub_rn(cx, __ddiv_rn((double)roi_width, 2.0))), (double)roi_width);
+  if (off > max_offset) return -1.0;
+  return __dmul_rn(__dmul_rn((double)area, aspect), __dsub_rn(1.0, off));            // area * aspect * (1.0 - center_offset)
+}
+
+// pass 0: best[b] = max score bits;  pass 1: key[b] = min first-appearance key among the roots with that score
+template <int PASS>
+__global__ void __launch_bounds__(256) k_cable_select(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                      const int* __restrict__ comp, size_t plane, const uint32_t* __restrict__ sums,
+                                                      int min_area, double min_aspect, double max_offset, int roi_width,
+                                                      unsigned long long* __restrict__ best, int* __restrict__ key) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int p = y * W + 32 * w + a;
+    if (lab_all[base + p] != p) continue;
+    const double s = cable_score(comp, plane, base + p, sums, min_area, min_aspect, max_offset, roi_width);
+    if (s < 0.0) continue;
+    const unsigned long long sb = (unsigned long long)__double_as_longlong(s) + 1ull;       // non-negative doubles order as integers; +1: 0 = none
+    if (PASS == 0) atomicMax(best + blockIdx.z, sb);
+    else if (sb == best[blockIdx.z]) atomicMin(key + blockIdx.z, comp[5 * plane + base + p]);
+  }
+}
+
+// out = 255 on the runs of the component whose key is key[b] (all zero when key[b] == INT_MAX)
+__global__ void __launch_bounds__(256) k_keep_component(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                        const int* __restrict__ comp, size_t plane, const int* __restrict__ key,
+                                                        uint8_t* __restrict__ out) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w], keep = 0;
+  const size_t base = (size_t)blockIdx.z * H * W;
+  const int k = key[blockIdx.z];
+  while (c) {
+    int a, len;
+    const uint32_t rm = first_run(c, a, len);
+    c &= ~rm;
+    if (comp[5 * plane + base + lab_all[base + y * W + 32 * w + a]] == k) keep |= rm;
+  }
+  store_bits_as_bytes(out + base + (size_t)y * W + 32 * w, keep, W - 32 * w, 255u);
+}
+
+// key[b] from best[b] = (area << 32 | INT_MAX - key) of k_diam_select
+__global__ void k_key_from_best(const unsigned long long* __restrict__ best, int* __restrict__ key, int B) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) key[b] = best[b] ? INT_MAX - (int)(uint32_t)best[b] : INT_MAX;
+}
+
+// ring = dilated & ~eroded, constrained = tape & ring as {0,1}
+__global__ void k_ring_and(const uint8_t* __restrict__ tape, const uint8_t* __restrict__ dil, const uint8_t* __restrict__ ero,
+                           uint8_t* __restrict__ out, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (tape[i] != 0 && dil[i] != 0 && ero[i] == 0) ? 1 : 0;
+}
+
+}  // namespace s2
+
+// shared tail: label `m`, statistics with keys, then the caller-specific selection fills key[b]; finally write the kept component
+static int label_with_keys(ub_ctx* ctx, const uint8_t* m, int B, int H, int W, cudaStream_t st) {
+  const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
+  const int Wd = (W + 31) / 32;
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  RUN(cclb_label(ctx, m, bits, nullptr, ctx->d_lab[0], B, H, W, ctx->d_comp, plane, st));
+  k_cclb_stats<true><<<dim3(cdiv(Wd, 32), cdiv(H, 8), B), dim3(32, 8), 0, st>>>(bits, ctx->d_lab[0], H, W, Wd, ctx->d_comp, plane);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
+int filter_cable_by_shape(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, int min_area, double min_aspect, double max_offset,
+                          int roi_width, uint8_t* out, cudaStream_t st) {
+  TimeScope ts(ctx, UB_T_CCL, st);
+  const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w, n = (size_t)B * H * W;
+  const int Wd = (W + 31) / 32;
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  int* lab = ctx->d_lab[0];
+  if ((double)H * W * W / 2.0 >= 4294967296.0) return ub_fail(ctx, UB_ERR_ARG, "ub_filter_cable_by_shape: %dx%d too large for 32-bit x sums", H, W);
+  if (!ctx->d_sums) {                                  // centroid scratch: one u32 per pixel position, allocated on first use
+    void* p = nullptr;
+    UB_CUDA(ctx, cudaMalloc(&p, sizeof(uint32_t) * plane));
+    ctx->d_sums = static_cast<uint32_t*>(p);
+  }
+  uint32_t* sums = ctx->d_sums;
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(ctx->d_tmp[2]);
+  int* key = reinterpret_cast<int*>(ctx->d_tmp[3]);
+  RUN(label_with_keys(ctx, mask, B, H, W, st));
+  UB_CUDA(ctx, cudaMemsetAsync(sums, 0, sizeof(uint32_t) * n, st));
+  UB_CUDA(ctx, cudaMemsetAsync(best, 0, sizeof(unsigned long long) * B, st));
+  UB_CUDA(ctx, cudaMemsetAsync(key, 0x7f, sizeof(int) * B, st));                     // 0x7f7f7f7f: larger than any key
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  k_cclb_sumx<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, sums);
+  k_cable_select<0><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, sums, min_area, min_aspect, max_offset, roi_width, best, key);
+  k_cable_select<1><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, sums, min_area, min_aspect, max_offset, roi_width, best, key);
+  k_keep_component<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, key, out);
+  UB_CHECK_LAUNCH_N(ctx, 4);
+  return UB_OK;
+}
+
+int constrain_tape_to_ring(ub_ctx* ctx, const uint8_t* tape, const uint8_t* cable, int B, int H, int W, int dilate_k, int erode_k,
+                           uint8_t* out, cudaStream_t st) {
+  const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w, n = (size_t)B * H * W;
+  const int Wd = (W + 31) / 32;
+  uint8_t *dil = ctx->d_tmp[0], *ero = ctx->d_tmp[1], *con = ctx->d_tmp[2];
+  RUN(morph_op(ctx, 0, dilate_k, cable, dil, nullptr, B, H, W, 1, st));
+  RUN(morph_op(ctx, 1, erode_k, cable, ero, nullptr, B, H, W, 1, st));
+  TimeScope ts(ctx, UB_T_CCL, st);
+  k_ring_and<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tape, dil, ero, con, n);
+  RUN(label_with_keys(ctx, con, B, H, W, st));
+  uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(ctx->d_tmp[0]);     // dil is dead
+  int* key = reinterpret_cast<int*>(ctx->d_tmp[1]);                                    // ero is dead
+  UB_CUDA(ctx, cudaMemsetAsync(best, 0, sizeof(unsigned long long) * B, st));
+  dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+  k_diam_select<<<g, dim3(32, 8), 0, st>>>(bits, ctx->d_lab[0], H, W, Wd, ctx->d_comp, plane, 1, best);
+  k_key_from_best<<<cdiv(B, 128), 128, 0, st>>>(best, key, B);
+  k_keep_component<<<g, dim3(32, 8), 0, st>>>(bits, ctx->d_lab[0], H, W, Wd, ctx->d_comp, plane, key, out);
+  UB_CHECK_LAUNCH_N(ctx, 4);
+  return UB_OK;
+}

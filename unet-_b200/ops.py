@@ -10,6 +10,7 @@ Same names, argument meaning and results as the reference functions:
   get_burr_mask_rulebased src/refactor/burr_detector.py:11-66 (the Laplacian-band detector of the refactored library)
   compute_diameter_metrics src/utils/geometry_enhanced.py:113-187 (Dc / Dt / delta-D of the refactored library)
   compute_thickness_profile src/utils/geometry_enhanced.py:190-228 (per-row delta-D profile)
+  filter_cable_by_shape, constrain_tape_to_ring   src/refactor/postprocess.py:12-118 (shape constraints on the masks)
   analyze_defects         src/utils/geometry_enhanced.py:236-330 (coverage, components, hole ratio, defect areas)
   visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
@@ -173,6 +174,35 @@ def compute_diameter_metrics(pred_mask, cable_cls=1, tape_cls=2, mm_per_px=0.05,
                                    delta_d_mm=dt_mm - dc_mm, valid_rows=valid_rows, cable_coverage=int(r[3]) / (h * w),
                                    tape_coverage=int(r[4]) / (h * w)))
     return res[0] if single else res
+
+
+def _cfg_get(cfg, name, default):
+    if cfg is None:
+        return default
+    return cfg.get(name, default) if isinstance(cfg, dict) else getattr(cfg, name, default)
+
+
+def filter_cable_by_shape(mask_cable, cfg=None, roi_width=512):
+    """filter_cable_by_shape(mask_cable, cfg: PostprocessConfig, roi_width) (src/refactor/postprocess.py:12-77): keep the
+    component with the best area * aspect * (1 - centre offset) among those passing the three gates -> {0, 255}.
+    cfg: the reference's PostprocessConfig, a dict, or None (defaults 1000 / 1.6 / 0.3, src/refactor/config.py:60-70)."""
+    m, was_np, single = _batched(mask_cable, 2)
+    c = _ctx(m.device, m.shape[0], tuple(m.shape[1:3]), (16, 16))
+    with torch.cuda.device(m.device):
+        out = c.filter_cable_by_shape(m, _cfg_get(cfg, "cable_min_area", 1000), _cfg_get(cfg, "cable_min_aspect", 1.6),
+                                      _cfg_get(cfg, "cable_max_center_offset", 0.3), roi_width)
+    return _unbatch(out, was_np, single)
+
+
+def constrain_tape_to_ring(mask_tape, mask_cable, cfg=None):
+    """constrain_tape_to_ring(mask_tape, mask_cable, cfg) (src/refactor/postprocess.py:80-118): tape restricted to
+    dilate(cable, 15) - erode(cable, 5), largest component -> {0, 255}.  Binary masks ({0,1} or {0,255})."""
+    t, was_np, single = _batched(mask_tape, 2)
+    cb, _, _ = _batched(mask_cable, 2)
+    c = _ctx(t.device, t.shape[0], tuple(t.shape[1:3]), (16, 16))
+    with torch.cuda.device(t.device):
+        out = c.constrain_tape_to_ring(t, cb.to(t.device), _cfg_get(cfg, "tape_ring_dilate", 15), _cfg_get(cfg, "tape_ring_erode", 5))
+    return _unbatch(out, was_np, single)
 
 
 class ThicknessProfile:
