@@ -124,15 +124,21 @@ class ClockSampler:
                 "samples": len(sm), "source": "nvidia-smi"}
 
 
-def make_frames(batch, seed):
+def make_frames(batch, seed, hw=FRAME_HW):
     import numpy as np
     import unet_b200.synth as S
-    # two thirds structured cable frames, one third speckle (non-trivial burr output)
-    n_sp = batch // 3
-    parts = [S.frames_cable(batch - n_sp, *FRAME_HW, seed=seed)]
+    # two thirds structured cable frames, one third speckle (non-trivial burr output); generated 64 at a time and tiled
+    base = min(batch, 64)
+    n_sp = base // 3
+    parts = [S.frames_cable(base - n_sp, *hw, seed=seed)]
     if n_sp:
-        parts.append(S.frames_speckle(n_sp, *FRAME_HW, seed=seed + 1000))
-    return np.concatenate(parts)
+        parts.append(S.frames_speckle(n_sp, *hw, seed=seed + 1000))
+    one = np.concatenate(parts)
+    return np.concatenate([one] * ((batch + base - 1) // base))[:batch]
+
+
+def workload_hw(workload):
+    return (512, 512) if workload == "net512" else FRAME_HW
 
 
 def ref_step(R, frame, sd, workload):
@@ -147,7 +153,7 @@ def make_workload_frames(workload, batch, seed):
     if workload == "enhanced":
         import unet_b200.synth as S
         return S.frames_cable(batch, 1080, 1920, seed=seed)        # SURVEY 8(d) `hires`
-    return make_frames(batch, seed)
+    return make_frames(batch, seed, workload_hw(workload))
 
 
 def cpu_reference_fps(frames, sd, n_frames, warm=1, workload="two_stage"):
@@ -198,7 +204,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload, args.batch), "frame": "800x448", "net": "512x512",
+            "config": {"workload": workload_name(args.workload, args.batch),
+                       "frame": f"{workload_hw(args.workload)[1]}x{workload_hw(args.workload)[0]}", "net": "512x512",
                        "batch_per_gpu": args.batch},
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -208,6 +215,8 @@ def run_reference(args):
 def workload_name(workload, batch):
     if workload == "enhanced":
         return f"enhanced_pipeline_1080p_rotate_resize_enhance_800x448_batch{batch}"
+    if workload == "net512":          # BASELINE config 5: 512x512 frames, batch 256, statistics gathered over NCCL
+        return f"two_stage_pipeline_512x512_batch{batch}"
     return f"two_stage_pipeline_800x448_batch{batch}"
 
 
@@ -227,7 +236,8 @@ def run_ours(args):
     B = args.batch
     sd = S.make_state_dict(0)
     enhanced = args.workload == "enhanced"
-    pipe = InspectionPipeline(sd, batch=B, frame_hw=FRAME_HW, net_hw=NET_HW, device=local,
+    fhw = workload_hw(args.workload)
+    pipe = InspectionPipeline(sd, batch=B, frame_hw=fhw, net_hw=NET_HW, device=local,
                               variant="enhanced" if enhanced else "standard", enhance=enhanced)
     # every rank owns a contiguous block of the global frame index space (weak scaling)
     lo, _ = shard_range(B * world, rank, world)
@@ -324,7 +334,7 @@ def run_ours(args):
         line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-                "config": {"workload": workload_name(args.workload, B), "frame": "800x448", "net": "512x512",
+                "config": {"workload": workload_name(args.workload, B), "frame": f"{fhw[1]}x{fhw[0]}", "net": "512x512",
                            "batch_per_gpu": B, "parallelism": f"frames sharded over {world} GPU(s)",
                            "l2": "activation working set ~12 GB/step per GPU >> 126 MB L2; no explicit flush"},
                 "e2e": {"value": B * world * args.steps / (e2e_ms / 1e3), "unit": "frames/s",
@@ -357,11 +367,14 @@ def main():
     ap.add_argument("--ref-frames-per-step", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-hbm-kernels", action="store_true", help="skip the per-entry-point stage-2 HBM table")
-    ap.add_argument("--workload", default="two_stage", choices=["two_stage", "enhanced"],
-                    help="two_stage: BASELINE metric config (default); enhanced: config 4 (1080p rotate+resize, enhance_image, multi-scale detector)")
+    ap.add_argument("--workload", default="two_stage", choices=["two_stage", "enhanced", "net512"],
+                    help="two_stage: BASELINE metric config (default); enhanced: config 4 (1080p rotate+resize, enhance_image, "
+                         "multi-scale detector); net512: config 5 (512x512 frames, batch 256 per GPU)")
     args = ap.parse_args()
     if args.workload == "enhanced" and args.batch == 64:
         args.batch = 16
+    if args.workload == "net512" and args.batch == 64:
+        args.batch = 256
     # The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner
     # from C), so fd 1 is pointed at stderr for the run and the JSON line goes to the saved descriptor.
     sys.stdout.flush()

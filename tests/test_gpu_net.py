@@ -129,6 +129,24 @@ def test_forward_other_class_counts(ncls):
     assert rel <= LOGIT_REL_TOL
 
 
+def test_module_other_configurations():
+    """the module contract with a 7-class head, a checkpoint saved with deep_supervision=False
+    (no ds* keys, infer_video.py:140-144) and a 256x256 input (infer_video.py:128)."""
+    from unet_b200 import NestedUNet
+    sd7 = S.make_state_dict(seed=5, num_classes=7)
+    nods = {k: v for k, v in sd7.items() if not k.startswith("ds")}
+    m = NestedUNet(num_classes=7, deep_supervision=False).to("cuda").eval()
+    assert set(m.state_dict().keys()) == set(nods.keys())
+    m.load_state_dict(nods, strict=True)
+    x = torch.rand(1, 3, 256, 256, generator=torch.Generator().manual_seed(7))
+    with torch.no_grad():
+        got = m(x.cuda()).cpu()
+    want = R.unet_forward(x, sd7)
+    assert got.shape == (1, 7, 256, 256)
+    assert float((got - want).abs().max() / want.abs().max()) <= LOGIT_REL_TOL
+    assert float((got.argmax(1) == want.argmax(1)).float().mean()) >= 0.995
+
+
 def test_forward_golden_reference_outputs(ctx, sd, golden_net):
     """Against logits produced by the REAL reference module (tests/golden/net.npz)."""
     for tag in ("a", "b"):
