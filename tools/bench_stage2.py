@@ -28,6 +28,7 @@ def measure(B=512, reps=10, log=None):
     mask_t = torch.from_numpy(np.stack([S.mask_blobs(H, W, seed=3, fill=0.02)] * B)).cuda()
     mask_b = torch.from_numpy(np.stack([S.mask_blobs(H, W, seed=4, fill=0.004)] * B)).cuda()
     preds = torch.from_numpy(np.stack([S.pred_classes(H, W, seed=i) for i in range(8)] * (B // 8))).cuda()
+    cand = ctx.blur_canny(gray, 50, 150)            # a realistic binary plane for the labelling row (Canny edges)
     roi = (218, 0, 421, 448)
     pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
     peak = json.load(open(pk))["hbm_gbs"] if os.path.exists(pk) else 6549.8
@@ -50,6 +51,7 @@ def measure(B=512, reps=10, log=None):
         ("ub_gaussian5: k_edge_fused<2>", lambda: ctx.gaussian5(gray), 2 * P),
         ("ub_blur_canny: k_edge_fused<1> + union-find hysteresis", lambda: ctx.blur_canny(gray, 50, 150), 2 * P),
         ("ub_burr: edges + band + morphology + CCL + filter", lambda: ctx.burr(gray, mask), 3 * P),
+        ("ub_ccl: connectedComponentsWithStats, labels in OpenCV order + stats", lambda: ctx.ccl(cand), 5 * P),
         ("ub_diameter_metrics: 2 x (CCL + largest component + row extents) + smoothing + medians", lambda: ctx.diameter_metrics(preds), P),
         ("ub_analyze_defects: 3 x CCL + CLOSE 5x5 + class histogram", lambda: ctx.analyze_defects(preds), P),
         ("ub_morph close 3x3 (k_morph_words)", lambda: ctx.morph("close", 3, mask), 2 * P),

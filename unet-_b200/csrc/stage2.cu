@@ -419,6 +419,105 @@ __global__ void k_relabel(const int* __restrict__ lab_all, int H, int W, const i
     s[0] = a[1]; s[1] = a[3]; s[2] = a[2] - a[1] + 1; s[3] = a[4] - a[3] + 1; s[4] = a[0];
   }
 }
+// ---- run-based export (ub_ccl's path): the first-appearance keys of the roots as a BIT plane, ranks by popcount ----
+// markbits[b][key >> 5] |= 1 << (key & 31) for every root; background accumulators from the zero bits of every word
+__global__ void __launch_bounds__(256) k_cclb_mark(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                   const int* __restrict__ comp, size_t plane, uint32_t* __restrict__ markbits, int KW,
+                                                   int* __restrict__ bgacc) {
+  __shared__ int s_bg[5];                                       // background count / min x / max x / min y / max y of this block
+  const int t = threadIdx.y * 32 + threadIdx.x;
+  if (t < 5) s_bg[t] = (t == 1 || t == 3) ? INT_MAX : (t == 0 ? 0 : -1);
+  __syncthreads();
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w < Wd && y < H) {
+    const uint32_t word = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+    const size_t base = (size_t)blockIdx.z * H * W;
+    uint32_t c = word;
+    while (c) {
+      int a, len;
+      c &= ~first_run(c, a, len);
+      const int p = y * W + 32 * w + a;
+      if (lab_all[base + p] == p) {
+        const int key = comp[5 * plane + base + p];
+        atomicOr(markbits + (size_t)blockIdx.z * KW + (key >> 5), 1u << (key & 31));
+      }
+    }
+    const int rem = W - 32 * w;
+    const uint32_t bg = ~word & (rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u));
+    if (bg) {
+      atomicAdd(&s_bg[0], __popc(bg));
+      atomicMin(&s_bg[1], 32 * w + __ffs(bg) - 1); atomicMax(&s_bg[2], 32 * w + 31 - __clz(bg));
+      atomicMin(&s_bg[3], y); atomicMax(&s_bg[4], y);
+    }
+  }
+  __syncthreads();
+  if (t == 0 && s_bg[0]) {
+    int* a = bgacc + blockIdx.z * 8;
+    atomicAdd(a, s_bg[0]);
+    atomicMin(a + 1, s_bg[1]); atomicMax(a + 2, s_bg[2]);
+    atomicMin(a + 3, s_bg[3]); atomicMax(a + 4, s_bg[4]);
+  }
+}
+// wordprefix[b][i] = number of marked keys in words [0, i); one block per frame
+__global__ void __launch_bounds__(1024) k_scan_bits(const uint32_t* __restrict__ markbits, int KW, int* __restrict__ wordprefix,
+                                                    int* __restrict__ n_labels) {
+  __shared__ int s_w[32];
+  const uint32_t* m = markbits + (size_t)blockIdx.x * KW;
+  int* wp = wordprefix + (size_t)blockIdx.x * KW;
+  const int per = (KW + 1023) / 1024, i0 = threadIdx.x * per, i1 = min(i0 + per, KW);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int sum = 0;
+  for (int i = i0; i < i1; ++i) sum += __popc(m[i]);
+  int v = sum;
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+  if (lane == 31) s_w[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    int t = s_w[lane];
+    for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t += u; }
+    s_w[lane] = t;
+  }
+  __syncthreads();
+  int run = v - sum + (warp ? s_w[warp - 1] : 0);               // exclusive prefix of this thread's chunk
+  for (int i = i0; i < i1; ++i) { wp[i] = run; run += __popc(m[i]); }
+  if (threadIdx.x == 1023) n_labels[blockIdx.x] = s_w[31] + 1;
+}
+// labels (OpenCV numbering) for the 32 pixels of every word + the stats row of every root
+__global__ void __launch_bounds__(256) k_cclb_relabel(const uint32_t* __restrict__ bits, const int* __restrict__ lab_all, int H, int W, int Wd,
+                                                      const int* __restrict__ comp, size_t plane, const uint32_t* __restrict__ markbits,
+                                                      const int* __restrict__ wordprefix, int KW, int* __restrict__ labels,
+                                                      int* __restrict__ stats, int max_labels, const int* __restrict__ bgacc) {
+  const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (w >= Wd || y >= H) return;
+  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const size_t base = (size_t)blockIdx.z * H * W;
+  int* out = labels ? labels + base + (size_t)y * W + 32 * w : nullptr;
+  const int nvalid = min(32, W - 32 * w);
+  int pos = 0;
+  while (c) {
+    int a, len;
+    c &= ~first_run(c, a, len);
+    const int p = y * W + 32 * w + a, r = lab_all[base + p];
+    const int key = comp[5 * plane + base + r];
+    const int lbl = wordprefix[(size_t)blockIdx.z * KW + (key >> 5)] +
+                    __popc(markbits[(size_t)blockIdx.z * KW + (key >> 5)] & ((1u << (key & 31)) - 1u)) + 1;
+    if (out) {
+      for (; pos < a; ++pos) out[pos] = 0;
+      for (; pos < a + len; ++pos) out[pos] = lbl;
+    }
+    if (r == p && stats && lbl < max_labels) {
+      const int* k = comp + base + r;
+      int* s = stats + ((size_t)blockIdx.z * max_labels + lbl) * 5;
+      s[0] = k[plane]; s[1] = k[3 * plane]; s[2] = k[2 * plane] - k[plane] + 1; s[3] = k[4 * plane] - k[3 * plane] + 1; s[4] = k[0];
+    }
+  }
+  if (out) for (; pos < nvalid; ++pos) out[pos] = 0;
+  if (w == 0 && y == 0 && stats && max_labels > 0) {
+    const int* a = bgacc + blockIdx.z * 8;
+    int* s = stats + (size_t)blockIdx.z * max_labels * 5;
+    s[0] = a[1]; s[1] = a[3]; s[2] = a[2] - a[1] + 1; s[3] = a[4] - a[3] + 1; s[4] = a[0];
+  }
+}
 __global__ void k_bg_init(int* bgacc, int B) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B * 8) { int k = i & 7; bgacc[i] = (k == 1 || k == 3) ? INT_MAX : (k == 2 || k == 4) ? -1 : 0; }
@@ -618,16 +717,37 @@ int enh_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int mode, i
   return UB_OK;
 }
 
-// labels / stats in OpenCV numbering (ub_ccl)
+// labels / stats in OpenCV numbering (ub_ccl).  Run-based path: labelling on packed rows, the roots' first-appearance keys as a
+// bit plane, ranks by popcount (a 32x smaller scan than one int per key), labels written 32 pixels per thread.
+// UB_CCL_PACKED=0 keeps the per-pixel kernels.
 int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels, int* stats, int max_labels, int* n_labels, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_CCL, st);
   const size_t plane = (size_t)ctx->max_batch * ctx->frame_h * ctx->frame_w;
   int* lab = ctx->d_lab[0];
-  int* mark = ctx->d_lab[1];
+  int* bg = ctx->d_counts;
   const int K = ((H + 1) / 2) * ((W + 1) / 2) * 4;
+  static const int packed_env = getenv("UB_CCL_PACKED") ? atoi(getenv("UB_CCL_PACKED")) : 1;
+  if (packed_env) {
+    const int Wd = (W + 31) / 32, KW = (K + 31) / 32;
+    const size_t nwords = (size_t)B * H * Wd;
+    uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+    uint32_t* markbits = bits + nwords;                                  // [B][KW]
+    int* wordprefix = reinterpret_cast<int*>(markbits + (size_t)B * KW); // [B][KW]   (nwords + 2*B*KW <= ints of d_lab[1])
+    dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+    RUN(cclb_label(ctx, src, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
+    k_cclb_stats<true><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_bg_init<<<cdiv(B * 8, 256), 256, 0, st>>>(bg, B);
+    UB_CUDA(ctx, cudaMemsetAsync(markbits, 0, sizeof(uint32_t) * (size_t)B * KW, st));
+    k_cclb_mark<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, markbits, KW, bg);
+    k_scan_bits<<<B, 1024, 0, st>>>(markbits, KW, wordprefix, n_labels ? n_labels : bg + (size_t)ctx->max_batch * 8 + ctx->max_batch);
+    if (stats) UB_CUDA(ctx, cudaMemsetAsync(stats, 0, sizeof(int) * (size_t)B * max_labels * 5, st));
+    k_cclb_relabel<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, markbits, wordprefix, KW, labels, stats, max_labels, bg);
+    UB_CHECK_LAUNCH_N(ctx, 5);
+    return UB_OK;
+  }
+  int* mark = ctx->d_lab[1];
   const int segs = (W + 31) / 32;
   dim3 gseg(cdiv(H * segs * 32, 256), 1, B), gpix(cdiv(W, 256), H, B);
-  int* bg = ctx->d_counts;
   RUN(ccl_label(ctx, src, lab, B, H, W, ctx->d_comp, plane, st));
   k_bg_init<<<cdiv(B * 8, 256), 256, 0, st>>>(bg, B);
   k_ccl_stats<<<gseg, 256, 0, st>>>(lab, H, W, ctx->d_comp, plane, bg);
