@@ -307,3 +307,24 @@ def test_postprocess_filters_golden_and_oracle(golden_geometry):
         same("tape_ring", ring[i], R.constrain_tape_to_ring(tape[i], cable[i]))
     z = np.zeros((64, 96), np.uint8)
     assert U.filter_cable_by_shape(z).max() == 0 and U.constrain_tape_to_ring(z, z).max() == 0
+
+
+def test_error_behaviour_through_the_c_abi(ctx):
+    """Bad arguments come back as a negative code + message (UbError), never as a crash, and leave the context usable."""
+    from unet_b200 import _lib
+    g = dev(S.frames_noise(1, 448, 800, seed=1)[..., 0].copy())
+    m = dev(S.mask_cable_synth(448, 800)[None])
+    with pytest.raises(_lib.UbError, match="exceed the context"):
+        ctx.gaussian5(dev(np.zeros((5, 448, 800), np.uint8)))              # batch 5 > max_batch 4
+    with pytest.raises(_lib.UbError, match="exceed the context"):
+        ctx.canny(dev(np.zeros((1, 900, 800), np.uint8)), 50, 150)         # frame larger than the context's
+    with pytest.raises(_lib.UbError, match="ellipse size"):
+        ctx.morph("dilate", 27, m)
+    with pytest.raises(_lib.UbError, match="variant"):
+        ctx.burr(g, m, variant=7, params=_lib.standard_params())
+    with pytest.raises(_lib.UbError, match="smaller than 16x16"):
+        ctx.diameter_metrics(dev(np.zeros((1, 8, 8), np.uint8)))
+    with pytest.raises(_lib.UbError, match="roi_width"):
+        ctx.filter_cable_by_shape(m, 10, 1.0, 0.5, 0)
+    out, px = ctx.burr(g, m)                                                # still works afterwards
+    assert out.shape == g.shape and int(px[0]) == int(out.sum())
