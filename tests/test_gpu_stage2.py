@@ -57,6 +57,27 @@ def test_preprocess_golden(ctx, golden_stage2, golden_frames):
         same(tag + " pre", x[0], golden_stage2[f"{tag}_pre_u8"].astype(np.float32) / 255.0)
 
 
+@pytest.mark.parametrize("hw,net", [((301, 397), (256, 256)), ((1080, 1920), (512, 512)), ((97, 131), (512, 512)), ((448, 800), (512, 512))])
+def test_preprocess_sizes_and_alignment(hw, net):
+    """preprocess_image at sizes whose rows are not 16-byte multiples (shared-memory staging starts mid-vector), a
+    downscale by more than 2 (no row shared between vertical taps), a strong upscale, and a frame pointer 1 byte off
+    alignment (first / last staged vector falls outside the buffer)."""
+    from unet_b200 import _lib
+    H, W = hw
+    c = _lib.Context(0, 3, hw, net)
+    try:
+        fr = S.frames_noise(3, H, W, seed=H + W)
+        x, _ = c.preprocess(dev(fr), want_gray=False)
+        for i in range(3):
+            same(f"x[{i}]", x[i], R.preprocess(fr[i], size=(net[1], net[0])).numpy())
+        raw = torch.zeros(fr.size + 1, dtype=torch.uint8, device="cuda")
+        raw[1:] = dev(fr).reshape(-1)
+        x, _ = c.preprocess(raw[1:].view(3, H, W, 3), want_gray=False)
+        same("x unaligned", x[2], R.preprocess(fr[2], size=(net[1], net[0])).numpy())
+    finally:
+        c.close()
+
+
 def test_normalize_frames(ctx, golden_stage2):
     big = S.frames_noise(2, 1080, 1920, seed=3)
     out = ctx.normalize_frames(dev(big), (800, 448), rotate=False)

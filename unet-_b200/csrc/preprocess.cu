@@ -85,48 +85,102 @@ struct SrcRot {
 };
 
 // preprocess_image (infer_two_stage_burr.py:122-127): BGR->RGB, resize, /255.
-// A block takes PRE_ROWS padded rows of one image (blockIdx.x = row group, the last group also covers the tile padding
-// behind the plane) and every thread walks them with stride 256, carrying (row, column) incrementally: no division per
-// position, and u/255 -> fp16 is a 256-entry shared-memory table built once per block (the IEEE division is exact either
-// way).  ncu before: 204 instructions per position, issue slots 71 % busy (profiles/r01_glue.md).
-constexpr int PRE_ROWS = 4;
-__global__ void __launch_bounds__(256) k_preprocess(const uint8_t* __restrict__ frames, int H, int W, int nh, int nw,
+// A block takes PRE_ROWS padded rows of one image (blockIdx.x = row group; the last group also zeroes the tile padding
+// behind the plane).  u/255 -> fp16 is a 256-entry shared-memory table built once per block (the IEEE division is exact
+// either way).  STAGED: the source rows the group's vertical taps touch are one contiguous byte range of the frame; it
+// is copied to shared memory first with aligned 16-byte loads, all in flight together, so the tap reads are
+// shared-memory bytes instead of dependent global byte loads.  !STAGED reads the taps from global memory (frames too
+// large for the shared-memory window, or UB_PRE_STAGED=0).  The first version (one position per thread, flat index)
+// was issue- and latency-bound: 204 instructions per position, DRAM at 25 % (profiles/r01_glue.md).
+constexpr int PRE_ROWS = 8, PRE_T = 288;              // 2 * 288 covers the 514-position pitch of a 512-wide plane
+constexpr int PRE_SMEM_MAX = 160 * 1024;
+template <bool STAGED>
+__global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict__ frames, int B, int H, int W, int nh, int nw,
                                                     const int4* __restrict__ ty, const int4* __restrict__ tx,
-                                                    act_t* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L) {
+                                                    act_t* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L,
+                                                    int stage_bytes) {
+  extern __shared__ __align__(16) uint8_t s_src[];
   __shared__ act_t s_lut[256];
-  s_lut[threadIdx.x] = f2a(__fdiv_rn((float)threadIdx.x, 255.0f));
-  __syncthreads();
+  if (threadIdx.x < 256) s_lut[threadIdx.x] = f2a(__fdiv_rn((float)threadIdx.x, 255.0f));
   const int b = blockIdx.y;
-  const int q0 = blockIdx.x * PRE_ROWS * L.pitch;
-  const int q1 = min(q0 + PRE_ROWS * L.pitch, L.ntiles * 128);          // the last group runs on into the tile padding
-  const int qend = (blockIdx.x + 1 == gridDim.x) ? L.ntiles * 128 : q1;
-  const uint8_t* img = frames + (size_t)b * H * W * 3;
-  act_t* dstp = x_pp ? x_pp + (((size_t)b * 2) * L.Ppl + L.G) * 8 : nullptr;
-  int yy = blockIdx.x * PRE_ROWS, xx = threadIdx.x;                      // pitch >= 256 is not required: wrap below
-  while (xx >= L.pitch) { xx -= L.pitch; ++yy; }
-  for (int q = q0 + threadIdx.x; q < qend; q += 256) {
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (yy >= 1 && yy <= nh && xx >= 1 && xx <= nw) {
-      const int4 cy = ty[yy - 1], cx = tx[xx - 1];
-      const uint8_t* r0 = img + (cy.x * W) * 3;
-      const uint8_t* r1 = img + (cy.y * W) * 3;
-      const int o0 = cx.x * 3, o1 = cx.y * 3;
-      uint32_t h[3];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {                              // RGB order: channel c reads B,G,R[2-c]
-        const int h0 = r0[o0 + 2 - c] * cx.z + r0[o1 + 2 - c] * cx.w;
-        const int h1 = r1[o0 + 2 - c] * cx.z + r1[o1 + 2 - c] * cx.w;
-        const int u = (((cy.z * (h0 >> 4)) >> 16) + ((cy.w * (h1 >> 4)) >> 16) + 2) >> 2;   // cv2's 11-bit fixed point
-        h[c] = (uint32_t)*reinterpret_cast<const uint16_t*>(&s_lut[u]);
-        if (x_nchw) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = __fdiv_rn((float)u, 255.0f);
+  const int W3 = W * 3;
+  const uint8_t* img = frames + (size_t)b * H * W3;
+  bool staged = false;
+  int sbase = 0;                                                 // tap (row r, byte o) is s_src[sbase + r * W3 + o]
+  if (STAGED) {
+    const int ya = max((int)blockIdx.x * PRE_ROWS, 1), yb = min((int)blockIdx.x * PRE_ROWS + PRE_ROWS - 1, nh);   // interior rows
+    if (ya <= yb) {
+      const int r_lo = ty[ya - 1].x, r_hi = ty[yb - 1].y;        // the tables are monotone, .x <= .y
+      const uint8_t* P = img + (size_t)r_lo * W3;
+      const int n = (r_hi - r_lo + 1) * W3;
+      const int a = (int)(reinterpret_cast<uintptr_t>(P) & 15);
+      const uint8_t* lo = frames;
+      const uint8_t* hi = frames + (size_t)B * H * W3;
+      if (a + n <= stage_bytes) {                                // always, by the host's sizing; else the taps stay in global memory
+        for (int i = threadIdx.x; i * 16 < a + n; i += PRE_T) {
+          const uint8_t* g = P - a + i * 16;                     // 16-byte aligned address
+          if (g >= lo && g + 16 <= hi) {
+            *reinterpret_cast<uint4*>(s_src + i * 16) = *reinterpret_cast<const uint4*>(g);
+          } else {                                               // first / last vector of the buffer: stay inside it
+            for (int k = 0; k < 16; ++k) s_src[i * 16 + k] = (g + k >= lo && g + k < hi) ? g[k] : (uint8_t)0;
+          }
+        }
+        staged = true;
+        sbase = a - r_lo * W3;
       }
-      v.x = h[0] | (h[1] << 16);
-      v.y = h[2];                                                // channels 3..7 are zero (+0.0 in either 16-bit format)
     }
-    if (dstp) *reinterpret_cast<uint4*>(dstp + (size_t)q * 8) = v;
-    xx += 256;
-    while (xx >= L.pitch) { xx -= L.pitch; ++yy; }
   }
+  __syncthreads();
+  // A thread owns a column of the group's rows: column coefficients loaded once, and the horizontal pass of a source
+  // row stays in registers for the next output row whenever cv2's two vertical taps share it (always, unless the
+  // resize shrinks by more than 2).  ty[] is the same for the whole block, so every branch on rows is uniform.
+  act_t* dstp = x_pp ? x_pp + (((size_t)b * 2) * L.Ppl + L.G) * 8 : nullptr;
+  const int y0 = blockIdx.x * PRE_ROWS, y1 = min(y0 + PRE_ROWS, nh + 2);
+  auto hpass = [&](int r, int o0, int o1, int wz, int ww, int (&h)[3]) {
+    if (STAGED && staged) {
+      const int base = sbase + r * W3;                           // 32-bit shared-memory index
+#pragma unroll
+      for (int c = 0; c < 3; ++c) h[c] = (s_src[base + o0 + c] * wz + s_src[base + o1 + c] * ww) >> 4;
+    } else {
+      const uint8_t* row = img + (size_t)r * W3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) h[c] = (row[o0 + c] * wz + row[o1 + c] * ww) >> 4;
+    }
+  };
+  for (int xx = threadIdx.x; xx < L.pitch; xx += PRE_T) {
+    const bool colin = xx >= 1 && xx <= nw;
+    int4 cx = make_int4(0, 0, 0, 0);
+    if (colin) cx = tx[xx - 1];
+    const int o0 = cx.x * 3, o1 = cx.y * 3;
+    int ra = -1, rb = -1, Ha[3] = {0, 0, 0}, Hb[3] = {0, 0, 0};    // source rows held and their horizontal passes (>> 4)
+    for (int yy = y0; yy < y1; ++yy) {
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (colin && yy >= 1 && yy <= nh) {
+        const int4 cy = ty[yy - 1];
+        int n0[3], n1[3];
+        if (cy.x == ra) { n0[0] = Ha[0]; n0[1] = Ha[1]; n0[2] = Ha[2]; }
+        else if (cy.x == rb) { n0[0] = Hb[0]; n0[1] = Hb[1]; n0[2] = Hb[2]; }
+        else hpass(cy.x, o0, o1, cx.z, cx.w, n0);
+        if (cy.y == rb) { n1[0] = Hb[0]; n1[1] = Hb[1]; n1[2] = Hb[2]; }
+        else if (cy.y == cy.x) { n1[0] = n0[0]; n1[1] = n0[1]; n1[2] = n0[2]; }
+        else hpass(cy.y, o0, o1, cx.z, cx.w, n1);
+        ra = cy.x; rb = cy.y;
+        uint32_t h[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {                            // RGB order: channel c reads B,G,R[2-c]
+          Ha[c] = n0[c]; Hb[c] = n1[c];
+          const int u = (((cy.z * n0[2 - c]) >> 16) + ((cy.w * n1[2 - c]) >> 16) + 2) >> 2;   // cv2's 11-bit fixed point
+          h[c] = (uint32_t)*reinterpret_cast<const uint16_t*>(&s_lut[u]);
+          if (x_nchw) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = __fdiv_rn((float)u, 255.0f);
+        }
+        v.x = h[0] | (h[1] << 16);
+        v.y = h[2];                                              // channels 3..7 are zero (+0.0 in either 16-bit format)
+      }
+      if (dstp) *reinterpret_cast<uint4*>(dstp + (size_t)(yy * L.pitch + xx) * 8) = v;
+    }
+  }
+  if (dstp && blockIdx.x + 1 == gridDim.x)                        // the tile padding behind the plane
+    for (int q = L.npos + threadIdx.x; q < L.ntiles * 128; q += PRE_T) *reinterpret_cast<uint4*>(dstp + (size_t)q * 8) = make_uint4(0, 0, 0, 0);
 }
 
 // cv2.cvtColor(BGR2GRAY) (infer_two_stage_burr.py:317): (3735 B + 19235 G + 9798 R + 2^14) >> 15
@@ -298,7 +352,15 @@ int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, i
     PPLayout L = pp_layout(nh, nw);
     TimeScope ts(ctx, UB_T_PREPOST, st);
     dim3 grid(cdiv(nh + 2, PRE_ROWS), B);
-    k_preprocess<<<grid, 256, 0, st>>>(frames, H, W, nh, nw, ty, tx, x_pp, x_nchw, L);
+    // source rows under PRE_ROWS output rows: the taps of the first and last row are (PRE_ROWS-1)*H/nh apart, + the second tap
+    const size_t stage = ((size_t)((PRE_ROWS - 1) * (size_t)H / nh + 3) * W * 3 + 32 + 15) & ~(size_t)15;
+    static const int staged_env = getenv("UB_PRE_STAGED") ? atoi(getenv("UB_PRE_STAGED")) : 1;
+    if (staged_env && stage <= (size_t)PRE_SMEM_MAX) {
+      if (stage > 48 * 1024) cudaFuncSetAttribute(k_preprocess<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_MAX);
+      k_preprocess<true><<<grid, PRE_T, stage, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, (int)stage);
+    } else {
+      k_preprocess<false><<<grid, PRE_T, 0, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, 0);
+    }
     UB_CHECK_LAUNCH(ctx);
   }
   if (gray) {
