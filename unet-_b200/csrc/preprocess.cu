@@ -93,6 +93,7 @@ struct SrcRot {
 // large for the shared-memory window, or UB_PRE_STAGED=0).  The first version (one position per thread, flat index)
 // was issue- and latency-bound: 204 instructions per position, DRAM at 25 % (profiles/r01_glue.md).
 constexpr int PRE_ROWS = 8, PRE_T = 288;              // 2 * 288 covers the 514-position pitch of a 512-wide plane
+static_assert(PRE_T >= 256 + PRE_ROWS, "threads 256.. load the row coefficients");
 constexpr int PRE_SMEM_MAX = 160 * 1024;
 template <bool STAGED>
 __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict__ frames, int B, int H, int W, int nh, int nw,
@@ -101,7 +102,12 @@ __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict_
                                                     int stage_bytes) {
   extern __shared__ __align__(16) uint8_t s_src[];
   __shared__ act_t s_lut[256];
+  __shared__ int4 s_ty[PRE_ROWS];                                // the group's row coefficients (read once per position below)
   if (threadIdx.x < 256) s_lut[threadIdx.x] = f2a(__fdiv_rn((float)threadIdx.x, 255.0f));
+  if (threadIdx.x >= 256 && threadIdx.x < 256 + PRE_ROWS) {
+    const int yy = blockIdx.x * PRE_ROWS + threadIdx.x - 256;
+    if (yy >= 1 && yy <= nh) s_ty[threadIdx.x - 256] = ty[yy - 1];
+  }
   const int b = blockIdx.y;
   const int W3 = W * 3;
   const uint8_t* img = frames + (size_t)b * H * W3;
@@ -156,7 +162,7 @@ __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict_
     for (int yy = y0; yy < y1; ++yy) {
       uint4 v = make_uint4(0, 0, 0, 0);
       if (colin && yy >= 1 && yy <= nh) {
-        const int4 cy = ty[yy - 1];
+        const int4 cy = s_ty[yy - y0];
         int n0[3], n1[3];
         if (cy.x == ra) { n0[0] = Ha[0]; n0[1] = Ha[1]; n0[2] = Ha[2]; }
         else if (cy.x == rb) { n0[0] = Hb[0]; n0[1] = Hb[1]; n0[2] = Hb[2]; }
