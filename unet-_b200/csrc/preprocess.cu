@@ -95,7 +95,7 @@ struct SrcRot {
 constexpr int PRE_ROWS = 8, PRE_T = 288;              // 2 * 288 covers the 514-position pitch of a 512-wide plane
 static_assert(PRE_T >= 256 + PRE_ROWS, "threads 256.. load the row coefficients");
 constexpr int PRE_SMEM_MAX = 160 * 1024;
-template <bool STAGED>
+template <bool STAGED, bool NCHW>
 __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict__ frames, int B, int H, int W, int nh, int nw,
                                                     const int4* __restrict__ ty, const int4* __restrict__ tx,
                                                     act_t* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L,
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict_
           Ha[c] = n0[c]; Hb[c] = n1[c];
           const int u = (((cy.z * n0[2 - c]) >> 16) + ((cy.w * n1[2 - c]) >> 16) + 2) >> 2;   // cv2's 11-bit fixed point
           h[c] = (uint32_t)*reinterpret_cast<const uint16_t*>(&s_lut[u]);
-          if (x_nchw) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = __fdiv_rn((float)u, 255.0f);
+          if (NCHW) x_nchw[(((size_t)b * 3 + c) * nh + (yy - 1)) * nw + (xx - 1)] = __fdiv_rn((float)u, 255.0f);
         }
         v.x = h[0] | (h[1] << 16);
         v.y = h[2];                                              // channels 3..7 are zero (+0.0 in either 16-bit format)
@@ -361,11 +361,14 @@ int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, i
     // source rows under PRE_ROWS output rows: the taps of the first and last row are (PRE_ROWS-1)*H/nh apart, + the second tap
     const size_t stage = ((size_t)((PRE_ROWS - 1) * (size_t)H / nh + 3) * W * 3 + 32 + 15) & ~(size_t)15;
     static const int staged_env = getenv("UB_PRE_STAGED") ? atoi(getenv("UB_PRE_STAGED")) : 1;
+    auto launch = [&](auto kern, size_t smem) {
+      if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_MAX);
+      kern<<<grid, PRE_T, smem, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, (int)smem);
+    };
     if (staged_env && stage <= (size_t)PRE_SMEM_MAX) {
-      if (stage > 48 * 1024) cudaFuncSetAttribute(k_preprocess<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_MAX);
-      k_preprocess<true><<<grid, PRE_T, stage, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, (int)stage);
+      if (x_nchw) launch(k_preprocess<true, true>, stage); else launch(k_preprocess<true, false>, stage);
     } else {
-      k_preprocess<false><<<grid, PRE_T, 0, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, 0);
+      if (x_nchw) launch(k_preprocess<false, true>, 0); else launch(k_preprocess<false, false>, 0);
     }
     UB_CHECK_LAUNCH(ctx);
   }
