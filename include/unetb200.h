@@ -218,6 +218,12 @@ int ub_pipeline_wait(ub_ctx* ctx, int slot);
  * x0 [B,cin0,H,W] (layer 0: 3 channels), x1 [B,cin1,H,W] or NULL -> out [B,cout,H,W]. */
 int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0_dev, const float* x1_dev, int B, int H, int W,
                   float* out_dev, void* stream);
+/* conv1 of a decoder block (layer 10, 12, 14 or 16) on cat([x0, Upsample(x2, bilinear, align_corners)(x1_low)])
+ * (src/models/unetpp.py:76,111-116): x0 [B,cin0,H,W], x1_low [B,cin1,H/2,W/2] -> out [B,cout,H,W].  fused != 0
+ * interpolates inside the conv kernel (layers 14 and 16; UB_ERR_ARG for the others), fused == 0 materialises the
+ * upsampled tensor first; the two results are bit-identical. */
+int ub_debug_conv_up(ub_ctx* ctx, int layer, const float* x0_dev, const float* x1_low_dev, int B, int H, int W,
+                     int fused, float* out_dev, void* stream);
 /* Copies activation buffer `index` of the last forward (order: x_in,t0,x0_0,p0,t1,x1_0,p1,t2,
  * x2_0,p2,t3,x3_0,p3,t4,x4_0,up4,x3_1,up3,x2_2,up2,x1_3,up1) to NCHW fp32 [B,C,H,W]. */
 int ub_debug_activation(ub_ctx* ctx, int index, int B, int C, int H, int W, float* out_dev, void* stream);

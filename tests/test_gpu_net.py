@@ -112,6 +112,31 @@ def test_fused_pool_equals_maxpool_of_layer_output(ctx, hw):
         assert torch.equal(p, F.max_pool2d(a, 2)), f"level {lvl}"
 
 
+@pytest.mark.parametrize("li,hw", [(16, (128, 160)), (16, (72, 92)), (16, (36, 60)), (16, (16, 16)),
+                                   (14, (64, 80)), (14, (36, 44)), (14, (8, 20))])
+def test_fused_upsample_equals_materialised(ctx, sd, li, hw):
+    """cat([skip, Upsample(x2, bilinear, align_corners=True)(below)]) -> conv1 (src/models/unetpp.py:76,111-116): the
+    kernel that interpolates `below` on the way into shared memory must give the bits of the path that materialises
+    the upsampled tensor first (same fp16 rounding of the interpolated value), for every tile shape (4/2/1 M-tiles per
+    box, ragged last 30-column tile, image smaller than one box), and both must match torch within the layer tolerance."""
+    blk, idx, c0, c1, cout = LAYERS[li]
+    h, w = hw
+    g = torch.Generator().manual_seed(100 + li + h)
+    x0 = torch.rand(2, c0, h, w, generator=g) * 2 - 0.5
+    xl = torch.rand(2, c1, h // 2, w // 2, generator=g) * 2 - 0.5
+    fused = ctx.debug_conv_up(li, x0.cuda(), xl.cuda(), cout, True).cpu()
+    plain = ctx.debug_conv_up(li, x0.cuda(), xl.cuda(), cout, False).cpu()
+    torch.cuda.synchronize()
+    assert float(plain.abs().max()) > 0
+    assert torch.equal(fused, plain), f"{int((fused != plain).sum())} of {fused.numel()} outputs differ, max {float((fused - plain).abs().max())}"
+    wf, bfold = folded(sd, blk, idx)
+    up = F.interpolate(bf(xl).double(), scale_factor=2, mode="bilinear", align_corners=True)
+    want = F.relu(F.conv2d(torch.cat([bf(x0).double(), up], 1), wf.double(), bfold.double(), padding=1)).float()
+    err = (fused - want).abs()
+    # the interpolated operand is rounded to fp16 after each of the two blends: ~2^-10 relative per input, averaged over K
+    assert float(err.max()) <= 2.0 ** -8 * float(want.abs().max()) + 2e-3, f"max err {float(err.max())} vs max |ref| {float(want.abs().max())}"
+
+
 @pytest.mark.parametrize("ncls", [2, 5, 8])
 def test_forward_other_class_counts(ncls):
     """The fused 1x1 head has a 3-class fast path; other class counts take the generic one."""

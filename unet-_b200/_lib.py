@@ -79,6 +79,7 @@ SIGNATURES = {
     "ub_pipeline_submit": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _I]),
     "ub_pipeline_wait": (_I, [_P, _I]),
     "ub_debug_conv": (_I, [_P, _I, _P, _P, _I, _I, _I, _P, _P]),
+    "ub_debug_conv_up": (_I, [_P, _I, _P, _P, _I, _I, _I, _I, _P, _P]),
     "ub_debug_activation": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "ub_timing_enable": (_I, [_P, _I]),
     "ub_timing_read": (_I, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int64), _I]),
@@ -396,6 +397,13 @@ class Context:
         self._check(lib().ub_debug_conv(self._h, layer, self._dev(x0, torch.float32),
                                         self._dev(x1, torch.float32) if x1 is not None else None, b, h, w,
                                         out.data_ptr(), self.stream))
+        return out
+
+    def debug_conv_up(self, layer, x0, x1_low, cout, fused):
+        b, _, h, w = x0.shape
+        out = torch.empty((b, cout, h, w), dtype=torch.float32, device=x0.device)
+        self._check(lib().ub_debug_conv_up(self._h, layer, self._dev(x0, torch.float32), self._dev(x1_low, torch.float32),
+                                           b, h, w, int(fused), out.data_ptr(), self.stream))
         return out
 
     def debug_activation(self, index, b, c, h, w):

@@ -568,6 +568,35 @@ int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0, const float* x1, int 
   return pp_to_nchw(ctx, ctx->act[outb[lvl]], B, d.cout, H, W, out, st);
 }
 
+// conv1 of a decoder block from the half-resolution `below` tensor: fused = 1 runs the layer's fused-upsample kernel
+// (error if it has none), fused = 0 materialises Upsample(x2) first -- the two must agree bit for bit.
+int ub_debug_conv_up(ub_ctx* ctx, int layer, const float* x0, const float* x1_low, int B, int H, int W, int fused, float* out,
+                     void* stream) {
+  NEED_CTX(ctx);
+  if (layer < 10 || layer > 16 || (layer & 1) || !x0 || !x1_low || !out || (H & 1) || (W & 1)) return ub_fail(ctx, UB_ERR_ARG, "bad argument");
+  if (!ctx->weights_set) return ub_fail(ctx, UB_ERR_STATE, "ub_set_weights has not been called");
+  const LayerDef& d = kLayers[layer];
+  const int lvl = layer < 12 ? 3 : layer < 14 ? 2 : layer < 16 ? 1 : 0;
+  if (B > ctx->max_batch || pp_layout(H, W).Ppl > pp_layout(ctx->net_h >> lvl, ctx->net_w >> lvl).Ppl)
+    return ub_fail(ctx, UB_ERR_ARG, "shape exceeds the context at pyramid level %d", lvl);
+  cudaStream_t st = as_stream(stream);
+  static const int in0[4] = {2, 5, 8, 11}, upb[4] = {21, 19, 17, 15}, outb[4] = {1, 4, 7, 10}, lowb[4] = {4, 7, 10, 13};
+  act_t *s0 = ctx->act[in0[lvl]], *low = ctx->act[lowb[lvl]], *up = ctx->act[upb[lvl]], *o = ctx->act[outb[lvl]];
+  RUN(nchw_to_pp(ctx, x0, B, d.cin0, H, W, s0, d.cin0, st));
+  RUN(nchw_to_pp(ctx, x1_low, B, d.cin1, H / 2, W / 2, low, d.cin1, st));
+  ConvArgs a{};
+  a.src0 = s0; a.out = o; a.B = B; a.H = H; a.W = W;
+  if (fused) {
+    if (!conv_rows_can_upsample(ctx, ctx->conv[layer]) || (H & 3)) return ub_fail(ctx, UB_ERR_ARG, "layer %d has no fused-upsample kernel", layer);
+    a.src1 = low; a.up1 = true;
+  } else {
+    RUN(upsample2_pp(ctx, low, B, d.cin1, H / 2, W / 2, up, st));
+    a.src1 = up;
+  }
+  RUN(run_conv_layer(ctx, ctx->conv[layer], a, st));
+  return pp_to_nchw(ctx, o, B, d.cout, H, W, out, st);
+}
+
 int ub_debug_activation(ub_ctx* ctx, int index, int B, int C, int H, int W, float* out, void* stream) {
   NEED_CTX(ctx);
   if (index < 0 || index > 21 || !out || C > kActC[index]) return ub_fail(ctx, UB_ERR_ARG, "bad argument");

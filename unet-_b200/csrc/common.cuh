@@ -177,6 +177,7 @@ struct ConvArgs {
   const float* head_w; const float* head_b; int num_classes;
   float* logits; uint8_t* pred;
   act_t* pool_out;             // non-null: also write MaxPool2d(2,2) of the output into this PP plane (conv_rows only)
+  bool up1;                    // src1 is [B, cin1, H/2, W/2]: bilinear x2 upsample fused into the operand path (conv_rows only)
 };
 int conv3x3_simt(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv3x3_tc(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
@@ -184,6 +185,7 @@ int conv_tc_init(ub_ctx* ctx);
 int conv3x3_rows(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);
 int conv_rows_init(ub_ctx* ctx);
 bool conv_rows_can_pool(const ub_ctx* ctx, const ConvLayer& L);   // the layer's kernel has a fused-pool variant
+bool conv_rows_can_upsample(const ub_ctx* ctx, const ConvLayer& L);   // ... a fused-upsample variant (ConvArgs::up1)
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // activation buffers (ub_ctx::act): channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu

@@ -49,6 +49,9 @@ struct RowsParams {
   PPLayout L;
   int ncls; float* logits; uint8_t* pred;      // fused 1x1 head (ncls > 0), COUT == 32
   act_t* pool_out; PPLayout Lp; int pool_smem;  // fused MaxPool2d(2,2) (POOL kernels): pooled PP plane, its layout, staging offset
+  // fused Upsample(x2, bilinear, align_corners) of source 1 (UPS kernels): tm1 views the HALF-resolution tensor, box =
+  // low_rows x UP_LC columns x KC/8 chunks, staged in a ring of low_slots boxes at shared-memory offset low_off
+  float up_sy, up_sx; int low_rows, low_chunk, low_stage, low_slots, low_off;
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
 #ifdef UB_ROWS_TRACE
   long long* trace;                            // [6 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
@@ -69,6 +72,9 @@ int g_trace_dump = 0;
 #endif
 
 constexpr int NTHREADS = 19 * 32;        // 16 epilogue warps, producer, two MMA issuers
+constexpr int UP_WARPS = 8;               // UPS kernels: interpolation warps 19..26 (two per 8-channel chunk of a k-block)
+constexpr int UP_LC = 18;                 // staged low-resolution columns: 32 output columns touch at most 17 + 1
+constexpr int UP_BAR = 9;                 // named barrier of the interpolation warps (1..8 belong to the fused pool)
 
 template <int COUT, int KC>
 struct RCfg {
@@ -117,8 +123,16 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
 // interior of the pooled plane is written; its zero border is set once by the host (net_glue.cu).
 constexpr int POOL_SMEM = 16 * 1024;      // 16 warps x 2 buffers x [2 x 16 slots] x 16 B
 
-template <int COUT, int KC, int NCLS, bool POOL>
-__global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
+//
+// UPS: source 1 is given at HALF resolution and `Upsample(scale_factor=2, mode='bilinear', align_corners=True)`
+// (src/models/unetpp.py:76,111-116) happens on the way into shared memory: for a k-block of source 1 the producer
+// stages the low-resolution patch under the box (TMA), and eight interpolation warps write the K-major A operand of
+// the stage -- the same bytes the TMA box of the materialised tensor would have delivered (same packed 16-bit
+// a + l*(c-a) blends as k_upsample2, so the layer's output is bit-identical).  The TMA / MMA / epilogue warps do not
+// change: the stage's `full` barrier simply gets its arrival from the interpolation warps.  Removes the upsampled
+// tensor (2 x 16-bit x Cin1 per pixel written and read back) from HBM.
+template <int COUT, int KC, int NCLS, bool POOL, bool UPS>
+__global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
   using C = RCfg<COUT, KC>;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -127,6 +141,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * S;
   const uint32_t bar_tfull = bar_empty + 8 * S, bar_tempty = bar_tfull + 8 * 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 8));
+  [[maybe_unused]] const uint32_t bar_lfull = smem_u32(smem) + 256, bar_lempty = bar_lfull + 64;   // UPS: low-resolution ring
+  [[maybe_unused]] const uint32_t low_base = smem_u32(smem) + P.low_off;
   float* s_bias = reinterpret_cast<float*>(smem + 512);        // [COUT] (<= 64 floats)
   const uint32_t a_base = smem_u32(smem) + C::HDR;
   const uint32_t b_base = a_base + S * P.a_stage;
@@ -136,6 +152,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
   if (threadIdx.x == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 2); }
     for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, C::WARPS_PER_BUF); }
+    if (UPS) for (int i = 0; i < P.low_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x < COUT) s_bias[threadIdx.x] = P.bias[threadIdx.x];
@@ -154,6 +171,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
       tma_prefetch_desc(&P.tm0);
       tma_prefetch_desc(&P.tm1);
       int s = 0; uint32_t ph = 0; bool first = true;
+      [[maybe_unused]] int ls = 0; [[maybe_unused]] uint32_t lph = 0;
       [[maybe_unused]] int nbox = 0;
       for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
         const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
@@ -161,6 +179,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
         const bool load_b = !P.b_resident || first;
         for (int kb = 0; kb < P.kbn; ++kb) {
           const uint32_t full = bar_full + 8 * s;
+          if (UPS && kb >= P.kb0) {
+            // low-resolution patch under the box: rows yl0.., columns xl0.. of the half-size image (padded coordinates +1)
+            const int xb = tx * T_VALID - 1, yb = ty * T_ROWS * P.mt - 1;
+            const int xl0 = (int)(P.up_sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(P.up_sy * (float)(yb < 0 ? 0 : yb));
+            mbar_wait(bar_lempty + 8 * ls, lph ^ 1);
+            mbar_expect_tx(bar_lfull + 8 * ls, P.low_stage);
+            tma_load_4d(low_base + ls * P.low_stage, &P.tm1, (xl0 + 1) * 8, yl0 + 1, (kb - P.kb0) * C::CPK, b, bar_lfull + 8 * ls);
+            if (++ls == P.low_slots) { ls = 0; lph ^= 1; }
+            if (load_b) {                                      // weights of this k-block ride on the stage's `full` barrier
+              mbar_wait(bar_empty + 8 * s, ph ^ 1);            // (its previous phase is over once the slot has been released)
+              mbar_expect_tx_only(full, C::B_STAGE);
+              bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE, P.w + (size_t)kb * 3 * (size_t)(KC * C::NP), C::B_STAGE, full);
+            }
+            if (++s == S) { s = 0; ph ^= 1; }
+            continue;
+          }
           UB_TR(0, nbox, 0);
           mbar_wait(bar_empty + 8 * s, ph ^ 1);
           UB_TR(0, nbox, 1);
@@ -177,7 +211,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
         first = false;
       }
     }
-  } else if (warp >= 17) {
+  } else if (warp == 17 || warp == 18) {
     // ===================== MMA issuers (warps 17, 18) =====================
     // Two warps issue alternate M-tiles (tile parity = accumulator parity).  For a lone issuer the barrier waits and the
     // two tcgen05.commit per tile (~90 clk each) do not overlap its own MMAs: tools/ubench_commit.cu measures 647 clk per
@@ -236,6 +270,89 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
           __syncwarp();
           if (++s == S) { s = 0; ph ^= 1; }
         }
+      }
+    }
+  } else if (UPS && warp >= 19) {
+    // ===================== interpolation warps (UPS): A operand of the source-1 k-blocks =====================
+    // Warp = (chunk of the k-block, half of the box rows), lane = box column.  A thread walks down its rows exactly as
+    // k_upsample2 does: column terms once per group, every low-resolution row x-blended once, one y-blend per output.
+    if constexpr (UPS) {
+      const int iw = warp - 19, cc = iw & 3, rhalf = iw >> 2;
+      const int R = T_ROWS * P.mt + 2, r_begin = rhalf * (R >> 1), r_end = r_begin + (R >> 1);
+      const int step_b = (int)gridDim.x / tiles_per_img, step_r = (int)gridDim.x - step_b * tiles_per_img;
+      const int step_y = step_r / P.tiles_x, step_x = step_r - step_y * P.tiles_x;
+      int b = (int)blockIdx.x / tiles_per_img, tgy, tx;
+      {
+        const int t = (int)blockIdx.x - b * tiles_per_img;
+        tgy = t / P.tiles_x; tx = t - tgy * P.tiles_x;
+      }
+      int s = 0; uint32_t ph = 0; int ls = 0; uint32_t lph = 0;
+      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
+        const int xb = tx * T_VALID - 1, yb = tgy * T_ROWS * P.mt - 1;
+        const int xl0 = (int)(P.up_sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(P.up_sy * (float)(yb < 0 ? 0 : yb));
+        const int x = xb + lane;
+        const bool xin = x >= 0 && x < L.W;                      // outside: zero border (or never-consumed columns)
+        const float fx = P.up_sx * (float)(x < 0 ? 0 : (x >= L.W ? L.W - 1 : x));
+        const int x0 = (int)fx;
+        const float lx = fx - (float)x0;
+        const act2_t lx2 = f2a2(lx, lx);
+        const uint32_t col_off = (uint32_t)(x0 - xl0) * 16 + cc * P.low_chunk;
+        for (int kb = 0; kb < P.kbn; ++kb) {
+          if (kb >= P.kb0) {
+            mbar_wait(bar_lfull + 8 * ls, lph);                  // low-resolution patch landed
+            mbar_wait(bar_empty + 8 * s, ph ^ 1);                // the stage's previous MMAs have retired
+            const uint32_t lo = low_base + ls * P.low_stage + col_off;
+            const uint32_t dst = a_base + s * P.a_stage + cc * P.a_chunk + lane * 16;
+            act2_t top[4], bot[4];
+            auto blend_row = [&](int row, act2_t* r) {
+              uint32_t a0, a1, a2, a3, c0, c1, c2, c3;
+              ld_shared_v4(lo + row * (UP_LC * 16), a0, a1, a2, a3);
+              ld_shared_v4(lo + row * (UP_LC * 16) + 16, c0, c1, c2, c3);
+              const uint32_t av[4] = {a0, a1, a2, a3}, cv[4] = {c0, c1, c2, c3};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const act2_t ha = *reinterpret_cast<const act2_t*>(&av[j]), hc = *reinterpret_cast<const act2_t*>(&cv[j]);
+                r[j] = __hfma2(lx2, __hsub2(hc, ha), ha);
+              }
+            };
+            int cur = -2;
+            for (int r = r_begin; r < r_end; ++r) {
+              const int y = yb + r;
+              const bool yin = y >= 0 && y < L.H;
+              const float fy = P.up_sy * (float)(y < 0 ? 0 : (y >= L.H ? L.H - 1 : y));
+              const int y0 = (int)fy;
+              const float ly = fy - (float)y0;
+              const act2_t ly2 = f2a2(ly, ly);
+              if (y0 != cur) {
+                if (y0 == cur + 1) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) top[j] = bot[j];
+                } else {
+                  blend_row(y0 - yl0, top);
+                }
+                blend_row(y0 + 1 - yl0, bot);
+                cur = y0;
+              }
+              uint32_t o[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const act2_t v = __hfma2(ly2, __hsub2(bot[j], top[j]), top[j]);
+                o[j] = (xin && yin) ? *reinterpret_cast<const uint32_t*>(&v) : 0u;
+              }
+              st_shared_v4(dst + r * SEG_BYTES, o[0], o[1], o[2], o[3]);
+            }
+            fence_proxy_async_smem();                            // generic-proxy writes -> visible to the tensor core's reads
+            named_bar_sync(UP_BAR, UP_WARPS * 32);
+            if (iw == 0 && lane == 0) { mbar_arrive(bar_full + 8 * s); mbar_arrive(bar_lempty + 8 * ls); }
+            if (++ls == P.low_slots) { ls = 0; lph ^= 1; }
+          }
+          if (++s == S) { s = 0; ph ^= 1; }
+        }
+        tx += step_x;
+        if (tx >= P.tiles_x) { tx -= P.tiles_x; ++tgy; }
+        tgy += step_y;
+        if (tgy >= P.tiles_y) { tgy -= P.tiles_y; ++b; }
+        b += step_b;
       }
     }
   } else {
@@ -393,11 +510,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_rows(const __grid_constant
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 
-template <int COUT, int KC, int NCLS, bool POOL = false>
+template <int COUT, int KC, int NCLS, bool POOL = false, bool UPS = false>
 int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
   using C = RCfg<COUT, KC>;
-  auto kern = k_conv_rows<COUT, KC, NCLS, POOL>;
-  constexpr int BUDGET = SMEM_BUDGET - (POOL ? POOL_SMEM : 0);
+  static_assert(!UPS || KC == 32, "fused upsample: the interpolation warps are laid out for four chunks per k-block");
+  auto kern = k_conv_rows<COUT, KC, NCLS, POOL, UPS>;
+  constexpr int LOW_SLOTS = 2;
+  // UPS: room for the ring of low-resolution patches; a patch under a (4*mt+2)-row box has at most 2*mt+3 rows
+  // (the source index advances by < 0.5 per output row), sized here for the largest mt
+  constexpr int BUDGET = SMEM_BUDGET - (POOL ? POOL_SMEM : 0) - (UPS ? LOW_SLOTS * C::CPK * (2 * C::NBUF + 3) * UP_LC * 16 : 0);
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
@@ -427,10 +548,18 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   P.tiles_y = a.H / (T_ROWS * mt);
   P.total_items = (long long)a.B * P.tiles_x * P.tiles_y;
   int r = tmap_pp_rows(ctx, &P.tm0, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
-  if (r == UB_OK) r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK)
-                              : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
-  if (r != UB_OK) return r;
   int smem = C::HDR + stages * P.a_stage + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
+  if (UPS) {
+    const int h = a.H / 2, w = a.W / 2;
+    P.up_sy = (float)(h - 1) / (float)(a.H - 1); P.up_sx = (float)(w - 1) / (float)(a.W - 1);   // as upsample2_pp
+    P.low_rows = 2 * mt + 3; P.low_chunk = P.low_rows * UP_LC * 16; P.low_stage = C::CPK * P.low_chunk;
+    P.low_slots = LOW_SLOTS; P.low_off = smem; smem += LOW_SLOTS * P.low_stage;
+    if (r == UB_OK) r = tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, pp_layout(h, w), UP_LC, P.low_rows, C::CPK);
+  } else if (r == UB_OK) {
+    r = Lr.cin1 ? tmap_pp_rows(ctx, &P.tm1, a.src1, a.B, Lr.cin1 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK)
+                : tmap_pp_rows(ctx, &P.tm1, a.src0, a.B, Lr.cin0 / 8, P.L, T_COLS, T_ROWS * mt + 2, C::CPK);
+  }
+  if (r != UB_OK) return r;
   if (POOL) { P.pool_smem = (smem + 1023) & ~1023; smem = P.pool_smem + POOL_SMEM; }
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
 #ifdef UB_ROWS_TRACE
@@ -440,7 +569,7 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   UB_CUDA(ctx, cudaMemsetAsync(d_trace, 0, tr_bytes, st));
   P.trace = d_trace;
 #endif
-  kern<<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  kern<<<(unsigned)grid, UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, smem, st>>>(P);
   UB_CHECK_LAUNCH(ctx);
 #ifdef UB_ROWS_TRACE
   if (const char* dir = getenv("UB_ROWS_TRACE_DIR")) {
@@ -465,6 +594,11 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& 
     if (cout != 32 || kc != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs COUT=32 KC=32 (got %d, %d)", cout, kc);
     return P.ncls == 3 ? launch_rows<32, 32, 3>(ctx, P, a, Lr, st, init_only) : launch_rows<32, 32, 8>(ctx, P, a, Lr, st, init_only);
   }
+  if (a.up1 || (init_only && P.low_slots)) {
+    if (cout == 32 && kc == 32) return launch_rows<32, 32, 0, false, true>(ctx, P, a, Lr, st, init_only);
+    if (cout == 64 && kc == 32) return launch_rows<64, 32, 0, false, true>(ctx, P, a, Lr, st, init_only);
+    return ub_fail(ctx, UB_ERR_ARG, "conv_rows: no fused upsample for COUT=%d KC=%d", cout, kc);
+  }
   if (P.pool_out) {
     if (cout == 32 && kc == 32) return launch_rows<32, 32, 0, true>(ctx, P, a, Lr, st, init_only);
     if (cout == 64 && kc == 64) return launch_rows<64, 64, 0, true>(ctx, P, a, Lr, st, init_only);
@@ -481,16 +615,22 @@ int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& 
 
 int conv_rows_init(ub_ctx* ctx) {
   static RowsParams P{};
-  const int cfgs[8][4] = {{32, 16, 0, 0}, {32, 32, 0, 0}, {64, 32, 0, 0}, {64, 64, 0, 0}, {32, 32, 3, 0}, {32, 32, 8, 0},
-                          {32, 32, 0, 1}, {64, 64, 0, 1}};
+  const int cfgs[10][4] = {{32, 16, 0, 0}, {32, 32, 0, 0}, {64, 32, 0, 0}, {64, 64, 0, 0}, {32, 32, 3, 0}, {32, 32, 8, 0},
+                           {32, 32, 0, 1}, {64, 64, 0, 1}, {32, 32, 0, 2}, {64, 32, 0, 2}};
   ConvArgs a{}; ConvLayer Lr{};
   for (auto& c : cfgs) {
     P.ncls = c[2];
-    P.pool_out = c[3] ? reinterpret_cast<act_t*>(&P) : nullptr;     // any non-null value: selects the POOL instantiation
+    P.pool_out = c[3] == 1 ? reinterpret_cast<act_t*>(&P) : nullptr;     // any non-null value: selects the POOL instantiation
+    P.low_slots = c[3] == 2;                                             // ... and the UPS instantiation
     int r = dispatch_rows(ctx, c[0], c[1], P, a, Lr, nullptr, true);
     if (r != UB_OK) return r;
   }
   return UB_OK;
+}
+
+bool conv_rows_can_upsample(const ub_ctx* ctx, const ConvLayer& L) {
+  static const bool off = getenv("UB_FUSE_UP") && atoi(getenv("UB_FUSE_UP")) == 0;
+  return !off && ctx->conv_impl != 1 && L.fold && L.cin1 > 0 && L.kc == 32 && (L.cout == 32 || L.cout == 64);
 }
 
 bool conv_rows_can_pool(const ub_ctx* ctx, const ConvLayer& L) {
@@ -510,6 +650,8 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
     if (a.head_w || (a.H & 1) || (a.W & 1)) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: fused pool needs even H, W and no head");
     P.pool_out = a.pool_out; P.Lp = pp_layout(a.H / 2, a.W / 2);
   }
+  if (a.up1 && (!Lr.cin1 || a.pool_out || a.head_w || (a.H & 1) || (a.W & 1)))
+    return ub_fail(ctx, UB_ERR_ARG, "conv_rows: fused upsample needs a second source, even H, W, no pool and no head");
   if (a.head_w) {
     if (Lr.cout != 32) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == 32");
     P.ncls = a.num_classes;

@@ -206,9 +206,9 @@ int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStrea
 
 static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
                     act_t* out, int B, int H, int W, cudaStream_t st,
-                    float* logits = nullptr, uint8_t* pred = nullptr, bool head = false, act_t* pool_out = nullptr) {
+                    float* logits = nullptr, uint8_t* pred = nullptr, bool head = false, act_t* pool_out = nullptr, bool up1 = false) {
   ConvArgs a{};
-  a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W; a.pool_out = pool_out;
+  a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W; a.pool_out = pool_out; a.up1 = up1;
   if (head) {
     a.head_w = ctx->head_w; a.head_b = ctx->head_b; a.num_classes = ctx->num_classes;
     a.logits = logits; a.pred = pred;
@@ -235,6 +235,17 @@ static int run_conv_pool(ub_ctx* ctx, int li, int pslot, const act_t* src, act_t
   return run_conv(ctx, li, src, nullptr, out, B, H, W, st, nullptr, nullptr, false, pooled);
 }
 
+// conv1 of a decoder block on cat([skip, up(below)]) (unetpp.py:111-116).  Where the layer's kernel has the fused
+// variant, `below` goes in at half resolution and is interpolated on the way into shared memory; otherwise the
+// upsampled tensor is materialised in `up` first.
+static int run_conv_up(ub_ctx* ctx, int li, const act_t* skip, const act_t* below, act_t* up, act_t* out, int Cbelow,
+                       int B, int H, int W, cudaStream_t st) {
+  if (conv_rows_can_upsample(ctx, ctx->conv[li]) && !(H & 3))
+    return run_conv(ctx, li, skip, below, out, B, H, W, st, nullptr, nullptr, false, nullptr, true);
+  RUN(upsample2_pp(ctx, below, B, Cbelow, H / 2, W / 2, up, st));
+  return run_conv(ctx, li, skip, up, out, B, H, W, st);
+}
+
 // The network input comes from exactly one of x_nchw / frames; with frames the preprocess kernel writes the PP input.
 int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const uint8_t* frames, int fh, int fw,
                    float* logits, uint8_t* pred, cudaStream_t st) {
@@ -259,17 +270,13 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const 
   RUN(run_conv(ctx, 9, A[A_T4], nullptr, A[A_X40], B, h4, w4, st));
   // decoder (unetpp.py:111-116): cat([skip, up(below)]) is never materialised -- the conv reads its K range from
   // two sources
-  RUN(upsample2_pp(ctx, A[A_X40], B, 512, h4, w4, A[A_UP4], st));
-  RUN(run_conv(ctx, 10, A[A_X30], A[A_UP4], A[A_T3], B, h3, w3, st));
+  RUN(run_conv_up(ctx, 10, A[A_X30], A[A_X40], A[A_UP4], A[A_T3], 512, B, h3, w3, st));
   RUN(run_conv(ctx, 11, A[A_T3], nullptr, A[A_X31], B, h3, w3, st));
-  RUN(upsample2_pp(ctx, A[A_X31], B, 256, h3, w3, A[A_UP3], st));
-  RUN(run_conv(ctx, 12, A[A_X20], A[A_UP3], A[A_T2], B, h2, w2, st));
+  RUN(run_conv_up(ctx, 12, A[A_X20], A[A_X31], A[A_UP3], A[A_T2], 256, B, h2, w2, st));
   RUN(run_conv(ctx, 13, A[A_T2], nullptr, A[A_X22], B, h2, w2, st));
-  RUN(upsample2_pp(ctx, A[A_X22], B, 128, h2, w2, A[A_UP2], st));
-  RUN(run_conv(ctx, 14, A[A_X10], A[A_UP2], A[A_T1], B, h1, w1, st));
+  RUN(run_conv_up(ctx, 14, A[A_X10], A[A_X22], A[A_UP2], A[A_T1], 128, B, h1, w1, st));
   RUN(run_conv(ctx, 15, A[A_T1], nullptr, A[A_X13], B, h1, w1, st));
-  RUN(upsample2_pp(ctx, A[A_X13], B, 64, h1, w1, A[A_UP1], st));
-  RUN(run_conv(ctx, 16, A[A_X00], A[A_UP1], A[A_T0], B, H, W, st));
+  RUN(run_conv_up(ctx, 16, A[A_X00], A[A_X13], A[A_UP1], A[A_T0], 64, B, H, W, st));
   // conv0_4.conv2 with the 1x1 `final` head (unetpp.py:119) and argmax fused in the epilogue
   RUN(run_conv(ctx, 17, A[A_T0], nullptr, A[A_X04], B, H, W, st, logits, pred, true));
   return UB_OK;
