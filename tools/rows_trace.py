@@ -14,14 +14,14 @@ def med(x):
 def report(path):
     raw = np.fromfile(path, dtype=np.int64)
     cout, kc, ncls, kbn, mt, stages, items, grid = raw[:8]
-    t = raw[8:].reshape(6, TR_N, 8)
+    t = raw[8:].reshape(7, TR_N, 8)
     groups = (items + grid - 1) // grid
     tiles = min(int(groups * mt), TR_N)
     boxes = min(int(groups * kbn), TR_N)
     print(f"== {path}: COUT={cout} KC={kc} NCLS={ncls} kbn={kbn} mt={mt} stages={stages} groups/CTA={groups}")
     p, m = t[0, :boxes], t[1, :tiles]
     t0 = p[0, 0]
-    span = max(m[:, 2].max(), t[2:, :, 3].max()) - t0
+    span = max(m[:, 2].max(), t[2:6, :, 3].max()) - t0
     print(f"  block 0 span {span} clk = {span / tiles:.0f} clk per M-tile")
     # producer
     print(f"  producer: wait-empty {med(p[2:, 1] - p[2:, 0]):.0f}  issue {med(p[2:, 2] - p[2:, 1]):.0f}  "
@@ -52,6 +52,14 @@ def report(path):
         if mt == nbuf:
             print(f"      tile end -> next group top {med(e[1:, 4] - e[:-1, 3]):.0f}  group top -> before wait {med(e[:, 0] - e[:, 4]):.0f}  "
                   f"tfull seen -> first TMEM data {med(e[:, 5] - e[:, 1]):.0f}  first-half math + second load {med(e[:, 2] - e[:, 5]):.0f}")
+    # interpolation warp 0 (fused upsample)
+    u = t[6]
+    nu = int((u[:, 3] > 0).sum())
+    if nu > 4:
+        u = u[2:nu]
+        print(f"  interp warp 0: wait-low {med(u[:, 1] - u[:, 0]):.0f} (mean {(u[:, 1] - u[:, 0]).mean():.0f})  wait-empty {med(u[:, 2] - u[:, 1]):.0f} "
+              f"(mean {(u[:, 2] - u[:, 1]).mean():.0f})  interpolate+store {med(u[:, 3] - u[:, 2]):.0f} (mean {(u[:, 3] - u[:, 2]).mean():.0f})  "
+              f"stage period {med(np.diff(u[:, 3])):.0f} (mean {np.diff(u[:, 3]).mean():.0f})")
     # latency from MMA commit to epilogue start, from epilogue arrive to MMA resume
     if cout != 64:
         for g in range(1):

@@ -147,7 +147,7 @@ void ub_destroy(ub_ctx* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto& p : c->act) cudaFree(p);
-  for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.bias); }
+  for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.w2); cudaFree(L.bias); }
   cudaFree(c->head_w); cudaFree(c->head_b);
   cudaFree(c->d_frames); cudaFree(c->d_gray); cudaFree(c->d_pred);
   for (auto& p : c->d_mask) cudaFree(p);
@@ -204,7 +204,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     RUN(get(bn + ".running_mean", d.cout, &mu));
     RUN(get(bn + ".running_var", d.cout, &var));
     const int kbn = cin_pad / d.kc, cpk = d.kc / 8, nnt = d.cout / d.bn;
-    std::vector<act_t> wp((size_t)d.cout * cin_pad * 9);
+    std::vector<act_t> wp((size_t)d.cout * cin_pad * 9), wp2(d.fold ? wp.size() : 0);
     std::vector<float> bias(d.cout);
     for (int co = 0; co < d.cout; ++co) {
       const double scale = (double)g[co] / sqrt((double)var[co] + 1e-5);
@@ -221,6 +221,10 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
           const size_t o = d.fold ? (((((size_t)kb * 3 + tap / 3) * cpk + cc) * (3 * d.cout) + (tap % 3) * d.cout + co) * 8) + j
                                   : ((((((size_t)nt * kbn + kb) * 9 + tap) * cpk + cc) * d.bn + r) * 8) + j;
           wp[o] = f2a(v);
+          if (d.fold) {
+            const int nph = 3 * d.cout / 2, n = (tap % 3) * d.cout + co;
+            wp2[((((((size_t)(n / nph) * kbn + kb) * 3 + tap / 3) * cpk + cc) * nph) + n % nph) * 8 + j] = wp[o];
+          }
         }
       }
     }
@@ -229,6 +233,10 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn; L.fold = d.fold;
     if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
     if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
+    if (d.fold) {
+      if (!L.w2) RUN(dmalloc(ctx, &L.w2, wp2.size()));
+      UB_CUDA(ctx, cudaMemcpy(L.w2, wp2.data(), wp2.size() * sizeof(act_t), cudaMemcpyHostToDevice));
+    }
     UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(act_t), cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
   }

@@ -87,6 +87,9 @@ struct ConvLayer {
   int fold = 0;        // 1: kx-folded weights [kblock][ky][kc/8][kx*cout+co][8] (conv_rows.cu, cout <= 64)
   // weights bf16 [cout/bn][kblocks][9 taps][kc/8][bn][8], bias fp32 [cout]
   act_t* w = nullptr;
+  // fold layers, CTA-pair kernels: the same weights split by halves of N' = 3*cout,
+  // [half][kblock][ky][kc/8][N'/2][8] (each CTA of a pair holds one half, contiguous)
+  act_t* w2 = nullptr;
   float* bias = nullptr;
 };
 

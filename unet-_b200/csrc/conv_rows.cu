@@ -52,14 +52,16 @@ struct RowsParams {
   // fused Upsample(x2, bilinear, align_corners) of source 1 (UPS kernels): tm1 views the HALF-resolution tensor, box =
   // low_rows x UP_LC columns x KC/8 chunks, staged in a ring of low_slots boxes at shared-memory offset low_off
   float up_sy, up_sx; int low_rows, low_chunk, low_stage, low_slots, low_off;
+  int wbytes;                                  // CG2 kernels: bytes of this CTA's half of the weights (all k-blocks, resident)
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
 #ifdef UB_ROWS_TRACE
-  long long* trace;                            // [6 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
+  long long* trace;                            // [7 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
 #endif
 };
 
 // Pipeline trace (debug builds only, tools/build_trace_lib.sh): block 0 stamps clock64 at the hand-over points of every
-// role.  Roles: 0 producer (index = box), 1 MMA issuer (index = M-tile), 2.. epilogue warpgroups (index = use).
+// role.  Roles: 0 producer (index = box), 1 MMA issuer (index = M-tile), 2-5 epilogue warpgroups (index = use),
+// 6 interpolation warp 0 (index = source-1 stage).
 #ifdef UB_ROWS_TRACE
 constexpr int TR_N = 1024;
 int g_trace_dump = 0;
@@ -76,11 +78,12 @@ constexpr int UP_WARPS = 8;               // UPS kernels: interpolation warps 19
 constexpr int UP_LC = 18;                 // staged low-resolution columns: 32 output columns touch at most 17 + 1
 constexpr int UP_BAR = 9;                 // named barrier of the interpolation warps (1..8 belong to the fused pool)
 
-template <int COUT, int KC>
+template <int COUT, int KC, bool CG2 = false>
 struct RCfg {
   static constexpr int NP = 3 * COUT;                          // folded N
+  static constexpr int NPH = CG2 ? NP / 2 : NP;                // rows of B this CTA holds (a CTA pair splits N between its two CTAs)
   static constexpr int CPK = KC / 8;
-  static constexpr int B_KY = KC * NP * 2;                     // one ky of one k-block
+  static constexpr int B_KY = KC * NPH * 2;                    // one ky of one k-block
   static constexpr int B_STAGE = 3 * B_KY;
   static constexpr bool SPLIT = COUT == 64;                    // two warpgroups share one accumulator
   static constexpr int NBUF = SPLIT ? 2 : 4;
@@ -111,6 +114,116 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
   return r;
 }
 
+// Interpolation warp of a UPS kernel.  Warp = (chunk of the k-block, half of the box rows), lane = box column; NR = rows
+// per warp = 2*mt+1.  The arithmetic is k_upsample2's: source index = dst * (in-1)/(out-1) in fp32, x-blend of every
+// low-resolution row once, one y-blend per output, all as packed 16-bit a + l*(c-a).  Per group a thread sets up its
+// column terms and a row table (low-resolution row offset, packed y weight) in registers; a stage is then NR
+// iterations of {0-2 row loads + x-blends, one y-blend, one 16-byte store}.  Each warp arrives on the stage's barriers
+// by itself (full / lempty count UP_WARPS arrivals), so the eight warps never wait for one another.
+template <int NR, bool CG2>
+__device__ __forceinline__ void ups_warp(const RowsParams& P, const int iw, const int lane, const uint32_t bar_full,
+                                         const uint32_t bar_empty, const uint32_t bar_lfull, const uint32_t bar_lempty,
+                                         const uint32_t a_base, const uint32_t low_base) {
+  const int cc = iw & 3, r_begin = (iw >> 2) * NR;
+  const int S = P.num_stages, LS = P.low_slots, kb0 = P.kb0, kbn = P.kbn, W = P.L.W, H = P.L.H, mtr = T_ROWS * P.mt;
+  const int a_stage = P.a_stage, low_stage = P.low_stage, tiles_x = P.tiles_x, tiles_y = P.tiles_y;
+  const float sx = P.up_sx, sy = P.up_sy;
+  const long long total = P.total_items;
+  const int tiles_per_img = tiles_x * tiles_y;
+  const int step_b = (int)gridDim.x / tiles_per_img, step_r = (int)gridDim.x - step_b * tiles_per_img;
+  const int step_y = step_r / tiles_x, step_x = step_r - step_y * tiles_x;
+  int tgy, tx;
+  {
+    const int t = (int)blockIdx.x % tiles_per_img;
+    tgy = t / tiles_x; tx = t - tgy * tiles_x;
+  }
+  const uint32_t dst0 = a_base + cc * P.a_chunk + lane * 16 + r_begin * SEG_BYTES;
+  const uint32_t lo0 = low_base + cc * P.low_chunk;
+  int s = 0; uint32_t ph = 0; int ls = 0; uint32_t lph = 0;
+  [[maybe_unused]] int nst = 0;
+  const long long rank = CG2 ? (long long)cluster_ctarank() : 0;
+  for (long long grp = blockIdx.x; grp - rank < total; grp += gridDim.x) {
+    if (CG2 && grp >= total) { tx = tiles_x - 1; tgy = tiles_y - 1; }       // odd tail: the peer repeats the last group
+    const int xb = tx * T_VALID - 1, yb = tgy * mtr - 1;
+    const int xl0 = (int)(sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(sy * (float)(yb < 0 ? 0 : yb));
+    const int x = xb + lane;
+    const float fx = sx * (float)(x < 0 ? 0 : (x >= W ? W - 1 : x));
+    const int x0 = (int)fx;
+    const float lxf = fx - (float)x0;
+    const act2_t lx2 = f2a2(lxf, lxf);
+    const uint32_t lo_col = lo0 + (uint32_t)(x0 - xl0) * 16;
+    int roff[NR]; uint32_t lyp[NR]; uint32_t ok = 0;            // row table of this group
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+      const int y = yb + r_begin + i;
+      const float fy = sy * (float)(y < 0 ? 0 : (y >= H ? H - 1 : y));
+      const int y0 = (int)fy;
+      const float lyf = fy - (float)y0;
+      const act2_t l2 = f2a2(lyf, lyf);
+      roff[i] = (y0 - yl0) * (UP_LC * 16);
+      lyp[i] = *reinterpret_cast<const uint32_t*>(&l2);
+      if (y >= 0 && y < H && x >= 0 && x < W) ok |= 1u << i;      // outside: zero border (or never-consumed columns)
+    }
+    for (int kb = 0; kb < kbn; ++kb) {
+      if (kb >= kb0) {
+        if (iw == 0 && lane == 0) UB_TR(6, nst, 0);
+        mbar_wait_sleep(bar_lfull + 8 * ls, lph);                // low-resolution patch landed
+        if (iw == 0 && lane == 0) UB_TR(6, nst, 1);
+        mbar_wait_sleep(bar_empty + 8 * s, ph ^ 1);              // the stage's previous MMAs have retired
+        if (iw == 0 && lane == 0) UB_TR(6, nst, 2);
+        const uint32_t lo = lo_col + ls * low_stage, dst = dst0 + s * a_stage;
+        act2_t top[4], bot[4];
+        auto blend_row = [&](uint32_t addr, act2_t* r) {
+          uint32_t av[4], cv[4];
+          lds_v4(addr, av[0], av[1], av[2], av[3]);
+          lds_v4(addr + 16, cv[0], cv[1], cv[2], cv[3]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const act2_t ha = *reinterpret_cast<const act2_t*>(&av[j]), hc = *reinterpret_cast<const act2_t*>(&cv[j]);
+            r[j] = __hfma2(lx2, __hsub2(hc, ha), ha);
+          }
+        };
+        int cur = -(1 << 20);
+#pragma unroll
+        for (int i = 0; i < NR; ++i) {
+          if (roff[i] != cur) {                                  // warp-uniform
+            if (roff[i] == cur + UP_LC * 16) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) top[j] = bot[j];
+            } else {
+              blend_row(lo + roff[i], top);
+            }
+            blend_row(lo + roff[i] + UP_LC * 16, bot);
+            cur = roff[i];
+          }
+          const act2_t ly2 = *reinterpret_cast<const act2_t*>(&lyp[i]);
+          uint32_t o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const act2_t v = __hfma2(ly2, __hsub2(bot[j], top[j]), top[j]);
+            o[j] = (ok >> i) & 1u ? *reinterpret_cast<const uint32_t*>(&v) : 0u;
+          }
+          sts_v4(dst + i * SEG_BYTES, o[0], o[1], o[2], o[3]);
+        }
+        if (CG2) fence_proxy_async_all(); else fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's reads
+        __syncwarp();
+        if (lane == 0) {                                         // CG2: bar_full is the leader CTA's barrier (shared::cluster address)
+          if (CG2) mbar_arrive_cluster(bar_full + 8 * s); else mbar_arrive(bar_full + 8 * s);
+          mbar_arrive(bar_lempty + 8 * ls);
+        }
+        if (iw == 0 && lane == 0) UB_TR(6, nst, 3);
+        ++nst;
+        if (++ls == LS) { ls = 0; lph ^= 1; }
+      }
+      if (++s == S) { s = 0; ph ^= 1; }
+    }
+    tx += step_x;
+    if (tx >= tiles_x) { tx -= tiles_x; ++tgy; }
+    tgy += step_y;
+    if (tgy >= tiles_y) tgy -= tiles_y;
+  }
+}
+
 // NCLS: 0 = plain layer; 3 = fused head with exactly 3 classes (the shipped model); 8 = fused head with a run-time
 // class count <= 8.  The class count must be a compile-time constant on the hot configuration: with the run-time
 // bound the head cost 8x32 predicated FFMAs plus local-memory traffic per pixel and made the last layer issue-bound
@@ -131,9 +244,19 @@ constexpr int POOL_SMEM = 16 * 1024;      // 16 warps x 2 buffers x [2 x 16 slot
 // a + l*(c-a) blends as k_upsample2, so the layer's output is bit-identical).  The TMA / MMA / epilogue warps do not
 // change: the stage's `full` barrier simply gets its arrival from the interpolation warps.  Removes the upsampled
 // tensor (2 x 16-bit x Cin1 per pixel written and read back) from HBM.
-template <int COUT, int KC, int NCLS, bool POOL, bool UPS>
+//
+// CG2: the CTAs run as pairs (clusters of two on one TPC) and the leader issues tcgen05.mma.cta_group::2 with M = 256:
+// rows 0-127 are the leader's M-tile, rows 128-255 the peer's (each from its own shared memory, into its own TMEM), and
+// each CTA holds half of the N' weight rows.  Measured (tools/ubench_mma2.cu): an N' = 96 MMA costs 72 clk per 128 rows
+// with cta_group::1 (the ~60-clk floor is per instruction) but 49.4 clk per 256 rows as a pair -- 5450 -> 7970
+// FLOP/clk/SM -- and the B operand is read from shared memory once per 256 rows.  Both CTAs walk the same sequence of
+// stages; everything that tells the issuing thread "ready" (TMA complete_tx, interpolation warps, epilogue warps
+// handing accumulators back) arrives on the LEADER's barriers, and the leader's commits are multicast to both CTAs.
+// Weights are resident: every CTA loads its half once before the loop.
+template <int COUT, int KC, int NCLS, bool POOL, bool UPS, bool CG2>
 __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) k_conv_rows(const __grid_constant__ RowsParams P) {
-  using C = RCfg<COUT, KC>;
+  using C = RCfg<COUT, KC, CG2>;
+  const uint32_t rank = CG2 ? cluster_ctarank() : 0;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = P.num_stages;
@@ -149,21 +272,43 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
   const PPLayout& L = P.L;
   const int tiles_per_img = P.tiles_x * P.tiles_y;
 
+  constexpr int NCTA = CG2 ? 2 : 1;
+  const uint32_t bar_w = smem_u32(smem) + 384;                 // CG2: this CTA's resident weights have landed
   if (threadIdx.x == 0) {
-    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 2); }
-    for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, C::WARPS_PER_BUF); }
-    if (UPS) for (int i = 0; i < P.low_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, 1); }
+    // CG2: the leader's full / tempty barriers also count the peer's interpolation / epilogue warps
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, UPS ? NCTA * UP_WARPS : 1); mbar_init(bar_empty + 8 * i, 2); }
+    for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, NCTA * C::WARPS_PER_BUF); }
+    if (UPS) for (int i = 0; i < P.low_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, UP_WARPS); }
+    if (CG2) mbar_init(bar_w, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x < COUT) s_bias[threadIdx.x] = P.bias[threadIdx.x];
   if (warp == 16) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (CG2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // where "ready" signals go: the leader CTA's barriers (shared::cluster addresses), or this CTA's own without pairs
+  [[maybe_unused]] const uint32_t lead_full = CG2 ? mapa_u32(bar_full, 0) : bar_full;
+  [[maybe_unused]] const uint32_t lead_tempty = CG2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
+  if constexpr (CG2) {
+    // resident weights: this CTA's half of every k-block, loaded once; the pair starts when both halves are in
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(bar_w, P.wbytes);
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(P.w) + (size_t)rank * P.wbytes;
+      for (int o = 0; o < P.wbytes; o += 32768) bulk_g2s(b_base + o, src + o, P.wbytes - o < 32768 ? P.wbytes - o : 32768, bar_w);
+    }
+    mbar_wait(bar_w, 0);
+    cluster_sync();                                            // also: the peer's barriers exist before anything arrives on them
+  }
 
   if (warp == 16) {
     // ===================== producer: one TMA box (+ one weight copy) per k-block =====================
@@ -173,10 +318,11 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
       int s = 0; uint32_t ph = 0; bool first = true;
       [[maybe_unused]] int ls = 0; [[maybe_unused]] uint32_t lph = 0;
       [[maybe_unused]] int nbox = 0;
-      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
+      for (long long grp0 = blockIdx.x; grp0 - rank < P.total_items; grp0 += gridDim.x) {
+        const long long grp = grp0 < P.total_items ? grp0 : P.total_items - 1;    // CG2 odd tail: the peer repeats the last group
         const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
         const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
-        const bool load_b = !P.b_resident || first;
+        const bool load_b = !CG2 && (!P.b_resident || first);
         for (int kb = 0; kb < P.kbn; ++kb) {
           const uint32_t full = bar_full + 8 * s;
           if (UPS && kb >= P.kb0) {
@@ -198,10 +344,22 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
           UB_TR(0, nbox, 0);
           mbar_wait(bar_empty + 8 * s, ph ^ 1);
           UB_TR(0, nbox, 1);
-          mbar_expect_tx(full, P.a_stage + (load_b ? C::B_STAGE : 0));
           // box origin: padded row 4*mt*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
+          if constexpr (CG2) {
+            // both CTAs' boxes complete on the leader's barrier; the leader expects the bytes of both
+            if (rank == 0) {
+              mbar_expect_tx(full, 2 * P.a_stage);
+              if (UPS) mbar_arrive_n(full, 2 * UP_WARPS - 1);
+            }
+            const CUtensorMap* tm = kb < P.kb0 ? &P.tm0 : &P.tm1;
+            tma_load_4d_pair(a_base + s * P.a_stage, tm, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb < P.kb0 ? kb : kb - P.kb0) * C::CPK, b,
+                             lead_full + 8 * s);
+          } else {
+          mbar_expect_tx(full, P.a_stage + (load_b ? C::B_STAGE : 0));
+          if (UPS) mbar_arrive_n(full, UP_WARPS - 1);            // UPS kernels: `full` counts the eight interpolation warps
           if (kb < P.kb0) tma_load_4d(a_base + s * P.a_stage, &P.tm0, tx * T_VALID * 8, ty * T_ROWS * P.mt, kb * C::CPK, b, full);
           else tma_load_4d(a_base + s * P.a_stage, &P.tm1, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb - P.kb0) * C::CPK, b, full);
+          }
           if (load_b)
             bulk_g2s(b_base + (P.b_resident ? kb : s) * C::B_STAGE, P.w + (size_t)kb * 3 * (size_t)(KC * C::NP), C::B_STAGE, full);
           UB_TR(0, nbox, 2);
@@ -211,6 +369,8 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
         first = false;
       }
     }
+  } else if ((warp == 17 || warp == 18) && rank != 0) {
+    // CG2 peer: its tensor core is driven by the leader's instructions
   } else if (warp == 17 || warp == 18) {
     // ===================== MMA issuers (warps 17, 18) =====================
     // Two warps issue alternate M-tiles (tile parity = accumulator parity).  For a lone issuer the barrier waits and the
@@ -221,18 +381,19 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
     // divisions in here.
     {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) |
-                                 ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+                                 ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)((CG2 ? 256 : 128) >> 4) << 24);
       const int wi = warp - 17;
+      [[maybe_unused]] const uint32_t peer_empty = CG2 ? mapa_u32(bar_empty, 1) : 0;
       int it = 0;                                                 // counts M-tiles (accumulator uses)
       int s = 0; uint32_t ph = 0;
-      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x, it += P.mt) {
+      for (long long grp = blockIdx.x; grp - rank < P.total_items; grp += gridDim.x, it += P.mt) {
         for (int kb = 0; kb < P.kbn; ++kb) {
           if (lane == 0 && kb == 0) UB_TR(1, it + wi, 4);
           mbar_wait(bar_full + 8 * s, ph);
           tc_fence_after();
           if (lane == 0 && kb == 0) UB_TR(1, it + wi, 3);          // first box of the group landed
           const uint32_t a_st = a_base + s * P.a_stage;
-          const uint32_t b_st = b_base + (P.b_resident ? kb : s) * C::B_STAGE;
+          const uint32_t b_st = b_base + ((CG2 || P.b_resident) ? kb : s) * C::B_STAGE;
           bool mine = false;
           for (int m = 0; m < P.mt; ++m) {
             if (((it + m) & 1) != wi) continue;
@@ -253,19 +414,28 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
                   // A: M-tile m, tap row ky = box rows 4m+ky .. 4m+ky+3; rows 16 B apart, 8-row groups 128 B apart,
                   // the two K chunks a_chunk apart
                   const uint64_t ad = make_desc(a_st + 2 * k16 * P.a_chunk + (m * T_ROWS + ky) * SEG_BYTES, P.a_chunk, 128);
-                  const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NP * 16, C::NP * 16, 128);
-                  tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+                  const uint64_t bd = make_desc(b_st + ky * C::B_KY + 2 * k16 * C::NPH * 16, C::NPH * 16, 128);
+                  if (CG2) tc_mma_pair(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
+                  else tc_mma(d_tmem, ad, bd, IDESC, (kb | ky | k16) != 0);
                 }
               }
-              if (kb == P.kbn - 1) tc_commit(bar_tfull + 8 * buf);                           // accumulator of M-tile m complete
+              if (kb == P.kbn - 1) {                                                         // accumulator of M-tile m complete (in both CTAs)
+                if (CG2) tc_commit_pair(bar_tfull + 8 * buf, 3);
+                else tc_commit(bar_tfull + 8 * buf);
+              }
             }
             __syncwarp();
             if (lane == 0 && kb == P.kbn - 1) UB_TR(1, it + m, 2);
           }
           // hand the box back once this warp's MMAs have read it (plain arrive if it had no M-tile in this group)
           if (elect_one()) {
-            if (mine) tc_commit(bar_empty + 8 * s);
-            else mbar_arrive(bar_empty + 8 * s);
+            if (CG2) {
+              if (mine) tc_commit_pair(bar_empty + 8 * s, 3);
+              else { mbar_arrive(bar_empty + 8 * s); mbar_arrive_cluster(peer_empty + 8 * s); }
+            } else {
+              if (mine) tc_commit(bar_empty + 8 * s);
+              else mbar_arrive(bar_empty + 8 * s);
+            }
           }
           __syncwarp();
           if (++s == S) { s = 0; ph ^= 1; }
@@ -274,86 +444,10 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
     }
   } else if (UPS && warp >= 19) {
     // ===================== interpolation warps (UPS): A operand of the source-1 k-blocks =====================
-    // Warp = (chunk of the k-block, half of the box rows), lane = box column.  A thread walks down its rows exactly as
-    // k_upsample2 does: column terms once per group, every low-resolution row x-blended once, one y-blend per output.
     if constexpr (UPS) {
-      const int iw = warp - 19, cc = iw & 3, rhalf = iw >> 2;
-      const int R = T_ROWS * P.mt + 2, r_begin = rhalf * (R >> 1), r_end = r_begin + (R >> 1);
-      const int step_b = (int)gridDim.x / tiles_per_img, step_r = (int)gridDim.x - step_b * tiles_per_img;
-      const int step_y = step_r / P.tiles_x, step_x = step_r - step_y * P.tiles_x;
-      int b = (int)blockIdx.x / tiles_per_img, tgy, tx;
-      {
-        const int t = (int)blockIdx.x - b * tiles_per_img;
-        tgy = t / P.tiles_x; tx = t - tgy * P.tiles_x;
-      }
-      int s = 0; uint32_t ph = 0; int ls = 0; uint32_t lph = 0;
-      for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
-        const int xb = tx * T_VALID - 1, yb = tgy * T_ROWS * P.mt - 1;
-        const int xl0 = (int)(P.up_sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(P.up_sy * (float)(yb < 0 ? 0 : yb));
-        const int x = xb + lane;
-        const bool xin = x >= 0 && x < L.W;                      // outside: zero border (or never-consumed columns)
-        const float fx = P.up_sx * (float)(x < 0 ? 0 : (x >= L.W ? L.W - 1 : x));
-        const int x0 = (int)fx;
-        const float lx = fx - (float)x0;
-        const act2_t lx2 = f2a2(lx, lx);
-        const uint32_t col_off = (uint32_t)(x0 - xl0) * 16 + cc * P.low_chunk;
-        for (int kb = 0; kb < P.kbn; ++kb) {
-          if (kb >= P.kb0) {
-            mbar_wait(bar_lfull + 8 * ls, lph);                  // low-resolution patch landed
-            mbar_wait(bar_empty + 8 * s, ph ^ 1);                // the stage's previous MMAs have retired
-            const uint32_t lo = low_base + ls * P.low_stage + col_off;
-            const uint32_t dst = a_base + s * P.a_stage + cc * P.a_chunk + lane * 16;
-            act2_t top[4], bot[4];
-            auto blend_row = [&](int row, act2_t* r) {
-              uint32_t a0, a1, a2, a3, c0, c1, c2, c3;
-              ld_shared_v4(lo + row * (UP_LC * 16), a0, a1, a2, a3);
-              ld_shared_v4(lo + row * (UP_LC * 16) + 16, c0, c1, c2, c3);
-              const uint32_t av[4] = {a0, a1, a2, a3}, cv[4] = {c0, c1, c2, c3};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const act2_t ha = *reinterpret_cast<const act2_t*>(&av[j]), hc = *reinterpret_cast<const act2_t*>(&cv[j]);
-                r[j] = __hfma2(lx2, __hsub2(hc, ha), ha);
-              }
-            };
-            int cur = -2;
-            for (int r = r_begin; r < r_end; ++r) {
-              const int y = yb + r;
-              const bool yin = y >= 0 && y < L.H;
-              const float fy = P.up_sy * (float)(y < 0 ? 0 : (y >= L.H ? L.H - 1 : y));
-              const int y0 = (int)fy;
-              const float ly = fy - (float)y0;
-              const act2_t ly2 = f2a2(ly, ly);
-              if (y0 != cur) {
-                if (y0 == cur + 1) {
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) top[j] = bot[j];
-                } else {
-                  blend_row(y0 - yl0, top);
-                }
-                blend_row(y0 + 1 - yl0, bot);
-                cur = y0;
-              }
-              uint32_t o[4];
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const act2_t v = __hfma2(ly2, __hsub2(bot[j], top[j]), top[j]);
-                o[j] = (xin && yin) ? *reinterpret_cast<const uint32_t*>(&v) : 0u;
-              }
-              st_shared_v4(dst + r * SEG_BYTES, o[0], o[1], o[2], o[3]);
-            }
-            fence_proxy_async_smem();                            // generic-proxy writes -> visible to the tensor core's reads
-            named_bar_sync(UP_BAR, UP_WARPS * 32);
-            if (iw == 0 && lane == 0) { mbar_arrive(bar_full + 8 * s); mbar_arrive(bar_lempty + 8 * ls); }
-            if (++ls == P.low_slots) { ls = 0; lph ^= 1; }
-          }
-          if (++s == S) { s = 0; ph ^= 1; }
-        }
-        tx += step_x;
-        if (tx >= P.tiles_x) { tx -= P.tiles_x; ++tgy; }
-        tgy += step_y;
-        if (tgy >= P.tiles_y) { tgy -= P.tiles_y; ++b; }
-        b += step_b;
-      }
+      if (P.mt == 4) ups_warp<9, CG2>(P, warp - 19, lane, lead_full, bar_empty, bar_lfull, bar_lempty, a_base, low_base);
+      else if (P.mt == 2) ups_warp<5, CG2>(P, warp - 19, lane, lead_full, bar_empty, bar_lfull, bar_lempty, a_base, low_base);
+      else ups_warp<3, CG2>(P, warp - 19, lane, lead_full, bar_empty, bar_lfull, bar_lempty, a_base, low_base);
     }
   } else {
     // ===================== epilogue (warps 0-15) =====================
@@ -377,7 +471,8 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
     [[maybe_unused]] const uint32_t stage_mine = smem_u32(smem) + P.pool_smem + warp * 1024 + (lane >> 1) * 16;
     [[maybe_unused]] const uint32_t stage_peer = smem_u32(smem) + P.pool_smem + (warp ^ 1) * 1024 + (lane >> 1) * 16;
     int it = 0;
-    for (long long grp = blockIdx.x; grp < P.total_items; grp += gridDim.x) {
+    for (long long grp = blockIdx.x; grp - rank < P.total_items; grp += gridDim.x) {
+    if (CG2 && grp >= P.total_items) { b = P.B - 1; tgy = P.tiles_y - 1; tx = P.tiles_x - 1; }   // odd tail: the peer repeats the last group
     if (lane == 0 && wq == 0) UB_TR(2 + grp_w, it / C::NBUF, 4);
     const int x = tx * T_VALID - 1 + lane;
     const bool valid = lane >= 1 && lane <= T_VALID && x < L.W;
@@ -415,7 +510,9 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
         if (half == 1) {                                       // accumulator fully read: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(bar_tempty + 8 * my_buf);
+          if (lane == 0) {
+            if (CG2) mbar_arrive_cluster(lead_tempty + 8 * my_buf); else mbar_arrive(bar_tempty + 8 * my_buf);
+          }
           if (lane == 0 && wq == 0) UB_TR(2 + grp_w, use, 2);
         }
         uint32_t hv[8];
@@ -502,19 +599,21 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
 
   tc_fence_before();
   __syncthreads();
+  if (CG2) cluster_sync();                   // no CTA leaves (or frees its TMEM) while the pair's MMAs / remote arrivals may still touch it
   if (warp == 16) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+    if (CG2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
   }
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 
-template <int COUT, int KC, int NCLS, bool POOL = false, bool UPS = false>
-int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
-  using C = RCfg<COUT, KC>;
+template <int COUT, int KC, int NCLS, bool POOL, bool UPS, bool CG2>
+int launch_rows_cg(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
+  using C = RCfg<COUT, KC, CG2>;
   static_assert(!UPS || KC == 32, "fused upsample: the interpolation warps are laid out for four chunks per k-block");
-  auto kern = k_conv_rows<COUT, KC, NCLS, POOL, UPS>;
+  auto kern = k_conv_rows<COUT, KC, NCLS, POOL, UPS, CG2>;
   constexpr int LOW_SLOTS = 2;
   // UPS: room for the ring of low-resolution patches; a patch under a (4*mt+2)-row box has at most 2*mt+3 rows
   // (the source index advances by < 0.5 per output row), sized here for the largest mt
@@ -536,6 +635,7 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
     const int a_stage = C::CPK * (T_ROWS * cand + 2) * SEG_BYTES;
     int st_n;
     if (C::HDR + resident_bytes + 2 * a_stage <= BUDGET) { P.b_resident = 1; st_n = (BUDGET - C::HDR - resident_bytes) / a_stage; }
+    else if (CG2) continue;                                    // pair kernels keep their (half-size) weights resident
     else { P.b_resident = 0; st_n = (BUDGET - C::HDR) / (a_stage + C::B_STAGE); }
     if (st_n >= 2 || cand == 1) { mt = cand; stages = st_n; break; }
   }
@@ -562,18 +662,37 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   if (r != UB_OK) return r;
   if (POOL) { P.pool_smem = (smem + 1023) & ~1023; smem = P.pool_smem + POOL_SMEM; }
   long long grid = P.total_items < ctx->sm_count ? P.total_items : ctx->sm_count;
+  if (CG2) {
+    // clusters of two; an odd last group is computed by both CTAs of its pair (identical stores)
+    const long long pairs = (P.total_items + 1) / 2, max_pairs = ctx->sm_count / 2;
+    grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
+    P.w = Lr.w2; P.wbytes = resident_bytes;
+  }
 #ifdef UB_ROWS_TRACE
   static long long* d_trace = nullptr;
-  const size_t tr_bytes = sizeof(long long) * 6 * TR_N * 8;
+  const size_t tr_bytes = sizeof(long long) * 7 * TR_N * 8;
   if (!d_trace) UB_CUDA(ctx, cudaMalloc(&d_trace, tr_bytes));
   UB_CUDA(ctx, cudaMemsetAsync(d_trace, 0, tr_bytes, st));
   P.trace = d_trace;
 #endif
-  kern<<<(unsigned)grid, UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, smem, st>>>(P);
+  if (CG2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, P));
+  } else {
+    kern<<<(unsigned)grid, UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, smem, st>>>(P);
+  }
   UB_CHECK_LAUNCH(ctx);
 #ifdef UB_ROWS_TRACE
   if (const char* dir = getenv("UB_ROWS_TRACE_DIR")) {
-    std::vector<long long> h(6 * TR_N * 8);
+    std::vector<long long> h(7 * TR_N * 8);
     UB_CUDA(ctx, cudaStreamSynchronize(st));
     UB_CUDA(ctx, cudaMemcpy(h.data(), d_trace, tr_bytes, cudaMemcpyDeviceToHost));
     char path[512];
@@ -587,6 +706,21 @@ int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& 
   }
 #endif
   return UB_OK;
+}
+
+// CTA pairs (cta_group::2 MMAs) unless UB_ROWS_PAIR=0; init registers both instantiations
+bool rows_pair_enabled() {
+  static const bool on = !(getenv("UB_ROWS_PAIR") && atoi(getenv("UB_ROWS_PAIR")) == 0);
+  return on;
+}
+template <int COUT, int KC, int NCLS, bool POOL = false, bool UPS = false>
+int launch_rows(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
+  if (init_only) {
+    int r = launch_rows_cg<COUT, KC, NCLS, POOL, UPS, false>(ctx, P, a, Lr, st, true);
+    return r != UB_OK ? r : launch_rows_cg<COUT, KC, NCLS, POOL, UPS, true>(ctx, P, a, Lr, st, true);
+  }
+  if (rows_pair_enabled() && Lr.w2 && ctx->sm_count >= 2) return launch_rows_cg<COUT, KC, NCLS, POOL, UPS, true>(ctx, P, a, Lr, st, false);
+  return launch_rows_cg<COUT, KC, NCLS, POOL, UPS, false>(ctx, P, a, Lr, st, false);
 }
 
 int dispatch_rows(ub_ctx* ctx, int cout, int kc, RowsParams& P, const ConvArgs& a, const ConvLayer& Lr, cudaStream_t st, bool init_only) {
