@@ -14,7 +14,7 @@ def med(x):
 def report(path):
     raw = np.fromfile(path, dtype=np.int64)
     cout, kc, ncls, kbn, mt, stages, items, grid = raw[:8]
-    t = raw[8:].reshape(7, TR_N, 8)
+    t = raw[8:].reshape(8, TR_N, 8)
     groups = (items + grid - 1) // grid
     tiles = min(int(groups * mt), TR_N)
     boxes = min(int(groups * kbn), TR_N)
@@ -60,6 +60,14 @@ def report(path):
         print(f"  interp warp 0: wait-low {med(u[:, 1] - u[:, 0]):.0f} (mean {(u[:, 1] - u[:, 0]).mean():.0f})  wait-empty {med(u[:, 2] - u[:, 1]):.0f} "
               f"(mean {(u[:, 2] - u[:, 1]).mean():.0f})  interpolate+store {med(u[:, 3] - u[:, 2]):.0f} (mean {(u[:, 3] - u[:, 2]).mean():.0f})  "
               f"stage period {med(np.diff(u[:, 3])):.0f} (mean {np.diff(u[:, 3]).mean():.0f})")
+    lo = t[7]
+    nl = int((lo[:, 1] > 0).sum())
+    if nl > 8 and nu > 4:
+        # interpolation warp 0 belongs to team 0 = even low boxes
+        k = min(nl // 2, int((t[6][:, 3] > 0).sum())) - 2
+        iss = lo[0:2 * k:2, 1][2:]; land = t[6][:k, 1][2:]; start = t[6][:k, 0][2:]
+        print(f"  low box (team 0): producer wait-lempty {med(lo[2:nl, 1] - lo[2:nl, 0]):.0f}  issue -> landed-seen {med(land - iss):.0f} (mean {(land - iss).mean():.0f})  "
+              f"issue relative to the team reaching its wait {med(iss - start):.0f}")
     # latency from MMA commit to epilogue start, from epilogue arrive to MMA resume
     if cout != 64:
         for g in range(1):

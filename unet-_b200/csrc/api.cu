@@ -239,6 +239,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     }
     UB_CUDA(ctx, cudaMemcpy(L.w, wp.data(), wp.size() * sizeof(act_t), cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+    for (int i = 0; i < 64 && i < d.cout; ++i) L.bias_host[i] = bias[i];
   }
   const float *hw, *hb;
   RUN(get("final.weight", (int64_t)ctx->num_classes * 32, &hw));

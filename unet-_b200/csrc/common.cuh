@@ -91,6 +91,7 @@ struct ConvLayer {
   // [half][kblock][ky][kc/8][N'/2][8] (each CTA of a pair holds one half, contiguous)
   act_t* w2 = nullptr;
   float* bias = nullptr;
+  float bias_host[64] = {0};   // host mirror of the first 64 biases (conv_rows passes them as kernel parameters)
 };
 
 // ---------------------------------------------------------------------------------

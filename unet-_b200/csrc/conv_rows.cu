@@ -54,8 +54,10 @@ struct RowsParams {
   float up_sy, up_sx; int low_rows, low_chunk, low_stage, low_slots, low_off;
   int wbytes;                                  // CG2 kernels: bytes of this CTA's half of the weights (all k-blocks, resident)
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
+  float biasv[64];                             // folded BN bias per output channel: read through the constant bank (the
+                                               // shared-memory pipe is what bounds these kernels, profiles/r02_conv.md)
 #ifdef UB_ROWS_TRACE
-  long long* trace;                            // [7 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
+  long long* trace;                            // [8 roles][TR_N][8] clock64 stamps of block 0 (tools/rows_trace.py)
 #endif
 };
 
@@ -114,19 +116,22 @@ __device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
   return r;
 }
 
-// Interpolation warp of a UPS kernel.  Warp = (chunk of the k-block, half of the box rows), lane = box column; NR = rows
-// per warp = 2*mt+1.  The arithmetic is k_upsample2's: source index = dst * (in-1)/(out-1) in fp32, x-blend of every
-// low-resolution row once, one y-blend per output, all as packed 16-bit a + l*(c-a).  Per group a thread sets up its
-// column terms and a row table (low-resolution row offset, packed y weight) in registers; a stage is then NR
-// iterations of {0-2 row loads + x-blends, one y-blend, one 16-byte store}.  Each warp arrives on the stage's barriers
-// by itself (full / lempty count UP_WARPS arrivals), so the eight warps never wait for one another.
+// Interpolation warp of a UPS kernel.  The eight warps form two teams that take alternate source-1 stages (so two stages
+// are interpolated concurrently); inside a team a warp = (pair of chunks of the k-block, half of the box rows), lane = box
+// column, NR = rows per warp = 2*mt+1.  A thread runs the two chunks as two independent dependency chains (the walk is
+// latency-bound: load -> x-blend -> y-blend -> store).  The arithmetic is k_upsample2's: source index =
+// dst * (in-1)/(out-1) in fp32, x-blend of every low-resolution row once, one y-blend per output, all as packed 16-bit
+// a + l*(c-a).  Per group a thread sets up its column terms and a row table (low-resolution row offset, packed y weight)
+// in registers.  Each warp arrives on the stage's barriers by itself (full / lempty count UP_TEAM arrivals per CTA).
+constexpr int UP_TEAM = UP_WARPS / 2;     // warps per team = arrivals per stage and CTA
 template <int NR, bool CG2>
 __device__ __forceinline__ void ups_warp(const RowsParams& P, const int iw, const int lane, const uint32_t bar_full,
                                          const uint32_t bar_empty, const uint32_t bar_lfull, const uint32_t bar_lempty,
                                          const uint32_t a_base, const uint32_t low_base) {
-  const int cc = iw & 3, r_begin = (iw >> 2) * NR;
+  const int team = iw >> 2, cp = iw & 1, r_begin = ((iw >> 1) & 1) * NR;   // chunks 2*cp, 2*cp+1
   const int S = P.num_stages, LS = P.low_slots, kb0 = P.kb0, kbn = P.kbn, W = P.L.W, H = P.L.H, mtr = T_ROWS * P.mt;
   const int a_stage = P.a_stage, low_stage = P.low_stage, tiles_x = P.tiles_x, tiles_y = P.tiles_y;
+  const uint32_t a_chunk = P.a_chunk, low_chunk = P.low_chunk;
   const float sx = P.up_sx, sy = P.up_sy;
   const long long total = P.total_items;
   const int tiles_per_img = tiles_x * tiles_y;
@@ -137,10 +142,10 @@ __device__ __forceinline__ void ups_warp(const RowsParams& P, const int iw, cons
     const int t = (int)blockIdx.x % tiles_per_img;
     tgy = t / tiles_x; tx = t - tgy * tiles_x;
   }
-  const uint32_t dst0 = a_base + cc * P.a_chunk + lane * 16 + r_begin * SEG_BYTES;
-  const uint32_t lo0 = low_base + cc * P.low_chunk;
+  const uint32_t dst0 = a_base + 2 * cp * a_chunk + lane * 16 + r_begin * SEG_BYTES;
+  const uint32_t lo0 = low_base + 2 * cp * low_chunk;
   int s = 0; uint32_t ph = 0; int ls = 0; uint32_t lph = 0;
-  [[maybe_unused]] int nst = 0;
+  int nst = 0;                                                  // source-1 stages seen so far (team = parity)
   const long long rank = CG2 ? (long long)cluster_ctarank() : 0;
   for (long long grp = blockIdx.x; grp - rank < total; grp += gridDim.x) {
     if (CG2 && grp >= total) { tx = tiles_x - 1; tgy = tiles_y - 1; }       // odd tail: the peer repeats the last group
@@ -166,52 +171,65 @@ __device__ __forceinline__ void ups_warp(const RowsParams& P, const int iw, cons
     }
     for (int kb = 0; kb < kbn; ++kb) {
       if (kb >= kb0) {
-        if (iw == 0 && lane == 0) UB_TR(6, nst, 0);
-        mbar_wait_sleep(bar_lfull + 8 * ls, lph);                // low-resolution patch landed
-        if (iw == 0 && lane == 0) UB_TR(6, nst, 1);
-        mbar_wait_sleep(bar_empty + 8 * s, ph ^ 1);              // the stage's previous MMAs have retired
-        if (iw == 0 && lane == 0) UB_TR(6, nst, 2);
-        const uint32_t lo = lo_col + ls * low_stage, dst = dst0 + s * a_stage;
-        act2_t top[4], bot[4];
-        auto blend_row = [&](uint32_t addr, act2_t* r) {
-          uint32_t av[4], cv[4];
-          lds_v4(addr, av[0], av[1], av[2], av[3]);
-          lds_v4(addr + 16, cv[0], cv[1], cv[2], cv[3]);
+        if ((nst & 1) == team) {
+          if (iw == 0 && lane == 0) UB_TR(6, nst >> 1, 0);
+          mbar_wait_sleep(bar_lfull + 8 * ls, lph);              // low-resolution patch landed
+          if (iw == 0 && lane == 0) UB_TR(6, nst >> 1, 1);
+          mbar_wait_sleep(bar_empty + 8 * s, ph ^ 1);            // the stage's previous MMAs have retired
+          if (iw == 0 && lane == 0) UB_TR(6, nst >> 1, 2);
+          const uint32_t lo = lo_col + ls * low_stage, dst = dst0 + s * a_stage;
+          act2_t top[2][4], bot[2][4];
+          auto blend_row = [&](uint32_t addr, act2_t (*r)[4]) {  // both chunks of this thread: r[0], r[1]
+            uint32_t av[2][4], cv[2][4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const act2_t ha = *reinterpret_cast<const act2_t*>(&av[j]), hc = *reinterpret_cast<const act2_t*>(&cv[j]);
-            r[j] = __hfma2(lx2, __hsub2(hc, ha), ha);
-          }
-        };
-        int cur = -(1 << 20);
-#pragma unroll
-        for (int i = 0; i < NR; ++i) {
-          if (roff[i] != cur) {                                  // warp-uniform
-            if (roff[i] == cur + UP_LC * 16) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) top[j] = bot[j];
-            } else {
-              blend_row(lo + roff[i], top);
+            for (int c = 0; c < 2; ++c) {
+              lds_v4(addr + c * low_chunk, av[c][0], av[c][1], av[c][2], av[c][3]);
+              lds_v4(addr + c * low_chunk + 16, cv[c][0], cv[c][1], cv[c][2], cv[c][3]);
             }
-            blend_row(lo + roff[i] + UP_LC * 16, bot);
-            cur = roff[i];
-          }
-          const act2_t ly2 = *reinterpret_cast<const act2_t*>(&lyp[i]);
-          uint32_t o[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const act2_t v = __hfma2(ly2, __hsub2(bot[j], top[j]), top[j]);
-            o[j] = (ok >> i) & 1u ? *reinterpret_cast<const uint32_t*>(&v) : 0u;
+            for (int c = 0; c < 2; ++c)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const act2_t ha = *reinterpret_cast<const act2_t*>(&av[c][j]), hc = *reinterpret_cast<const act2_t*>(&cv[c][j]);
+                r[c][j] = __hfma2(lx2, __hsub2(hc, ha), ha);
+              }
+          };
+          int cur = -(1 << 20);
+#pragma unroll
+          for (int i = 0; i < NR; ++i) {
+            if (roff[i] != cur) {                                // warp-uniform
+              if (roff[i] == cur + UP_LC * 16) {
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) top[c][j] = bot[c][j];
+              } else {
+                blend_row(lo + roff[i], top);
+              }
+              blend_row(lo + roff[i] + UP_LC * 16, bot);
+              cur = roff[i];
+            }
+            const act2_t ly2 = *reinterpret_cast<const act2_t*>(&lyp[i]);
+            const bool keep = (ok >> i) & 1u;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              uint32_t o[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const act2_t v = __hfma2(ly2, __hsub2(bot[c][j], top[c][j]), top[c][j]);
+                o[j] = keep ? *reinterpret_cast<const uint32_t*>(&v) : 0u;
+              }
+              sts_v4(dst + c * a_chunk + i * SEG_BYTES, o[0], o[1], o[2], o[3]);
+            }
           }
-          sts_v4(dst + i * SEG_BYTES, o[0], o[1], o[2], o[3]);
+          fence_proxy_async_smem();                              // generic-proxy writes -> visible to the tensor core's reads
+          __syncwarp();
+          if (lane == 0) {                                       // CG2: bar_full is the leader CTA's barrier (shared::cluster address)
+            if (CG2) mbar_arrive_cluster(bar_full + 8 * s); else mbar_arrive(bar_full + 8 * s);
+            mbar_arrive(bar_lempty + 8 * ls);
+          }
+          if (iw == 0 && lane == 0) UB_TR(6, nst >> 1, 3);
         }
-        if (CG2) fence_proxy_async_all(); else fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's reads
-        __syncwarp();
-        if (lane == 0) {                                         // CG2: bar_full is the leader CTA's barrier (shared::cluster address)
-          if (CG2) mbar_arrive_cluster(bar_full + 8 * s); else mbar_arrive(bar_full + 8 * s);
-          mbar_arrive(bar_lempty + 8 * ls);
-        }
-        if (iw == 0 && lane == 0) UB_TR(6, nst, 3);
         ++nst;
         if (++ls == LS) { ls = 0; lph ^= 1; }
       }
@@ -266,7 +284,6 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 8));
   [[maybe_unused]] const uint32_t bar_lfull = smem_u32(smem) + 256, bar_lempty = bar_lfull + 64;   // UPS: low-resolution ring
   [[maybe_unused]] const uint32_t low_base = smem_u32(smem) + P.low_off;
-  float* s_bias = reinterpret_cast<float*>(smem + 512);        // [COUT] (<= 64 floats)
   const uint32_t a_base = smem_u32(smem) + C::HDR;
   const uint32_t b_base = a_base + S * P.a_stage;
   const PPLayout& L = P.L;
@@ -276,13 +293,12 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
   const uint32_t bar_w = smem_u32(smem) + 384;                 // CG2: this CTA's resident weights have landed
   if (threadIdx.x == 0) {
     // CG2: the leader's full / tempty barriers also count the peer's interpolation / epilogue warps
-    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, UPS ? NCTA * UP_WARPS : 1); mbar_init(bar_empty + 8 * i, 2); }
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, UPS ? NCTA * UP_TEAM : 1); mbar_init(bar_empty + 8 * i, 2); }
     for (int i = 0; i < C::NBUF; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, NCTA * C::WARPS_PER_BUF); }
-    if (UPS) for (int i = 0; i < P.low_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, UP_WARPS); }
+    if (UPS) for (int i = 0; i < P.low_slots; ++i) { mbar_init(bar_lfull + 8 * i, 1); mbar_init(bar_lempty + 8 * i, UP_TEAM); }
     if (CG2) mbar_init(bar_w, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (threadIdx.x < COUT) s_bias[threadIdx.x] = P.bias[threadIdx.x];
   if (warp == 16) {
     if (CG2) {
       asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
@@ -317,7 +333,32 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
       tma_prefetch_desc(&P.tm1);
       int s = 0; uint32_t ph = 0; bool first = true;
       [[maybe_unused]] int ls = 0; [[maybe_unused]] uint32_t lph = 0;
-      [[maybe_unused]] int nbox = 0;
+      [[maybe_unused]] int nbox = 0, nlow = 0;
+      // UPS: the ring of low-resolution patches has its own cursor and runs ahead of the stage ring (a box needs ~2000 clk
+      // from issue to landing, profiles/r02_conv.md): a patch is requested as soon as a ring slot is free, not when the
+      // in-order walk over the stages reaches its k-block.
+      [[maybe_unused]] long long lgrp = blockIdx.x, low_issued = 0, low_needed = 0;
+      [[maybe_unused]] int lkb = P.kb0;
+      [[maybe_unused]] auto issue_low = [&](bool blocking) -> bool {
+        if (lgrp - rank >= P.total_items) return false;
+        UB_TR(7, nlow, 0);
+        if (blocking) mbar_wait(bar_lempty + 8 * ls, lph ^ 1);
+        else if (!mbar_test(bar_lempty + 8 * ls, lph ^ 1)) return false;
+        UB_TR(7, nlow, 1);
+        ++nlow;
+        const long long g = lgrp < P.total_items ? lgrp : P.total_items - 1;
+        const int b = (int)(g / tiles_per_img), t = (int)(g - (long long)b * tiles_per_img);
+        const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
+        // rows yl0.., columns xl0.. of the half-size image (padded coordinates +1) lie under the box
+        const int xb = tx * T_VALID - 1, yb = ty * T_ROWS * P.mt - 1;
+        const int xl0 = (int)(P.up_sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(P.up_sy * (float)(yb < 0 ? 0 : yb));
+        mbar_expect_tx(bar_lfull + 8 * ls, P.low_stage);
+        tma_load_4d(low_base + ls * P.low_stage, &P.tm1, (xl0 + 1) * 8, yl0 + 1, (lkb - P.kb0) * C::CPK, b, bar_lfull + 8 * ls);
+        if (++ls == P.low_slots) { ls = 0; lph ^= 1; }
+        if (++lkb == P.kbn) { lkb = P.kb0; lgrp += gridDim.x; }
+        ++low_issued;
+        return true;
+      };
       for (long long grp0 = blockIdx.x; grp0 - rank < P.total_items; grp0 += gridDim.x) {
         const long long grp = grp0 < P.total_items ? grp0 : P.total_items - 1;    // CG2 odd tail: the peer repeats the last group
         const int b = (int)(grp / tiles_per_img), t = (int)(grp - (long long)b * tiles_per_img);
@@ -326,13 +367,9 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
         for (int kb = 0; kb < P.kbn; ++kb) {
           const uint32_t full = bar_full + 8 * s;
           if (UPS && kb >= P.kb0) {
-            // low-resolution patch under the box: rows yl0.., columns xl0.. of the half-size image (padded coordinates +1)
-            const int xb = tx * T_VALID - 1, yb = ty * T_ROWS * P.mt - 1;
-            const int xl0 = (int)(P.up_sx * (float)(xb < 0 ? 0 : xb)), yl0 = (int)(P.up_sy * (float)(yb < 0 ? 0 : yb));
-            mbar_wait(bar_lempty + 8 * ls, lph ^ 1);
-            mbar_expect_tx(bar_lfull + 8 * ls, P.low_stage);
-            tma_load_4d(low_base + ls * P.low_stage, &P.tm1, (xl0 + 1) * 8, yl0 + 1, (kb - P.kb0) * C::CPK, b, bar_lfull + 8 * ls);
-            if (++ls == P.low_slots) { ls = 0; lph ^= 1; }
+            while (issue_low(false)) { }
+            if (low_issued <= low_needed) issue_low(true);       // normally the ring is already ahead of the stages
+            ++low_needed;
             if (load_b) {                                      // weights of this k-block ride on the stage's `full` barrier
               mbar_wait(bar_empty + 8 * s, ph ^ 1);            // (its previous phase is over once the slot has been released)
               mbar_expect_tx_only(full, C::B_STAGE);
@@ -342,21 +379,22 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
             continue;
           }
           UB_TR(0, nbox, 0);
-          mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          if (UPS) { while (!mbar_test(bar_empty + 8 * s, ph ^ 1)) issue_low(false); }
+          else mbar_wait(bar_empty + 8 * s, ph ^ 1);
           UB_TR(0, nbox, 1);
           // box origin: padded row 4*mt*ty (= image row y0-1), padded column 30*tx (= image column x0-1)
           if constexpr (CG2) {
             // both CTAs' boxes complete on the leader's barrier; the leader expects the bytes of both
             if (rank == 0) {
               mbar_expect_tx(full, 2 * P.a_stage);
-              if (UPS) mbar_arrive_n(full, 2 * UP_WARPS - 1);
+              if (UPS) mbar_arrive_n(full, 2 * UP_TEAM - 1);
             }
             const CUtensorMap* tm = kb < P.kb0 ? &P.tm0 : &P.tm1;
             tma_load_4d_pair(a_base + s * P.a_stage, tm, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb < P.kb0 ? kb : kb - P.kb0) * C::CPK, b,
                              lead_full + 8 * s);
           } else {
           mbar_expect_tx(full, P.a_stage + (load_b ? C::B_STAGE : 0));
-          if (UPS) mbar_arrive_n(full, UP_WARPS - 1);            // UPS kernels: `full` counts the eight interpolation warps
+          if (UPS) mbar_arrive_n(full, UP_TEAM - 1);             // UPS kernels: `full` counts the four warps of an interpolation team
           if (kb < P.kb0) tma_load_4d(a_base + s * P.a_stage, &P.tm0, tx * T_VALID * 8, ty * T_ROWS * P.mt, kb * C::CPK, b, full);
           else tma_load_4d(a_base + s * P.a_stage, &P.tm1, tx * T_VALID * 8, ty * T_ROWS * P.mt, (kb - P.kb0) * C::CPK, b, full);
           }
@@ -520,7 +558,7 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
         for (int j = 0; j < 16; j += 2) {
           const uint32_t l0 = __shfl_up_sync(0xffffffffu, k0[j], 1), l1 = __shfl_up_sync(0xffffffffu, k0[j + 1], 1);
           const uint32_t r0 = __shfl_down_sync(0xffffffffu, k2[j], 1), r1 = __shfl_down_sync(0xffffffffu, k2[j + 1], 1);
-          const float2 bb = *reinterpret_cast<const float2*>(s_bias + c0 + j);
+          const float2 bb = make_float2(P.biasv[c0 + j], P.biasv[c0 + j + 1]);
           uint64_t v = add2(pack2(l0, l1), pack2(k1[j], k1[j + 1]));
           v = add2(v, pack2(r0, r1));
           v = add2(v, pack2(__float_as_uint(bb.x), __float_as_uint(bb.y)));
@@ -614,7 +652,7 @@ int launch_rows_cg(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLaye
   using C = RCfg<COUT, KC, CG2>;
   static_assert(!UPS || KC == 32, "fused upsample: the interpolation warps are laid out for four chunks per k-block");
   auto kern = k_conv_rows<COUT, KC, NCLS, POOL, UPS, CG2>;
-  constexpr int LOW_SLOTS = 2;
+  constexpr int LOW_SLOTS = CG2 ? 4 : 2;      // pair kernels hold half the weights: room for a deeper ring
   // UPS: room for the ring of low-resolution patches; a patch under a (4*mt+2)-row box has at most 2*mt+3 rows
   // (the source index advances by < 0.5 per output row), sized here for the largest mt
   constexpr int BUDGET = SMEM_BUDGET - (POOL ? POOL_SMEM : 0) - (UPS ? LOW_SLOTS * C::CPK * (2 * C::NBUF + 3) * UP_LC * 16 : 0);
@@ -670,7 +708,7 @@ int launch_rows_cg(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLaye
   }
 #ifdef UB_ROWS_TRACE
   static long long* d_trace = nullptr;
-  const size_t tr_bytes = sizeof(long long) * 7 * TR_N * 8;
+  const size_t tr_bytes = sizeof(long long) * 8 * TR_N * 8;
   if (!d_trace) UB_CUDA(ctx, cudaMalloc(&d_trace, tr_bytes));
   UB_CUDA(ctx, cudaMemsetAsync(d_trace, 0, tr_bytes, st));
   P.trace = d_trace;
@@ -692,7 +730,7 @@ int launch_rows_cg(ub_ctx* ctx, RowsParams& P, const ConvArgs& a, const ConvLaye
   UB_CHECK_LAUNCH(ctx);
 #ifdef UB_ROWS_TRACE
   if (const char* dir = getenv("UB_ROWS_TRACE_DIR")) {
-    std::vector<long long> h(7 * TR_N * 8);
+    std::vector<long long> h(8 * TR_N * 8);
     UB_CUDA(ctx, cudaStreamSynchronize(st));
     UB_CUDA(ctx, cudaMemcpy(h.data(), d_trace, tr_bytes, cudaMemcpyDeviceToHost));
     char path[512];
@@ -776,6 +814,7 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
   if (a.H % T_ROWS) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: H=%d must be a multiple of %d", a.H, T_ROWS);
   RowsParams P{};
   P.out = a.out; P.w = Lr.w; P.bias = Lr.bias;
+  memcpy(P.biasv, Lr.bias_host, sizeof(float) * (size_t)(Lr.cout < 64 ? Lr.cout : 64));
   P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
   P.L = pp_layout(a.H, a.W);
   P.tiles_x = cdiv(a.W, T_VALID);
