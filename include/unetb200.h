@@ -213,6 +213,22 @@ int ub_pipeline_submit(ub_ctx* ctx, const uint8_t* frames_bgr_host, int B, int v
                        const ub_roi* roi, const ub_burr_params* params, int32_t* frame_stats_host, int slot);
 int ub_pipeline_wait(ub_ctx* ctx, int slot);
 
+/* ub_pipeline_submit for a loop whose frames arrive at the SOURCE resolution (infer_two_stage_burr.py:270-280,
+ * infer_enhanced_burr.py:273-276): src u8 [B,src_h,src_w,3] on the host is copied to the device on the copy stream,
+ * rotated 90 degrees counter-clockwise (rotate != 0) and resized to the context's frame size on the device, then the step
+ * runs as in ub_pipeline_submit.  Wait with ub_pipeline_wait(slot). */
+int ub_pipeline_submit_src(ub_ctx* ctx, const uint8_t* src_bgr_host, int B, int src_h, int src_w, int rotate, int variant,
+                           const ub_roi* roi, const ub_burr_params* params, int32_t* frame_stats_host, int slot);
+
+/* ---- run-time switches and counters ------------------------------------------------- */
+/* name = "overlap" (1: gray / edge map on a second stream beside the network, default), "check_saturation" (1: every conv
+ * epilogue counts the outputs it clamps to the largest finite 16-bit value; 0: off.  ub_set_weights arms the check for the
+ * first forward after it, so a checkpoint loaded through infer_two_stage_burr.py:214-217 whose activations overflow the
+ * operand type is reported once at no steady-state cost). */
+int ub_set_option(ub_ctx* ctx, const char* name, int value);
+/* name = "saturated": outputs clamped so far while the check was on (synchronises the device); reset != 0 zeroes it. */
+int ub_get_stat(ub_ctx* ctx, const char* name, int64_t* value, int reset);
+
 /* ---- test hooks (layer-level parity checks; not used by the product path) ------------ */
 /* Runs conv layer `layer` (0..17 in network order; BN folded, ReLU) on NCHW fp32 inputs:
  * x0 [B,cin0,H,W] (layer 0: 3 channels), x1 [B,cin1,H,W] or NULL -> out [B,cout,H,W]. */

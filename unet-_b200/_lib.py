@@ -78,6 +78,9 @@ SIGNATURES = {
     "ub_pipeline_host": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P]),
     "ub_pipeline_submit": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _I]),
     "ub_pipeline_wait": (_I, [_P, _I]),
+    "ub_pipeline_submit_src": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _I]),
+    "ub_set_option": (_I, [_P, C.c_char_p, _I]),
+    "ub_get_stat": (_I, [_P, C.c_char_p, C.POINTER(C.c_int64), _I]),
     "ub_debug_conv": (_I, [_P, _I, _P, _P, _I, _I, _I, _P, _P]),
     "ub_debug_conv_up": (_I, [_P, _I, _P, _P, _I, _I, _I, _I, _P, _P]),
     "ub_debug_activation": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
@@ -386,6 +389,21 @@ class Context:
         r = C.byref(Roi(*roi)) if roi is not None else None
         p = C.byref(params) if params is not None else None
         self._check(lib().ub_pipeline_submit(self._h, _ptr(frames), frames.shape[0], variant, r, p, _ptr(stats_out), slot))
+
+    def pipeline_submit_src(self, src, stats_out, slot, rotate, variant=VARIANT_STANDARD, roi=None, params=None):
+        """pipeline_submit for frames at the source resolution: src pinned uint8 [b,sh,sw,3]; rotate + resize run on the device."""
+        r = C.byref(Roi(*roi)) if roi is not None else None
+        p = C.byref(params) if params is not None else None
+        b, sh, sw, _ = src.shape
+        self._check(lib().ub_pipeline_submit_src(self._h, _ptr(src), b, sh, sw, int(rotate), variant, r, p, _ptr(stats_out), slot))
+
+    def set_option(self, name: str, value: int):
+        self._check(lib().ub_set_option(self._h, name.encode(), int(value)))
+
+    def get_stat(self, name: str, reset=False) -> int:
+        v = C.c_int64(0)
+        self._check(lib().ub_get_stat(self._h, name.encode(), C.byref(v), int(reset)))
+        return int(v.value)
 
     def pipeline_wait(self, slot):
         self._check(lib().ub_pipeline_wait(self._h, slot))

@@ -55,6 +55,12 @@ int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cu
 
 // ---------------------------------------------------------------- layer tables
 namespace {
+// keeps the caller's current device across an entry point that has to switch to the context's
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 struct LayerDef { const char* block; int idx; int cin0, cin1, cout, kc, bn; int real_cin0; int fold; };
 // cin0 of the first layer is the 3 input channels zero-padded to 16 (one UMMA K step)
 const LayerDef kLayers[18] = {
@@ -102,9 +108,10 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   if (prop.major != 10)
     return ub_fail(nullptr, UB_ERR_ARCH, "device %d is sm_%d%d; libunetb200 is built for sm_100a only (no fallback path)",
                    device, prop.major, prop.minor);
-  e = cudaSetDevice(device);
-  if (e != cudaSuccess) return ub_fail(nullptr, UB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+  DeviceGuard guard(device);
+  if ((e = cudaGetLastError()) != cudaSuccess) return ub_fail(nullptr, UB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
   ub_ctx* c = new ub_ctx();
+  if (const char* ov = getenv("UB_OVERLAP")) c->overlap = atoi(ov);
   c->device = device; c->sm_count = prop.multiProcessorCount;
   c->max_batch = max_batch; c->frame_h = frame_h; c->frame_w = frame_w; c->net_h = net_h; c->net_w = net_w;
   c->num_classes = num_classes;
@@ -122,7 +129,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   if ((r = dmalloc(c, &c->d_frames, fpix * 3)) || (r = dmalloc(c, &c->d_gray, fpix)) || (r = dmalloc(c, &c->d_pred, npix)) ||
       (r = dmalloc(c, &c->d_lab[0], ipl)) || (r = dmalloc(c, &c->d_lab[1], ipl)) || (r = dmalloc(c, &c->d_comp, fpix * 6)) ||
       (r = dmalloc(c, &c->d_counts, (size_t)max_batch * 16)) || (r = dmalloc(c, &c->d_stats, (size_t)max_batch * 8)) ||
-      (r = dmalloc(c, &c->d_logits, npix * num_classes)))
+      (r = dmalloc(c, &c->d_logits, npix * num_classes)) || (r = dmalloc(c, &c->d_sat, 1)))
     return fail(r);
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
@@ -144,8 +151,9 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
 
 void ub_destroy(ub_ctx* c) {
   if (!c) return;
-  cudaSetDevice(c->device);
+  DeviceGuard guard(c->device);
   cudaDeviceSynchronize();
+  cudaFree(c->d_src[0]); cudaFree(c->d_src[1]); cudaFree(c->d_sat);
   for (auto& p : c->act) cudaFree(p);
   for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.w2); cudaFree(L.bias); }
   cudaFree(c->head_w); cudaFree(c->head_b);
@@ -179,7 +187,7 @@ int ub_set_conv_impl(ub_ctx* ctx, int impl) {
 int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
   NEED_CTX(ctx);
   if (!t || n <= 0) return ub_fail(ctx, UB_ERR_ARG, "no tensors");
-  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard guard(ctx->device);
   std::map<std::string, const ub_named_tensor*> m;
   for (int i = 0; i < n; ++i) if (t[i].name) m[t[i].name] = &t[i];
   auto get = [&](const std::string& name, int64_t numel, const float** out) -> int {
@@ -251,6 +259,29 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
   memcpy(ctx->head_host, hw, sizeof(float) * ctx->num_classes * 32);
   memcpy(ctx->head_host + ctx->num_classes * 32, hb, sizeof(float) * ctx->num_classes);
   ctx->weights_set = true;
+  ctx->sat_check_once = 1;            // the first forward with these weights counts saturated outputs
+  return UB_OK;
+}
+
+int ub_set_option(ub_ctx* ctx, const char* name, int value) {
+  NEED_CTX(ctx);
+  if (!name) return ub_fail(ctx, UB_ERR_ARG, "null option name");
+  if (!strcmp(name, "overlap")) ctx->overlap = value != 0;
+  else if (!strcmp(name, "check_saturation")) { ctx->sat_check = value != 0; if (!value) ctx->sat_check_once = 0; }
+  else return ub_fail(ctx, UB_ERR_ARG, "unknown option \"%s\"", name);
+  return UB_OK;
+}
+
+int ub_get_stat(ub_ctx* ctx, const char* name, int64_t* value, int reset) {
+  NEED_CTX(ctx);
+  if (!name || !value) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (strcmp(name, "saturated")) return ub_fail(ctx, UB_ERR_ARG, "unknown statistic \"%s\"", name);
+  DeviceGuard guard(ctx->device);
+  unsigned long long v = 0;
+  UB_CUDA(ctx, cudaDeviceSynchronize());
+  UB_CUDA(ctx, cudaMemcpy(&v, ctx->d_sat, sizeof v, cudaMemcpyDeviceToHost));
+  if (reset) UB_CUDA(ctx, cudaMemset(ctx->d_sat, 0, sizeof v));
+  *value = (int64_t)v;
   return UB_OK;
 }
 
@@ -478,7 +509,7 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
   uint8_t *cable = ctx->d_mask[0], *tape = ctx->d_mask[1], *burr = ctx->d_mask[2];
   // The gray frame and the edge map depend on the frames only: they run on a second stream beside the network
   // (fork / join with events; the integer kernels fill the SMs the tensor-core kernels leave idle at their tails).
-  static const int overlap_env = getenv("UB_OVERLAP") ? atoi(getenv("UB_OVERLAP")) : 1;
+  const int overlap_env = ctx->overlap;
   cudaStream_t sa = overlap_env ? ctx->aux_stream : st;
   if (overlap_env) {
     UB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
@@ -547,6 +578,42 @@ int ub_pipeline_submit(ub_ctx* ctx, const uint8_t* frames_host, int B, int varia
   return UB_OK;
 }
 
+int ub_pipeline_submit_src(ub_ctx* ctx, const uint8_t* src_host, int B, int src_h, int src_w, int rotate, int variant,
+                           const ub_roi* roi, const ub_burr_params* params, int32_t* stats_host, int slot) {
+  NEED_CTX(ctx);
+  if (!src_host || !stats_host) return ub_fail(ctx, UB_ERR_ARG, "null argument");
+  if (slot < 0 || slot > 1) return ub_fail(ctx, UB_ERR_ARG, "slot %d (0 or 1)", slot);
+  if (B < 1 || B > ctx->max_batch || src_h < 2 || src_w < 2) return ub_fail(ctx, UB_ERR_ARG, "batch %d / source %dx%d", B, src_h, src_w);
+  if (ctx->slot_batch[slot]) return ub_fail(ctx, UB_ERR_STATE, "slot %d is still in flight: call ub_pipeline_wait first", slot);
+  const size_t fbytes = (size_t)ctx->frame_h * ctx->frame_w * 3, sbytes = (size_t)src_h * src_w * 3;
+  if (sbytes * ctx->max_batch > ctx->src_bytes) {              // (re)allocate both source slots for this source size
+    UB_CUDA(ctx, cudaDeviceSynchronize());
+    for (int i = 0; i < 2; ++i) { cudaFree(ctx->d_src[i]); ctx->d_src[i] = nullptr; }
+    ctx->src_bytes = 0;
+    for (int i = 0; i < 2; ++i) {
+      cudaError_t e = cudaMalloc(&ctx->d_src[i], sbytes * ctx->max_batch);
+      if (e != cudaSuccess) return ub_fail(ctx, UB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", sbytes * ctx->max_batch, cudaGetErrorString(e));
+    }
+    ctx->src_bytes = sbytes * ctx->max_batch;
+  }
+  if (slot == 1 && !ctx->d_frames2) {
+    cudaError_t e = cudaMalloc(&ctx->d_frames2, fbytes * ctx->max_batch);
+    if (e != cudaSuccess) return ub_fail(ctx, UB_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", fbytes * ctx->max_batch, cudaGetErrorString(e));
+  }
+  uint8_t* d_fr = slot ? ctx->d_frames2 : ctx->d_frames;
+  int32_t* d_st = ctx->d_stats + (size_t)slot * ctx->max_batch * 4;
+  UB_CUDA(ctx, cudaMemcpyAsync(ctx->d_src[slot], src_host, sbytes * B, cudaMemcpyHostToDevice, ctx->copy_stream));
+  UB_CUDA(ctx, cudaEventRecord(ctx->ev_h2d[slot], ctx->copy_stream));
+  cudaStream_t st = ctx->own_stream;
+  UB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_h2d[slot], 0));
+  RUN(normalize_frames_impl(ctx, ctx->d_src[slot], B, src_h, src_w, rotate, d_fr, ctx->frame_h, ctx->frame_w, st));
+  RUN(ub_pipeline(ctx, d_fr, B, variant, roi, params, d_st, nullptr, st));
+  UB_CUDA(ctx, cudaMemcpyAsync(stats_host, d_st, sizeof(int32_t) * 4 * B, cudaMemcpyDeviceToHost, st));
+  UB_CUDA(ctx, cudaEventRecord(ctx->ev_done[slot], st));
+  ctx->slot_batch[slot] = B;
+  return UB_OK;
+}
+
 int ub_pipeline_wait(ub_ctx* ctx, int slot) {
   NEED_CTX(ctx);
   if (slot < 0 || slot > 1) return ub_fail(ctx, UB_ERR_ARG, "slot %d (0 or 1)", slot);
@@ -573,6 +640,7 @@ int ub_debug_conv(ub_ctx* ctx, int layer, const float* x0, const float* x1, int 
   if (x1) RUN(nchw_to_pp(ctx, x1, B, d.cin1, H, W, ctx->act[in1[lvl]], d.cin1, st));
   ConvArgs a{};
   a.src0 = s0; a.src1 = x1 ? ctx->act[in1[lvl]] : nullptr; a.out = ctx->act[outb[lvl]]; a.B = B; a.H = H; a.W = W;
+  a.sat = ctx->sat_check ? ctx->d_sat : nullptr;
   RUN(run_conv_layer(ctx, ctx->conv[layer], a, st));
   return pp_to_nchw(ctx, ctx->act[outb[lvl]], B, d.cout, H, W, out, st);
 }

@@ -142,6 +142,12 @@ struct ub_ctx {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   int slot_batch[2] = {0, 0};
+  uint8_t* d_src[2] = {nullptr, nullptr};   // ub_pipeline_submit_src: raw source frames per slot (allocated on first use)
+  size_t src_bytes = 0;
+  int overlap = 1;                      // gray + edge map on the aux stream beside the network (UB_OVERLAP / ub_set_option)
+  int sat_check = 0;                    // conv epilogues count outputs that hit the 16-bit maximum (ub_set_option "check_saturation")
+  int sat_check_once = 0;               // ... for the next forward only (armed by ub_set_weights)
+  unsigned long long* d_sat = nullptr;  // the counter
   cudaStream_t aux_stream = nullptr;   // ub_pipeline: gray + edge map run here beside the network
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Timing tm;
@@ -180,6 +186,7 @@ struct ConvArgs {
   int B, H, W;
   const float* head_w; const float* head_b; int num_classes;
   float* logits; uint8_t* pred;
+  unsigned long long* sat;     // non-null: count outputs clamped to the largest finite 16-bit value
   act_t* pool_out;             // non-null: also write MaxPool2d(2,2) of the output into this PP plane (conv_rows only)
   bool up1;                    // src1 is [B, cin1, H/2, W/2]: bilinear x2 upsample fused into the operand path (conv_rows only)
 };

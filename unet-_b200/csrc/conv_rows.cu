@@ -52,6 +52,7 @@ struct RowsParams {
   // fused Upsample(x2, bilinear, align_corners) of source 1 (UPS kernels): tm1 views the HALF-resolution tensor, box =
   // low_rows x UP_LC columns x KC/8 chunks, staged in a ring of low_slots boxes at shared-memory offset low_off
   float up_sy, up_sx; int low_rows, low_chunk, low_stage, low_slots, low_off;
+  unsigned long long* sat;                     // non-null: count outputs that saturate the 16-bit activation type
   int wbytes;                                  // CG2 kernels: bytes of this CTA's half of the weights (all k-blocks, resident)
   float head[8 * 33];                          // [ncls][32] weights then [ncls] biases
   float biasv[64];                             // folded BN bias per output channel: read through the constant bank (the
@@ -573,6 +574,18 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
             hv[j >> 1] = valid ? relu_pack(v) : 0u;
           }
         }
+        if (!head && P.sat != nullptr) {                       // diagnostic: outputs that hit the largest finite value
+#ifdef UB_ACT_BF16
+          constexpr uint32_t MAXW = 0x7F7F7F7Fu;
+#else
+          constexpr uint32_t MAXW = 0x7BFF7BFFu;
+#endif
+          int cnt = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cnt += __popc(__vcmpeq2(hv[j], MAXW) & 0x00010001u);
+          cnt = __reduce_add_sync(0xffffffffu, cnt);
+          if (lane == 0 && cnt) atomicAdd(P.sat, (unsigned long long)cnt);
+        }
         if (!head && (valid || edge)) {
           act_t* o = o_grp + (size_t)(half * 2) * plane + (size_t)q * 8;
           *reinterpret_cast<uint4*>(o) = make_uint4(hv[0], hv[1], hv[2], hv[3]);
@@ -818,7 +831,7 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream
   P.B = a.B; P.kb0 = Lr.cin0 / Lr.kc; P.kbn = (Lr.cin0 + Lr.cin1) / Lr.kc;
   P.L = pp_layout(a.H, a.W);
   P.tiles_x = cdiv(a.W, T_VALID);
-  P.ncls = 0; P.logits = a.logits; P.pred = a.pred;
+  P.ncls = 0; P.logits = a.logits; P.pred = a.pred; P.sat = a.sat;
   if (a.pool_out) {
     if (a.head_w || (a.H & 1) || (a.W & 1)) return ub_fail(ctx, UB_ERR_ARG, "conv_rows: fused pool needs even H, W and no head");
     P.pool_out = a.pool_out; P.Lp = pp_layout(a.H / 2, a.W / 2);

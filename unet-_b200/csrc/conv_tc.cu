@@ -35,6 +35,7 @@ struct TcParams {
   long long total_items;
   PPLayout L;
   const float* head_w; const float* head_b; int ncls; float* logits; uint8_t* pred;
+  unsigned long long* sat;     // non-null: count outputs clamped to the largest finite 16-bit value
 };
 
 template <int BN, int KC, bool SHIFT_A>
@@ -232,6 +233,13 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
 #pragma unroll
         for (int j = 0; j < 32; ++j)
           f[j] = interior ? fminf(fmaxf(__uint_as_float(v[j]) + __ldg(P.bias + co0 + j), 0.f), UB_ACT_MAX) : 0.f;
+        if (P.sat != nullptr && P.head_w == nullptr) {         // diagnostic: outputs that hit the largest finite value
+          int cnt = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) cnt += f[j] >= UB_ACT_MAX;
+          cnt = __reduce_add_sync(0xffffffffu, cnt);
+          if (lane == 0 && cnt) atomicAdd(P.sat, (unsigned long long)cnt);
+        }
         if (P.head_w != nullptr) {
           if (interior) {
             float lg[8];
@@ -358,7 +366,7 @@ int conv3x3_tc(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t
   P.nch0 = Lr.cin0 / 8; P.nch1 = Lr.cin1 / 8; P.cout = Lr.cout; P.n_ntiles = Lr.cout / Lr.bn;
   P.L = pp_layout(a.H, a.W);
   P.total_items = (long long)a.B * P.L.ntiles * P.n_ntiles;
-  P.head_w = a.head_w; P.head_b = a.head_b; P.ncls = a.num_classes; P.logits = a.logits; P.pred = a.pred;
+  P.head_w = a.head_w; P.head_b = a.head_b; P.ncls = a.num_classes; P.logits = a.logits; P.pred = a.pred; P.sat = a.sat;
   if (a.head_w && (Lr.cout != 32 || Lr.bn != 32)) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == bn == 32");
   TimeScope ts(ctx, UB_T_CONV, st);
   // conv_impl 0: shifted-descriptor A operand (3 staged segments); 2: nine aligned segments

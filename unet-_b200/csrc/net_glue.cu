@@ -209,6 +209,7 @@ static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
                     float* logits = nullptr, uint8_t* pred = nullptr, bool head = false, act_t* pool_out = nullptr, bool up1 = false) {
   ConvArgs a{};
   a.src0 = s0; a.src1 = s1; a.out = out; a.B = B; a.H = H; a.W = W; a.pool_out = pool_out; a.up1 = up1;
+  a.sat = (ctx->sat_check || ctx->sat_check_once) ? ctx->d_sat : nullptr;
   if (head) {
     a.head_w = ctx->head_w; a.head_b = ctx->head_b; a.num_classes = ctx->num_classes;
     a.logits = logits; a.pred = pred;
@@ -279,5 +280,6 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const 
   RUN(run_conv_up(ctx, 16, A[A_X00], A[A_X13], A[A_UP1], A[A_T0], 64, B, H, W, st));
   // conv0_4.conv2 with the 1x1 `final` head (unetpp.py:119) and argmax fused in the epilogue
   RUN(run_conv(ctx, 17, A[A_T0], nullptr, A[A_X04], B, H, W, st, logits, pred, true));
+  ctx->sat_check_once = 0;
   return UB_OK;
 }

@@ -80,6 +80,7 @@ class NestedUNet(nn.Module):
         if self._weights_dirty:
             self._ctx.set_weights(self.state_dict())
             self._weights_dirty = False
+            self._check_saturation = True        # the first forward with new weights counts clamped activations
         return self._ctx
 
     def forward(self, x: torch.Tensor):
@@ -91,4 +92,14 @@ class NestedUNet(nn.Module):
             raise RuntimeError(f"expected input [B,3,H,W] with H,W multiples of 16, got {tuple(x.shape)}")
         x = x.contiguous().float()
         with torch.cuda.device(x.device):
-            return self._context(x).forward(x)
+            ctx = self._context(x)
+            y = ctx.forward(x)
+            if getattr(self, "_check_saturation", False):
+                self._check_saturation = False
+                n = ctx.get_stat("saturated", reset=True)
+                if n:
+                    import warnings
+                    warnings.warn(f"unet_b200.NestedUNet: {n} activations exceeded the fp16 operand range (65504) and were "
+                                  f"clamped in the first forward with these weights; logits may differ from the fp32 model",
+                                  RuntimeWarning, stacklevel=2)
+            return y

@@ -69,17 +69,21 @@ class InspectionPipeline:
             self.ctx.pipeline_host(frames_host, stats_host, self.variant, self.roi, self.params, masks_host)
         return stats_host
 
-    def stream_host(self, batches):
+    def stream_host(self, batches, src_rotate=None):
         """Generator over an iterable of pinned host uint8 [b,H,W,3] batches -> int32 [b,4] host statistics per batch,
         in order.  Two batches are in flight: the host->device copy of batch i+1 overlaps the compute of batch i
-        (ub_pipeline_submit / ub_pipeline_wait)."""
+        (ub_pipeline_submit / ub_pipeline_wait).  src_rotate = True / False: the batches are at the SOURCE resolution
+        [b,sh,sw,3] and are rotated (or not) and resized to the frame size on the device (ub_pipeline_submit_src)."""
         stats = [torch.empty((self.batch, 4), dtype=torch.int32).pin_memory() for _ in range(2)]
         pending = None                                   # (slot, frames kept alive, n)
         i = 0
         with torch.cuda.device(self.device):
             for frames in batches:
                 slot = i & 1
-                self.ctx.pipeline_submit(frames, stats[slot], slot, self.variant, self.roi, self.params)
+                if src_rotate is None:
+                    self.ctx.pipeline_submit(frames, stats[slot], slot, self.variant, self.roi, self.params)
+                else:
+                    self.ctx.pipeline_submit_src(frames, stats[slot], slot, src_rotate, self.variant, self.roi, self.params)
                 if pending is not None:
                     self.ctx.pipeline_wait(pending[0])
                     yield stats[pending[0]][: pending[2]].clone()
@@ -88,6 +92,35 @@ class InspectionPipeline:
             if pending is not None:
                 self.ctx.pipeline_wait(pending[0])
                 yield stats[pending[0]][: pending[2]].clone()
+
+    def saturated(self, reset=False) -> int:
+        """Conv outputs clamped to the largest finite 16-bit value while the check was on (the first step after the weights
+        were set, or always with ctx.set_option('check_saturation', 1)): non-zero means the checkpoint's activations
+        overflow the operand type and the masks are not to be trusted."""
+        return self.ctx.get_stat("saturated", reset)
+
+    class AsyncGather:
+        """All-gather of one step's statistics on a side stream: the collective of step i runs beside the
+        compute of step i+1.  start(stats) enqueues, result() makes the caller's stream wait and returns the tensor."""
+
+        def __init__(self, frame_offset, group=None):
+            self.offset, self.group = frame_offset, group
+            self.stream = torch.cuda.Stream()
+            self.done = torch.cuda.Event()
+            self.out = None
+
+        def start(self, stats):
+            ready = torch.cuda.Event()
+            ready.record()
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ready)
+                self.out = InspectionPipeline.gather_stats(stats, self.offset, self.group, equal_counts=True)
+                stats.record_stream(self.stream)
+                self.done.record(self.stream)
+
+        def result(self):
+            torch.cuda.current_stream().wait_event(self.done)
+            return self.out
 
     @staticmethod
     def gather_stats(stats: torch.Tensor, frame_offset: int, group=None, equal_counts: bool = False) -> torch.Tensor:

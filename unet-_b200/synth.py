@@ -143,6 +143,60 @@ def make_state_dict(seed: int = 0, num_classes: int = 3, input_channels: int = 3
     return sd
 
 
+def _forward_calibrating(sd, x):
+    """fp32 forward of the NestedUNet topology (src/models/unetpp.py:93-119) on x that REPLACES every BatchNorm's running
+    statistics in `sd` by the statistics of its own input, layer by layer (what training would have left there).
+    Test-data helper: plain torch.nn.functional, not part of the product path."""
+    import torch
+    import torch.nn.functional as F
+
+    def block(name, t):
+        for i in (1, 2):
+            t = F.conv2d(t, sd[f"{name}.conv{i}.weight"], sd[f"{name}.conv{i}.bias"], padding=1)
+            mu, var = t.mean((0, 2, 3)), t.var((0, 2, 3), unbiased=False)
+            sd[f"{name}.bn{i}.running_mean"], sd[f"{name}.bn{i}.running_var"] = mu.clone(), var.clone()
+            t = F.relu(F.batch_norm(t, mu, var, sd[f"{name}.bn{i}.weight"], sd[f"{name}.bn{i}.bias"], False, 0.0, 1e-5))
+        return t
+
+    up = lambda t: F.interpolate(t, scale_factor=2, mode="bilinear", align_corners=True)
+    pool = lambda t: F.max_pool2d(t, 2)
+    x0 = block("conv0_0", x); x1 = block("conv1_0", pool(x0)); x2 = block("conv2_0", pool(x1))
+    x3 = block("conv3_0", pool(x2)); x4 = block("conv4_0", pool(x3))
+    x31 = block("conv3_1", torch.cat([x3, up(x4)], 1)); x22 = block("conv2_2", torch.cat([x2, up(x31)], 1))
+    x13 = block("conv1_3", torch.cat([x1, up(x22)], 1)); x04 = block("conv0_4", torch.cat([x0, up(x13)], 1))
+    return F.conv2d(x04, sd["final.weight"], sd["final.bias"])
+
+
+def make_trained_like_state_dict(seed: int = 0, num_classes: int = 3, conv_scale: float = 3.0, gamma_max: float = 4.0,
+                                 head_gain: float = 8.0):
+    """A checkpoint shaped like a trained one rather than a fresh one: conv weights `conv_scale` times the
+    default init, BatchNorm gammas in [0.5, gamma_max], running statistics calibrated on structured frames so every BN
+    actually normalises its input (activations of order gamma, not of order 1), and a head with separated logits."""
+    import torch
+    sd = make_state_dict(seed, num_classes, head_gain=head_gain)
+    g = torch.Generator().manual_seed(seed + 77)
+    for k in list(sd):
+        if ".conv" in k and k.endswith(".weight"):
+            sd[k] = sd[k] * conv_scale
+        if ".bn" in k and k.endswith(".weight"):
+            sd[k] = 0.5 + torch.rand(sd[k].shape, generator=g) * (gamma_max - 0.5)
+    fr = np.concatenate([frames_cable(2, 128, 160, seed=seed + 5), frames_speckle(1, 128, 160, seed=seed + 6, n_blobs=40)])
+    x = torch.from_numpy(fr[..., ::-1].copy()).permute(0, 3, 1, 2).float() / 255.0
+    with torch.no_grad():
+        _forward_calibrating(sd, x)
+    return sd
+
+
+def make_overflow_state_dict(seed: int = 0):
+    """W0 with the two BatchNorm gammas of conv0_0 scaled (x200, x1000) so that the block's output exceeds the fp16 range
+    (65504) while every folded weight stays representable: the conv epilogues clamp -- what the saturation counter
+    exists to report."""
+    sd = make_state_dict(seed)
+    sd["conv0_0.bn1.weight"] = sd["conv0_0.bn1.weight"] * 200.0
+    sd["conv0_0.bn2.weight"] = sd["conv0_0.bn2.weight"] * 1000.0
+    return sd
+
+
 def frames_speckle(b: int, h: int = 448, w: int = 800, seed: int = 0, n_blobs: int = 400) -> np.ndarray:
     """Smooth dark background with sparse bright rectangles (3..14 px sides): yields
     many mid-sized edge components, so the component filter keeps a non-trivial subset."""
