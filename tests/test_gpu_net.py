@@ -231,7 +231,9 @@ def test_bf16_build_error_recorded(sd):
     import json, os, subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     lib = os.path.join(root, "build", "libunetb200_bf16.so")
-    if not os.path.exists(lib):
+    import glob
+    srcs = glob.glob(os.path.join(root, "unet-_b200", "csrc", "*.cu*")) + [os.path.join(root, "include", "unetb200.h")]
+    if not os.path.exists(lib) or os.path.getmtime(lib) < max(os.path.getmtime(f) for f in srcs):     # missing or stale
         r = subprocess.run(["bash", os.path.join(root, "tools", "build_variant.sh"), "bf16", "-DUB_ACT_BF16"], capture_output=True, text=True)
         if r.returncode != 0:
             pytest.skip("cannot build the bf16 variant here: " + r.stderr[-300:])
