@@ -165,6 +165,17 @@ int ub_ccl(ub_ctx* ctx, const uint8_t* src_dev, int B, int H, int W, int32_t* la
 int ub_sobel_edges(ub_ctx* ctx, const uint8_t* gray_dev, int B, int H, int W, int thresh, uint8_t* dst_dev, void* stream);
 int ub_laplacian_edges(ub_ctx* ctx, const uint8_t* gray_dev, int B, int H, int W, int thresh, uint8_t* dst_dev, void* stream);
 
+/* ub_sobel_edges without a context and without any allocation, for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  This entry point has no counterpart in the reference.
+ * gray u8 [B,H,W] and dst u8 [B,H,W] are device pointers on the
+ * CURRENT device; the result equals ub_sobel_edges' bit for bit.  The kernel pair's scratch (one int per frame: the
+ * maximum squared gradient) is a static device array of UB_STATIC_MAX_FRAMES entries (16 KB per GPU, held until the
+ * library is unloaded); B > UB_STATIC_MAX_FRAMES returns UB_ERR_ARG (message via ub_last_error(NULL)).  The call
+ * performs no cudaMalloc / cudaFree; the array is cleared on `stream` before use.  All calls share the array: calls that
+ * overlap on the GPU (different streams, no ordering) race -- serialise them. */
+#define UB_STATIC_MAX_FRAMES 4096
+int ub_sobel_edges_static(const uint8_t* gray_dev, int B, int H, int W, int thresh, uint8_t* dst_dev, void* stream);
+
 /* Whole detect_burrs_on_cable / detect_burrs_enhanced for a batch:
  * gray u8 [B,H,W], mask_cable u8 [B,H,W] in {0,1} -> burr_mask u8 [B,H,W] in {0,1},
  * burr_px i32 [B] (nullable). */

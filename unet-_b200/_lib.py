@@ -67,6 +67,7 @@ SIGNATURES = {
     "ub_morph": (_I, [_P, _I, _I, _P, _I, _I, _I, _I, _P, _P]),
     "ub_ccl": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _P, _P]),
     "ub_sobel_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_sobel_edges_static": (_I, [_P, _I, _I, _I, _I, _P, _P]),
     "ub_laplacian_edges": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "ub_burr": (_I, [_P, _I, _P, _P, _I, _I, _I, C.POINTER(BurrParams), _P, _P, _P]),
     "ub_cvt_lab": (_I, [_P, _I, _P, _I, _I, _I, _P, _P]),

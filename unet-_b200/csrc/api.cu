@@ -52,6 +52,7 @@ int filter_cable_by_shape(ub_ctx*, const uint8_t*, int, int, int, int, double, d
 int constrain_tape_to_ring(ub_ctx*, const uint8_t*, const uint8_t*, int, int, int, int, int, uint8_t*, cudaStream_t);
 int enh_edges(ub_ctx*, const uint8_t*, int, int, int, int, int, int, const uint8_t*, uint8_t*, cudaStream_t);
 int ccl_export(ub_ctx*, const uint8_t*, int, int, int, int*, int*, int, int*, cudaStream_t);
+int sobel_edges_static(const uint8_t*, int, int, int, int, uint8_t*, cudaStream_t);
 
 // ---------------------------------------------------------------- layer tables
 namespace {
@@ -414,6 +415,9 @@ int ub_sobel_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int th
   NEED_CTX(ctx);
   RUN(check_frame_shape(ctx, B, H, W));
   return enh_edges(ctx, gray, B, H, W, 1, thresh, 0, nullptr, dst, as_stream(stream));
+}
+int ub_sobel_edges_static(const uint8_t* gray, int B, int H, int W, int thresh, uint8_t* dst, void* stream) {
+  return sobel_edges_static(gray, B, H, W, thresh, dst, as_stream(stream));
 }
 int ub_laplacian_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int thresh, uint8_t* dst, void* stream) {
   NEED_CTX(ctx);

@@ -717,6 +717,38 @@ int enh_edges(ub_ctx* ctx, const uint8_t* gray, int B, int H, int W, int mode, i
   return UB_OK;
 }
 
+// ---- ub_sobel_edges_static: the Sobel-magnitude edge map without a context and without any allocation ------------
+// Scratch of the two-kernel scheme (k_sobel_max -> k_enh_edges) is the per-frame maximum of gx^2+gy^2; here it lives in a
+// file-scope device array that every GPU loading the library holds until exit (UB_STATIC_MAX_FRAMES ints = 16 KB).  In
+// host code the array's name is only a stand-in: its device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current.  All calls share the array (calls that overlap on the GPU race).
+static __device__ __align__(256) int g_static_sobel_max[UB_STATIC_MAX_FRAMES];
+
+int sobel_edges_static(const uint8_t* gray, int B, int H, int W, int thresh, uint8_t* dst, cudaStream_t st) {
+  static int* addr[64] = {nullptr};                     // device address of the scratch array, per device ordinal
+  if (!gray || !dst) return ub_fail(nullptr, UB_ERR_ARG, "ub_sobel_edges_static: null pointer");
+  if (B < 1 || H < 1 || W < 1) return ub_fail(nullptr, UB_ERR_ARG, "ub_sobel_edges_static: empty shape %dx%dx%d", B, H, W);
+  if (B > UB_STATIC_MAX_FRAMES)
+    return ub_fail(nullptr, UB_ERR_ARG, "ub_sobel_edges_static: %d frames exceed the static scratch (UB_STATIC_MAX_FRAMES = %d); "
+                   "split the batch or use ub_sobel_edges", B, UB_STATIC_MAX_FRAMES);
+  if (H > 65535 || B > 65535) return ub_fail(nullptr, UB_ERR_ARG, "ub_sobel_edges_static: H / B exceed the grid limits");
+  int dev = -1;
+  UB_CUDA(nullptr, cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return ub_fail(nullptr, UB_ERR_ARG, "ub_sobel_edges_static: device ordinal %d", dev);
+  if (!addr[dev]) {                                     // set-up, once per device, with that device current
+    int* p = nullptr;
+    UB_CUDA(nullptr, cudaGetSymbolAddress((void**)&p, g_static_sobel_max));
+    addr[dev] = p;
+  }
+  int* fmax = addr[dev];
+  dim3 gpix(cdiv(W, 256), H, B);
+  UB_CUDA(nullptr, cudaMemsetAsync(fmax, 0, sizeof(int) * B, st));      // the array keeps the last call's maxima
+  k_sobel_max<<<gpix, 256, 0, st>>>(gray, H, W, fmax);
+  k_enh_edges<<<gpix, 256, 0, st>>>(gray, H, W, fmax, 1, thresh, 0, nullptr, dst);
+  UB_CUDA(nullptr, cudaGetLastError());
+  return UB_OK;
+}
+
 // labels / stats in OpenCV numbering (ub_ccl).  Run-based path: labelling on packed rows, the roots' first-appearance keys as a
 // bit plane, ranks by popcount (a 32x smaller scan than one int per key), labels written 32 pixels per thread.
 // UB_CCL_PACKED=0 keeps the per-pixel kernels.
