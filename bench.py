@@ -29,7 +29,32 @@ FRAME_HW = (448, 800)
 NET_HW = (512, 512)
 GFLOP_PER_FRAME = 111.636          # 18 conv3x3 + final at 512x512, 2*MACs
 METRIC = "frames/sec (800x448 UNet++ + burr)"
-CONV_DRAM_BYTES_PER_FRAME = (11.661369e9 + 7.043801e9) / 64     # measured, see roofline.traffic
+CONV_SOURCES = ("conv_rows.cu", "conv_tc.cu", "tc_ptx.cuh", "net_glue.cu", "common.cuh")
+
+
+def conv_source_hash():
+    """sha256 over the sources of the conv kernels: an ncu capture belongs to the build it was taken from (the GPU box
+    has no .git, so the check is on the sources, not on a commit id)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in CONV_SOURCES:
+        h.update(open(os.path.join(ROOT, "unet-_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def conv_traffic(batch):
+    """DRAM bytes of the conv launches of one step from the newest profiles/rNN_conv_ncu.json (written by
+    tools/ncu_conv_summary.py from an `ncu --set full` capture).  Returns (bytes per step or None, note)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9][0-9]*_conv_ncu.json")))
+    if not files:
+        return None, "no profiles/rNN_conv_ncu.json"
+    d = json.load(open(files[-1]))
+    name = os.path.basename(files[-1])
+    per_frame = (d["dram_bytes_read"] + d["dram_bytes_write"]) / d["frames"]
+    if d.get("source_hash") != conv_source_hash():
+        return per_frame * batch, f"STALE: {name} was captured from other conv sources ({d.get('source_hash')} != {conv_source_hash()})"
+    return per_frame * batch, f"{name}: dram__bytes_read.sum + dram__bytes_write.sum over the {d['launches']} conv launches of one {d['frames']}-frame step"
 
 
 def load_peaks():
@@ -204,12 +229,17 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload, args.batch),
-                       "frame": f"{workload_hw(args.workload)[1]}x{workload_hw(args.workload)[0]}", "net": "512x512",
-                       "batch_per_gpu": args.batch},
+            "config": config_dict(args.workload, args.batch, args.gpus),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def config_dict(workload, batch, world):
+    hw = workload_hw(workload)
+    return {"workload": workload_name(workload, batch), "frame": f"{hw[1]}x{hw[0]}", "net": "512x512",
+            "batch_per_gpu": batch, "parallelism": f"frames sharded over {world} GPU(s)",
+            "l2": "activation working set ~12 GB/step per GPU >> 126 MB L2; no explicit flush"}
 
 
 def workload_name(workload, batch):
@@ -220,12 +250,162 @@ def workload_name(workload, batch):
     return f"two_stage_pipeline_800x448_batch{batch}"
 
 
-def run_ours(args):
-    import numpy as np
+class Leg:
+    """One workload on this rank's GPU: pipeline, resident frames, pinned host frames."""
+
+    def __init__(self, workload, B, world, rank, local):
+        import torch
+        import unet_b200.synth as S
+        from unet_b200.pipeline import InspectionPipeline, shard_range
+        self.workload, self.B, self.world, self.rank = workload, B, world, rank
+        self.enhanced = workload == "enhanced"
+        self.sd = S.make_state_dict(0)
+        self.pipe = InspectionPipeline(self.sd, batch=B, frame_hw=workload_hw(workload), net_hw=NET_HW, device=local,
+                                       variant="enhanced" if self.enhanced else "standard", enhance=self.enhanced)
+        # every rank owns a contiguous block of the global frame index space (weak scaling)
+        self.lo, _ = shard_range(B * world, rank, world)
+        self.frames_np = make_workload_frames(workload, B, seed=rank)
+        self.frames_host = torch.from_numpy(self.frames_np).pin_memory()
+        self.frames_dev = self.frames_host.cuda()
+        self.gather = InspectionPipeline.AsyncGather(self.lo) if world > 1 else None
+        self.h2d = int(self.frames_host.numel())
+        self.d2h = B * 4 * 4
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_dev(self):
+        """One step on resident frames.  With several ranks the statistics all-gather of this step runs on a side stream
+        beside the next step's compute; the result of the previous step's gather is returned."""
+        f = self.frames_dev
+        if self.enhanced:      # 1080p source: rotate 90 degrees CCW + resize to 800x448 (infer_enhanced_burr.py:273-276)
+            f = self.pipe.ctx.normalize_frames(f, (FRAME_HW[1], FRAME_HW[0]), rotate=True)
+        stats, _ = self.pipe.run(f)
+        if self.gather is None:
+            return stats
+        prev = self.gather.result() if self.gather.out is not None else None
+        self.gather.start(stats)
+        return prev
+
+    def last(self, out):
+        return self.gather.result() if self.gather is not None else out
+
+    def run_host_steps(self, n):
+        """n steps through the streaming host entry points (ub_pipeline_submit[_src] / ub_pipeline_wait): every step copies
+        its own frames host->device and its statistics device->host; the copy of step i+1 overlaps the compute of step i."""
+        it = self.pipe.stream_host((self.frames_host for _ in range(n)), src_rotate=True if self.enhanced else None)
+        for st_h in it:
+            if self.gather is not None:
+                self.gather.start(st_h.cuda(non_blocking=True))
+        if self.gather is not None:
+            self.gather.result()
+
+    def timed_dev(self, steps, warmup, timing=False, sampler=None):
+        import torch
+        for _ in range(warmup):
+            out = self.step_dev()
+        self.barrier()
+        if sampler is not None:
+            sampler.start()
+        ctx = self.pipe.ctx
+        if timing:
+            ctx.timing_enable(True)
+            ctx.timing_read(reset=True)
+        launches0 = ctx.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.barrier()
+        ev0.record()
+        for _ in range(steps):
+            out = self.step_dev()
+        out = self.last(out)           # the current stream waits for the last step's all-gather
+        ev1.record()
+        self.barrier()
+        ms = ev0.elapsed_time(ev1)
+        res = {"ms": ms, "launches": ctx.launch_count() - launches0, "out": out}
+        if timing:
+            res["classes"] = ctx.timing_read(reset=True)
+            ctx.timing_enable(False)
+        if sampler is not None:
+            res["clocks"] = sampler.stop()
+        return res
+
+    def timed_host(self, steps, warmup):
+        self.run_host_steps(max(2, warmup))
+        self.barrier()
+        t0 = time.perf_counter()
+        self.run_host_steps(steps)
+        self.barrier()
+        return (time.perf_counter() - t0) * 1e3
+
+    def close(self):
+        import torch
+        self.pipe.ctx.close()
+        del self.pipe, self.frames_dev, self.frames_host
+        torch.cuda.empty_cache()
+
+
+def max_over_ranks(vals, world):
     import torch
     import torch.distributed as dist
-    import unet_b200.synth as S
-    from unet_b200.pipeline import InspectionPipeline, shard_range
+    t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t]
+
+
+def side_workload(workload, world, rank, local, seconds=1.5):
+    """Short leg of another BASELINE configuration (4: enhanced, 5: net512) so that the driver's records carry them at
+    every N: device-resident and end-to-end frames/s, same timing rules as the headline (events, max over ranks)."""
+    B = 16 if workload == "enhanced" else 256
+    leg = Leg(workload, B, world, rank, local)
+    probe = leg.timed_dev(2, 3)["ms"] / 2
+    steps = int(max(4, min(200, seconds * 1e3 / max(probe, 1e-3))))
+    steps = int(max_over_ranks([steps], world)[0])
+    d = leg.timed_dev(steps, 1)
+    e2e_ms = leg.timed_host(steps, 2)
+    ms, e2e_ms = max_over_ranks([d["ms"], e2e_ms], world)
+    leg.close()
+    return {"config": config_dict(workload, B, world), "steps": steps, "ms_per_step": ms / steps,
+            "value": B * world * steps / (ms / 1e3), "unit": "frames/s",
+            "e2e": {"value": B * world * steps / (e2e_ms / 1e3), "unit": "frames/s",
+                    "h2d_bytes_per_step": leg.h2d, "d2h_bytes_per_step": leg.d2h}}
+
+
+def batch_sweep(sd, local, batches=(1, 4, 16), reps=30):
+    """Latency of one whole step at small batches (the reference loop is batch 1, infer_two_stage_burr.py:292-299):
+    host-issued launches against the captured CUDA graph of the step (ub_pipeline_graph)."""
+    import torch
+    from unet_b200.pipeline import InspectionPipeline
+    out = {}
+    for b in batches:
+        pipe = InspectionPipeline(sd, batch=b, frame_hw=FRAME_HW, net_hw=NET_HW, device=local)
+        frames = torch.from_numpy(make_frames(b, 7)).cuda()
+        row = {}
+        for mode in ("launches", "graph"):
+            if mode == "graph" and not hasattr(pipe, "run_graph"):
+                continue
+            fn = (lambda: pipe.run(frames)) if mode == "launches" else (lambda: pipe.run_graph(frames))
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fn()
+            torch.cuda.synchronize()
+            ms = (time.perf_counter() - t0) * 1e3 / reps
+            row[mode] = {"ms_per_step": ms, "frames_per_s": b / ms * 1e3}
+        out[f"batch{b}"] = row
+        pipe.ctx.close()
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -234,111 +414,55 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
-    sd = S.make_state_dict(0)
-    enhanced = args.workload == "enhanced"
-    fhw = workload_hw(args.workload)
-    pipe = InspectionPipeline(sd, batch=B, frame_hw=fhw, net_hw=NET_HW, device=local,
-                              variant="enhanced" if enhanced else "standard", enhance=enhanced)
-    # every rank owns a contiguous block of the global frame index space (weak scaling)
-    lo, _ = shard_range(B * world, rank, world)
-    frames_np = make_workload_frames(args.workload, B, seed=rank)
-    frames_host = torch.from_numpy(frames_np).pin_memory()
-    frames_dev = frames_host.cuda()
-    stats_host = torch.empty((B, 4), dtype=torch.int32).pin_memory()
+    leg = Leg(args.workload, B, world, rank, local)
+    sampler = ClockSampler(local) if rank == 0 else None
+    d = leg.timed_dev(args.steps, args.warmup, timing=True, sampler=sampler)
+    launches, tm, clocks = d["launches"], d["classes"], d.get("clocks")
+    summary = leg.pipe.summary(d["out"])
+    # end to end through the host entry points (H2D + compute + D2H inside the timed region)
+    e2e_ms = leg.timed_host(args.steps, max(2, args.warmup // 2))
+    ms, e2e_ms = max_over_ranks([d["ms"], e2e_ms], world)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    # roofline leg: the second stream (gray / edge map / hysteresis beside the net) is switched off so that the CUDA-event
+    # bracket of the conv class holds the convs alone; run for >= 1 s so that the clocks are the sustained ones
+    leg.pipe.ctx.set_option("overlap", 0)
+    roof_steps = int(max(args.steps, 1.2e3 / max(ms / args.steps, 1e-3))) if not args.quick else args.steps
+    roof_sampler = ClockSampler(local) if rank == 0 else None
+    r = leg.timed_dev(roof_steps, 2, timing=True, sampler=roof_sampler)
+    leg.pipe.ctx.set_option("overlap", 1)
+    frames_np, sd = leg.frames_np, leg.sd
+    h2d, d2h = leg.h2d, leg.d2h
+    leg.close()
 
-    def step_dev(src=None):
-        f = frames_dev if src is None else src
-        if enhanced:      # 1080p source: rotate 90 degrees CCW + resize to 800x448 (infer_enhanced_burr.py:273-276)
-            f = pipe.ctx.normalize_frames(f, (FRAME_HW[1], FRAME_HW[0]), rotate=True)
-        stats, _ = pipe.run(f)
-        if world > 1:
-            return InspectionPipeline.gather_stats(stats, lo, equal_counts=True)
-        return stats
+    extra = {}
+    if not args.quick and args.workload == "two_stage":
+        extra["workloads"] = {w: side_workload(w, world, rank, local) for w in ("enhanced", "net512")}
 
-    def step_host():
-        if enhanced:      # host frames in, host statistics out; copies on the compute stream inside the timed region
-            out = step_dev(frames_host.cuda(non_blocking=True))
-            stats_host.copy_(out[:B] if world == 1 else out[lo:lo + B])
-            return
-        pipe.run_host(frames_host, stats_host)
-        if world > 1:
-            InspectionPipeline.gather_stats(stats_host.cuda(non_blocking=True), lo, equal_counts=True)
-
-    for _ in range(args.warmup):
-        out = step_dev()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    pipe.ctx.timing_enable(True)
-    pipe.ctx.timing_read(reset=True)
-    launches0 = pipe.ctx.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record()
-    for _ in range(args.steps):
-        out = step_dev()
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = pipe.ctx.launch_count() - launches0
-    tm = pipe.ctx.timing_read(reset=True)
-    pipe.ctx.timing_enable(False)
-    clocks = sampler.stop() if rank == 0 else None
-    summary = pipe.summary(out)
-
-    # end to end through the host entry point (H2D + compute + D2H inside the timed region)
-    def run_host_steps(n):
-        if enhanced:
-            for _ in range(n):
-                step_host()
-            return
-        # the streaming host entry points (ub_pipeline_submit / _wait): every step copies its own frames host->device
-        # and its statistics device->host; the copy of step i+1 overlaps the compute of step i
-        for st_h in pipe.stream_host(frames_host for _ in range(n)):
-            if world > 1:
-                InspectionPipeline.gather_stats(st_h.cuda(non_blocking=True), lo, equal_counts=True)
-
-    run_host_steps(max(2, args.warmup // 2))
-    barrier()
-    t0 = time.perf_counter()
-    run_host_steps(args.steps)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-
-    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = float(t[0]), float(t[1])
     if rank == 0:
         peaks = load_peaks()
         fps = B * world * args.steps / (ms / 1e3)
-        conv_ms, conv_n = tm["conv3x3"]
-        tflops = GFLOP_PER_FRAME * B * args.steps / conv_ms if conv_ms > 0 else 0.0     # GFLOP/ms = TFLOP/s
-        roof = {"bound": "tensor", "kernel": "k_conv_tc (18 launches/step, tcgen05 implicit GEMM)",
-                "achieved": tflops, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                "frac": tflops / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16_tflops_sustained",
-                "frac_of_burst": tflops / peaks["tf"],
-                # dram__bytes_read.sum + dram__bytes_write.sum over the 18 conv launches of one 64-frame step
-                # (ncu --set full, profiles/r01i_conv_ncu_full.csv): 11.66 GB read + 7.04 GB written
-                "traffic": CONV_DRAM_BYTES_PER_FRAME * B, "traffic_unit": "bytes per step (18 launches), from profiles/r01i_conv_ncu_full.csv",
+        conv_ms, conv_n = r["classes"]["conv3x3"]
+        tflops = GFLOP_PER_FRAME * B * roof_steps / conv_ms if conv_ms > 0 else 0.0     # GFLOP/ms = TFLOP/s
+        conv_ms_ov = tm["conv3x3"][0]
+        traffic, traffic_note = conv_traffic(B)
+        roof = {"bound": "tensor", "kernel": "k_conv_rows / k_conv_tc (18 launches/step, tcgen05 implicit GEMM)",
+                "achieved": tflops, "peak": peaks["tf"], "unit": "TFLOP/s", "frac": tflops / peaks["tf"],
+                "peak_source": peaks["source"] + " bf16_tflops (burst)",
+                "frac_sustained": tflops / peaks["tf_sustained"], "peak_sustained": peaks["tf_sustained"],
+                "leg": {"steps": roof_steps, "seconds": r["ms"] / 1e3, "ms_per_step": r["ms"] / roof_steps,
+                        "conv_ms_per_step": conv_ms / roof_steps, "overlap": 0, "clocks": r.get("clocks")},
+                "achieved_in_timed_region": GFLOP_PER_FRAME * B * args.steps / conv_ms_ov if conv_ms_ov > 0 else 0.0,
+                "traffic": traffic, "traffic_note": traffic_note,
                 "algorithmic": f"{GFLOP_PER_FRAME} GFLOP/frame x {B} frames per step over the 18 conv launches",
-                "ms_per_step_by_class": {k: v[0] / args.steps for k, v in tm.items()},
-                "ms_per_step_by_class_note": "CUDA-event brackets per kernel class; gray/edge-map classes run on a second stream "
-                                             "beside the convs, so the classes overlap and do not add up to ms_per_step"}
+                "ms_per_step_by_class": {k: v[0] / roof_steps for k, v in r["classes"].items()},
+                "ms_per_step_by_class_note": "CUDA-event brackets per kernel class in the roofline leg (single stream, "
+                                             "so the classes are additive)"}
         line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-                "config": {"workload": workload_name(args.workload, B), "frame": f"{fhw[1]}x{fhw[0]}", "net": "512x512",
-                           "batch_per_gpu": B, "parallelism": f"frames sharded over {world} GPU(s)",
-                           "l2": "activation working set ~12 GB/step per GPU >> 126 MB L2; no explicit flush"},
+                "config": config_dict(args.workload, B, world),
                 "e2e": {"value": B * world * args.steps / (e2e_ms / 1e3), "unit": "frames/s",
-                        "h2d_bytes_per_step": int(frames_host.numel()), "d2h_bytes_per_step": int(stats_host.numel() * 4)},
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
                 "gpu_launches": int(launches), "roofline": roof, "clocks": clocks,
                 "checks": {"burr_frames": summary["burr_frames"], "frames": summary["frames"]}}
         if world == 1 and not args.no_cpu_baseline:
@@ -351,6 +475,10 @@ def run_ours(args):
             sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
             import bench_stage2
             line["hbm_kernels"] = bench_stage2.measure(512, 10)
+        if world == 1 and not args.quick and args.workload == "two_stage":
+            extra["batch_sweep"] = batch_sweep(sd, local)
+        if extra:
+            line["extra"] = extra
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -367,6 +495,7 @@ def main():
     ap.add_argument("--ref-frames-per-step", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-hbm-kernels", action="store_true", help="skip the per-entry-point stage-2 HBM table")
+    ap.add_argument("--quick", action="store_true", help="no side workloads, no batch sweep, short roofline leg")
     ap.add_argument("--workload", default="two_stage", choices=["two_stage", "enhanced", "net512"],
                     help="two_stage: BASELINE metric config (default); enhanced: config 4 (1080p rotate+resize, enhance_image, "
                          "multi-scale detector); net512: config 5 (512x512 frames, batch 256 per GPU)")

@@ -209,6 +209,15 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames_bgr_dev, int B, int variant,
                 const ub_roi* roi, const ub_burr_params* params,
                 int32_t* frame_stats_dev, uint8_t* masks_dev, void* stream);
 
+/* ub_pipeline replayed as a CUDA graph, for small batches where issuing the ~35 launches of a step from the host is the
+ * step time (the reference loop is batch 1, infer_two_stage_burr.py:292-299).  Same arguments and results as ub_pipeline.
+ * Graphs are cached per (pointers, B, variant, roi, params): the first call with a combination runs the plain step, the
+ * second captures it, later calls launch the captured graph.  `stream` must not be the legacy default stream (that, and
+ * runs with event timing or the saturation check on, take the plain path).  Pointers must stay valid while reused. */
+int ub_pipeline_graph(ub_ctx* ctx, const uint8_t* frames_bgr_dev, int B, int variant,
+                      const ub_roi* roi, const ub_burr_params* params,
+                      int32_t* frame_stats_dev, uint8_t* masks_dev, void* stream);
+
 /* Same, from HOST buffers (pinned for full speed): copies frames host->device, runs the
  * step, copies the stats (and masks if non-NULL) back, and waits for completion. */
 int ub_pipeline_host(ub_ctx* ctx, const uint8_t* frames_bgr_host, int B, int variant,

@@ -152,3 +152,11 @@ def test_run_loop_gloo_world2(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=180)
         assert p.returncode == 0, out
+
+
+def test_device_flag_has_no_cpu_path():
+    """--device cpu runs on the CPU in the reference (infer_two_stage_burr.py:206); here it must fail, not fall through
+    to whatever CUDA device is current."""
+    from unet_b200 import _lib
+    with pytest.raises(_lib.UbError):
+        K.resolve_device("cpu")

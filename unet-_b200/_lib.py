@@ -76,6 +76,7 @@ SIGNATURES = {
     "ub_sharpen3": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_enhance": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ub_pipeline": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P, _P]),
+    "ub_pipeline_graph": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P, _P]),
     "ub_pipeline_host": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _P]),
     "ub_pipeline_submit": (_I, [_P, _P, _I, _I, C.POINTER(Roi), C.POINTER(BurrParams), _P, _I]),
     "ub_pipeline_wait": (_I, [_P, _I]),
@@ -366,15 +367,20 @@ class Context:
         return dst
 
     # -- whole step
-    def pipeline(self, frames: torch.Tensor, variant=VARIANT_STANDARD, roi=None, params=None, want_masks=False):
+    def pipeline(self, frames: torch.Tensor, variant=VARIANT_STANDARD, roi=None, params=None, want_masks=False,
+                 stats=None, masks=None, graph=False):
+        """graph=True replays the step as a CUDA graph (ub_pipeline_graph): pass the same frames / stats / masks tensors
+        every time, the graph is keyed on their addresses."""
         b = frames.shape[0]
         assert tuple(frames.shape[1:3]) == self.frame_hw
-        stats = torch.empty((b, 4), dtype=torch.int32, device=frames.device)
-        masks = torch.empty((b, 3) + self.frame_hw, dtype=torch.uint8, device=frames.device) if want_masks else None
+        if stats is None:
+            stats = torch.empty((b, 4), dtype=torch.int32, device=frames.device)
+        if masks is None and want_masks:
+            masks = torch.empty((b, 3) + self.frame_hw, dtype=torch.uint8, device=frames.device)
         r = C.byref(Roi(*roi)) if roi is not None else None
         p = C.byref(params) if params is not None else None
-        self._check(lib().ub_pipeline(self._h, self._dev(frames, torch.uint8), b, variant, r, p, stats.data_ptr(),
-                                      _ptr(masks), self.stream))
+        fn = lib().ub_pipeline_graph if graph else lib().ub_pipeline
+        self._check(fn(self._h, self._dev(frames, torch.uint8), b, variant, r, p, stats.data_ptr(), _ptr(masks), self.stream))
         return stats, masks
 
     def pipeline_host(self, frames, stats_out, variant=VARIANT_STANDARD, roi=None, params=None, masks_out=None):

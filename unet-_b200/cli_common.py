@@ -257,3 +257,16 @@ def dist_env():
     import atexit
     atexit.register(lambda: dist.is_initialized() and dist.destroy_process_group())
     return rank, world, gather
+
+
+def resolve_device(name):
+    """--device of the reference CLIs (infer_two_stage_burr.py:184,206): only CUDA devices exist here.  'cuda' resolves to
+    the current device so that the printed device is the one the run uses; anything else fails loudly (no CPU path)."""
+    import torch
+    from . import _lib
+    dev = torch.device(name)
+    if dev.type != "cuda":
+        raise _lib.UbError(f"--device {name}: unet_b200 has no CPU path; use cuda or cuda:N")
+    if not torch.cuda.is_available():
+        raise _lib.UbError("no CUDA device: unet_b200 has no CPU fallback")
+    return torch.device("cuda", dev.index if dev.index is not None else torch.cuda.current_device())

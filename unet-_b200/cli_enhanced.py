@@ -62,7 +62,7 @@ def main(argv=None, out=print, state_dict=None):
     say(f"\n加载模型: {args.model}")
     sd = state_dict if state_dict is not None else K.load_state_dict(args.model)
     import torch
-    device = torch.device(args.device)
+    device = K.resolve_device(args.device)
     say(f"模型已加载到 {device}")
 
     sh, sw = (int(v) for v in args.synthetic_size.lower().split("x"))

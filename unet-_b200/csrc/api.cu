@@ -4,6 +4,7 @@
 #include <stdarg.h>
 #include <string.h>
 #include <map>
+#include <vector>
 #include "common.cuh"
 
 thread_local std::string g_last_error;
@@ -57,6 +58,21 @@ int sobel_edges_static(const uint8_t*, int, int, int, int, uint8_t*, cudaStream_
 // ---------------------------------------------------------------- layer tables
 namespace {
 // keeps the caller's current device across an entry point that has to switch to the context's
+struct StepKey {
+  const void* frames; void* stats; void* masks; int B, variant, overlap, has_roi, has_params; ub_roi roi; ub_burr_params params;
+};
+struct StepGraph { StepKey key; cudaGraphExec_t exec = nullptr; int calls = 0; int64_t launches = 0; };
+struct StepGraphs { std::vector<StepGraph> v; };
+constexpr size_t kMaxStepGraphs = 8;
+
+void step_graphs_free(ub_ctx* ctx) {
+  if (!ctx->graphs) return;
+  StepGraphs* g = static_cast<StepGraphs*>(ctx->graphs);
+  for (auto& e : g->v) if (e.exec) cudaGraphExecDestroy(e.exec);
+  delete g;
+  ctx->graphs = nullptr;
+}
+
 struct DeviceGuard {
   int prev = -1;
   explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; if (prev != dev) cudaSetDevice(dev); else prev = -1; }
@@ -154,6 +170,7 @@ void ub_destroy(ub_ctx* c) {
   if (!c) return;
   DeviceGuard guard(c->device);
   cudaDeviceSynchronize();
+  step_graphs_free(c);
   cudaFree(c->d_src[0]); cudaFree(c->d_src[1]); cudaFree(c->d_sat);
   for (auto& p : c->act) cudaFree(p);
   for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.w2); cudaFree(L.bias); }
@@ -181,6 +198,7 @@ int ub_set_conv_impl(ub_ctx* ctx, int impl) {
   NEED_CTX(ctx);
   if (impl < 0 || impl > 2) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A)", impl);
   ctx->conv_impl = impl;
+  step_graphs_free(ctx);                 // captured steps hold the old kernel choice
   return UB_OK;
 }
 
@@ -189,6 +207,8 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
   NEED_CTX(ctx);
   if (!t || n <= 0) return ub_fail(ctx, UB_ERR_ARG, "no tensors");
   DeviceGuard guard(ctx->device);
+  cudaDeviceSynchronize();
+  step_graphs_free(ctx);                 // captured steps hold the old weight pointers
   std::map<std::string, const ub_named_tensor*> m;
   for (int i = 0; i < n; ++i) if (t[i].name) m[t[i].name] = &t[i];
   auto get = [&](const std::string& name, int64_t numel, const float** out) -> int {
@@ -530,6 +550,59 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
     for (int k = 0; k < 3; ++k)
       UB_CUDA(ctx, cudaMemcpy2DAsync(masks + k * fpix, 3 * fpix, ctx->d_mask[k], fpix, fpix, B, cudaMemcpyDeviceToDevice, st));
   }
+  return UB_OK;
+}
+
+// ub_pipeline as a replayed CUDA graph.  A step is ~35 launches on two streams; at batch 64 the host issues them well
+// ahead of the device, at batch 1-4 (the reference loop is batch 1, infer_two_stage_burr.py:292-299) issuing them IS the
+// step time.  Graphs are keyed on everything that is baked into the launches (pointers, batch, variant, ROI, parameters,
+// the overlap switch).  The first call with a key runs the step eagerly (lazy allocations, one-time table uploads and the
+// armed saturation check happen there), the second captures and instantiates, later calls only launch.
+
+int ub_pipeline_graph(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub_roi* roi, const ub_burr_params* params,
+                      int32_t* frame_stats, uint8_t* masks, void* stream) {
+  NEED_CTX(ctx);
+  cudaStream_t st = as_stream(stream);
+  // the legacy default stream cannot be captured, and event-timed runs want their brackets: both run the plain step
+  if (st == nullptr || st == cudaStreamLegacy || ctx->tm.on || ctx->sat_check || ctx->sat_check_once)
+    return ub_pipeline(ctx, frames, B, variant, roi, params, frame_stats, masks, stream);
+  if (!ctx->graphs) ctx->graphs = new StepGraphs();
+  StepGraphs* G = static_cast<StepGraphs*>(ctx->graphs);
+  StepKey k;
+  memset(&k, 0, sizeof k);
+  k.frames = frames; k.stats = frame_stats; k.masks = masks; k.B = B; k.variant = variant; k.overlap = ctx->overlap;
+  k.has_roi = roi != nullptr; k.has_params = params != nullptr;
+  if (roi) k.roi = *roi;
+  if (params) memcpy(&k.params, params, sizeof *params);
+  StepGraph* e = nullptr;
+  for (auto& c : G->v) if (!memcmp(&c.key, &k, sizeof k)) { e = &c; break; }
+  if (!e) {
+    if (G->v.size() >= kMaxStepGraphs) {                       // drop the oldest
+      if (G->v.front().exec) cudaGraphExecDestroy(G->v.front().exec);
+      G->v.erase(G->v.begin());
+    }
+    G->v.push_back(StepGraph());
+    e = &G->v.back();
+    e->key = k;
+  }
+  if (e->calls++ == 0) return ub_pipeline(ctx, frames, B, variant, roi, params, frame_stats, masks, stream);
+  if (!e->exec) {
+    DeviceGuard guard(ctx->device);
+    const int64_t l0 = ctx->launches;
+    UB_CUDA(ctx, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int r = ub_pipeline(ctx, frames, B, variant, roi, params, frame_stats, masks, stream);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    e->launches = ctx->launches - l0;
+    ctx->launches = l0;                                        // nothing has run yet
+    if (r != UB_OK) { if (graph) cudaGraphDestroy(graph); e->calls = 0; return r; }
+    if (ce != cudaSuccess) { e->calls = 0; return ub_fail(ctx, UB_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce)); }
+    const cudaError_t ie = cudaGraphInstantiate(&e->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) { e->exec = nullptr; e->calls = 0; return ub_fail(ctx, UB_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ie)); }
+  }
+  UB_CUDA(ctx, cudaGraphLaunch(e->exec, st));
+  ctx->launches += e->launches;
   return UB_OK;
 }
 

@@ -150,6 +150,7 @@ struct ub_ctx {
   unsigned long long* d_sat = nullptr;  // the counter
   cudaStream_t aux_stream = nullptr;   // ub_pipeline: gray + edge map run here beside the network
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  void* graphs = nullptr;              // ub_pipeline_graph: captured steps (StepGraphs*, api.cu)
   Timing tm;
 };
 

@@ -463,6 +463,10 @@ int clahe(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, in
           int tiles_x, int tiles_y, cudaStream_t st) {
   if (tiles_x < 1 || tiles_y < 1 || tiles_x * tiles_y > 64 || W % tiles_x || H % tiles_y)
     return ub_fail(ctx, UB_ERR_ARG, "CLAHE: %dx%d does not divide into %dx%d tiles (<= 64 tiles; OpenCV would pad)", W, H, tiles_x, tiles_y);
+  // the per-tile LUTs live at the start of d_comp (24 bytes per frame pixel of the context)
+  if ((size_t)B * tiles_x * tiles_y * 256 > (size_t)24 * ctx->max_batch * ctx->frame_h * ctx->frame_w)
+    return ub_fail(ctx, UB_ERR_ARG, "CLAHE: %d images x %d tiles need more LUT scratch than a %dx%d context holds", B,
+                   tiles_x * tiles_y, ctx->frame_w, ctx->frame_h);
   TimeScope ts(ctx, UB_T_ENHANCE, st);
   const int area = (W / tiles_x) * (H / tiles_y);
   int clip = (int)(clip_limit * area / 256);

@@ -48,7 +48,8 @@ static int get_table(ub_ctx* ctx, int src, int dst, bool is_x, const int4** out,
     rc->host.push_back(h);
     int4* d = nullptr;
     UB_CUDA(ctx, cudaMalloc(&d, sizeof(int4) * dst));
-    UB_CUDA(ctx, cudaMemcpyAsync(d, h->data(), sizeof(int4) * dst, cudaMemcpyHostToDevice, st));
+    // blocking (once per shape): a later call on another stream must not read the table before it has landed
+    UB_CUDA(ctx, cudaMemcpy(d, h->data(), sizeof(int4) * dst, cudaMemcpyHostToDevice));
     it = rc->dev.emplace(key, d).first;
   }
   *out = it->second;

@@ -32,19 +32,23 @@ BURR_CONFIGS = {
     "high": {"band_out": 20, "laplacian_threshold": 20, "min_area": 20, "max_area": 1000, "morph_kernel": 5},
 }
 
-_contexts = {}
+_contexts = {}          # insertion-ordered: least recently used first
+_MAX_CONTEXTS = 4
 
 
-def _ctx(device, batch, frame_hw, net_hw=(512, 512)) -> _lib.Context:
-    """Cached scratch context for stand-alone operator calls."""
+def _ctx(device, batch, frame_hw, net_hw=(16, 16)) -> _lib.Context:
+    """Cached scratch context for stand-alone operator calls.  Operators that never run the network get minimal network
+    planes (16x16); at most _MAX_CONTEXTS contexts are kept, the least recently used one is closed."""
     dev = torch.device(device)
     key = (dev.index or 0, tuple(frame_hw), tuple(net_hw))
-    c = _contexts.get(key)
+    c = _contexts.pop(key, None)
     if c is None or c.max_batch < batch:
         if c is not None:
             c.close()
+        while len(_contexts) >= _MAX_CONTEXTS:
+            _contexts.pop(next(iter(_contexts))).close()
         c = _lib.Context(dev.index or 0, max_batch=max(batch, 1), frame_hw=frame_hw, net_hw=net_hw)
-        _contexts[key] = c
+    _contexts[key] = c
     return c
 
 

@@ -59,6 +59,18 @@ class InspectionPipeline:
         with torch.cuda.device(self.device):
             return self.ctx.pipeline(frames, self.variant, self.roi, self.params, want_masks)
 
+    def run_graph(self, frames: torch.Tensor, stats: torch.Tensor = None):
+        """run() replayed as a CUDA graph (ub_pipeline_graph) for small batches, where the host-side launches are the step
+        time.  The graph is keyed on the addresses of `frames` and `stats`: refill the same tensors between calls
+        (frames.copy_(...)).  Returns the stats tensor (owned by the pipeline unless given)."""
+        if stats is None:
+            if getattr(self, "_graph_stats", None) is None or self._graph_stats.shape[0] != frames.shape[0]:
+                self._graph_stats = torch.empty((frames.shape[0], 4), dtype=torch.int32, device=frames.device)
+            stats = self._graph_stats
+        with torch.cuda.device(self.device):
+            self.ctx.pipeline(frames, self.variant, self.roi, self.params, stats=stats, graph=True)
+        return stats
+
     def run_host(self, frames_host, stats_host=None, masks_host=None):
         """frames_host: (pinned) uint8 [B,H,W,3] on the host -> stats int32 [B,4] on the host.
         Includes the host->device and device->host copies; synchronous."""

@@ -213,3 +213,12 @@ def frames_speckle(b: int, h: int = 448, w: int = 800, seed: int = 0, n_blobs: i
         for c, gain in enumerate((1.0, 0.97, 0.93)):
             out[i, :, :, c] = np.clip(img * gain, 0, 255).astype(np.uint8)
     return out
+
+
+def status_frames(n_each: int = 16, h: int = 448, w: int = 800, seed: int = 100) -> np.ndarray:
+    """4 * n_each frames of four kinds -- cable with burr blobs, sparse speckle, iid noise, flat frames without any
+    edge -- for counting how often two implementations print the same [BURR!] / [OK] status."""
+    rng = np.random.default_rng(seed)
+    flat = np.clip(rng.normal(60.0, 1.0, size=(n_each, h, w, 3)), 0, 255).astype(np.uint8)
+    return np.concatenate([frames_cable(n_each, h, w, seed=seed), frames_speckle(n_each, h, w, seed=seed + 1),
+                           frames_noise(n_each, h, w, seed=seed + 2), flat])
