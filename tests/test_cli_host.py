@@ -160,3 +160,19 @@ def test_device_flag_has_no_cpu_path():
     from unet_b200 import _lib
     with pytest.raises(_lib.UbError):
         K.resolve_device("cpu")
+
+
+def test_prefetch_source_keeps_order_and_contract():
+    """The decode ring hands out the source's frames in order, then None forever, and releases cleanly mid-stream."""
+    frames = np.arange(37 * 4 * 6 * 3, dtype=np.uint8).reshape(37, 4, 6, 3)
+    src = K.PrefetchSource(K.ArraySource(frames), depth=5)
+    assert (src.total_frames, src.height, src.width) == (37, 4, 6)
+    got = []
+    while (f := src.read()) is not None:
+        got.append(f)
+    assert src.read() is None and len(got) == 37 and all(np.array_equal(a, b) for a, b in zip(got, frames))
+    src.release()
+    src = K.PrefetchSource(K.ArraySource(frames), depth=2)
+    assert np.array_equal(src.read(), frames[0])
+    src.release()                                   # reader thread blocked on a full queue must stop
+    assert not src.t.is_alive()

@@ -60,8 +60,72 @@ class VideoSource:
         self.cap.release()
 
 
-def open_source(video, synthetic: int, synthetic_hw=(448, 800), seed: int = 0):
-    """-> source or None (None = cannot be opened; the caller prints the reference's error line)."""
+class PrefetchSource:
+    """Decode ring: a thread reads ahead of the loop into a bounded queue, so that cv2's decode (which releases the GIL)
+    overlaps the device step, the drawing and the encode of the previous batch instead of alternating with them as in the
+    reference loop (infer_two_stage_burr.py:268-272).  Same read() / release() contract and frame order as the source."""
+
+    def __init__(self, src, depth: int = 128):
+        import queue
+        import threading
+        self.src = src
+        self.total_frames, self.fps, self.width, self.height = src.total_frames, src.fps, src.width, src.height
+        self.q = queue.Queue(maxsize=max(2, depth))
+        self.stop = False
+        self.done = False
+        self.decode_s = 0.0                       # time the thread spent inside src.read(): the decode ceiling
+        self.frames_read = 0
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _run(self):
+        while not self.stop:
+            t0 = time.perf_counter()
+            f = self.src.read()
+            self.decode_s += time.perf_counter() - t0
+            if f is not None:
+                self.frames_read += 1
+            while not self.stop:
+                try:
+                    self.q.put(f, timeout=0.1)
+                    break
+                except Exception:
+                    continue
+            if f is None:
+                return
+
+    def read(self):
+        if self.done:
+            return None
+        f = self.q.get()
+        if f is None:
+            self.done = True
+        return f
+
+    def decode_fps(self):
+        return self.frames_read / self.decode_s if self.decode_s > 0 else float("inf")
+
+    def release(self):
+        self.stop = True
+        try:
+            while True:
+                self.q.get_nowait()
+        except Exception:
+            pass
+        self.t.join(timeout=5)
+        self.src.release()
+
+
+def open_source(video, synthetic: int, synthetic_hw=(448, 800), seed: int = 0, prefetch: int = 0):
+    """-> source or None (None = cannot be opened; the caller prints the reference's error line).  prefetch > 0 wraps a
+    video file in a decode ring of that many frames."""
+    src = _open_source(video, synthetic, synthetic_hw, seed)
+    if src is not None and prefetch > 0 and isinstance(src, VideoSource):
+        return PrefetchSource(src, prefetch)
+    return src
+
+
+def _open_source(video, synthetic: int, synthetic_hw=(448, 800), seed: int = 0):
     if synthetic:
         from . import synth
         return ArraySource(synth.frames_cable(synthetic, synthetic_hw[0], synthetic_hw[1], seed=seed))

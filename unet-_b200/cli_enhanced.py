@@ -66,7 +66,7 @@ def main(argv=None, out=print, state_dict=None):
     say(f"模型已加载到 {device}")
 
     sh, sw = (int(v) for v in args.synthetic_size.lower().split("x"))
-    src = K.open_source(args.video, args.synthetic, (sh, sw))
+    src = K.open_source(args.video, args.synthetic, (sh, sw), prefetch=2 * args.batch)
     if src is None:
         say(f"错误: 无法打开视频 {args.video}")
         return 0

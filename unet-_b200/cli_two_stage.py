@@ -76,7 +76,7 @@ def main(argv=None, out=print, state_dict=None):
     r = FIXED_ROI_512
     say(f"\n固定ROI（512x512）: X[{r['x1']}, {r['x2']}] Y[{r['y1']}, {r['y2']}]")
 
-    src = K.open_source(args.video, args.synthetic)
+    src = K.open_source(args.video, args.synthetic, prefetch=2 * args.batch)
     if src is None:
         say(f"错误: 无法打开视频 {args.video}")
         return 0

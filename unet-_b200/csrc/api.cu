@@ -233,7 +233,10 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     RUN(get(bn + ".running_mean", d.cout, &mu));
     RUN(get(bn + ".running_var", d.cout, &var));
     const int kbn = cin_pad / d.kc, cpk = d.kc / 8, nnt = d.cout / d.bn;
-    std::vector<act_t> wp((size_t)d.cout * cin_pad * 9), wp2(d.fold ? wp.size() : 0);
+    // wp2: the CTA-pair layout (conv_rows: halves of N' = 3*cout; conv_tc with bn >= 64: halves of every n-tile, per stage)
+    const bool tc_pair = !d.fold && d.bn >= 64;
+    const int kys = d.bn >= 256 ? 1 : 3;               // kernel rows per pipeline stage of k_conv_tc (Cfg::KYS)
+    std::vector<act_t> wp((size_t)d.cout * cin_pad * 9), wp2(d.fold || tc_pair ? wp.size() : 0);
     std::vector<float> bias(d.cout);
     for (int co = 0; co < d.cout; ++co) {
       const double scale = (double)g[co] / sqrt((double)var[co] + 1e-5);
@@ -253,6 +256,11 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
           if (d.fold) {
             const int nph = 3 * d.cout / 2, n = (tap % 3) * d.cout + co;
             wp2[((((((size_t)(n / nph) * kbn + kb) * 3 + tap / 3) * cpk + cc) * nph) + n % nph) * 8 + j] = wp[o];
+          } else if (tc_pair) {
+            // [n-tile][k-block][stage][rank][row of the stage][kx][chunk][bn/2][8]
+            const int ky = tap / 3, kx = tap % 3, bh = d.bn / 2, nst = 3 / kys;
+            const size_t stg = ((size_t)nt * kbn + kb) * nst + ky / kys;
+            wp2[((((((stg * 2 + r / bh) * kys + ky % kys) * 3 + kx) * cpk + cc) * bh) + r % bh) * 8 + j] = wp[o];
           }
         }
       }
@@ -262,7 +270,7 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn; L.fold = d.fold;
     if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
     if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
-    if (d.fold) {
+    if (d.fold || tc_pair) {
       if (!L.w2) RUN(dmalloc(ctx, &L.w2, wp2.size()));
       UB_CUDA(ctx, cudaMemcpy(L.w2, wp2.data(), wp2.size() * sizeof(act_t), cudaMemcpyHostToDevice));
     }

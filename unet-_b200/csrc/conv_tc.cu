@@ -63,7 +63,7 @@ struct Cfg {
 // a cluster walk the SAME (n-tile, k-block) sequence on two neighbouring m-tiles, so each loads half of every weight
 // stage and multicasts it to both (the deep layers stream 74 KB of weights per 13 KB of activations and were bound
 // by L2->SM bandwidth, profiles/r01_conv.md).  An odd tail item is computed by both CTAs (identical stores).
-template <bool PAIR>
+template <int PAIR>
 __device__ __forceinline__ bool tc_item(const TcParams& P, int i, uint32_t rank, int& nt, int& mt, int& b) {
   if (!PAIR) {
     const long long item = blockIdx.x + (long long)i * gridDim.x;
@@ -83,9 +83,16 @@ __device__ __forceinline__ bool tc_item(const TcParams& P, int i, uint32_t rank,
   return true;
 }
 
-template <int BN, int KC, bool SHIFT_A, bool PAIR>
+// PAIR: 0 = independent CTAs; 1 = clusters of two sharing every weight stage by multicast (M = 128 MMAs in each CTA);
+// 2 = clusters of two driven by the leader's tcgen05.mma.cta_group::2: M = 256 over both CTAs' m-tiles, each CTA stages its
+// own activation segments and HALF of the N weight rows (ConvLayer::w2 layout), so a weight stage costs each SM half the
+// shared-memory fill and half the operand reads per FLOP.  1-D bulk copies cannot signal a barrier in the peer CTA, so the
+// peer's (otherwise idle) MMA warp relays: it waits for the local `full` barrier and arrives on the leader's `pfull`.
+template <int BN, int KC, bool SHIFT_A, int PAIR>
 __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcParams P) {
   using C = Cfg<BN, KC, SHIFT_A>;
+  constexpr bool CG2 = PAIR == 2;
+  constexpr int B_ST = CG2 ? C::B_STAGE / 2 : C::B_STAGE;              // bytes of weights per stage in THIS CTA
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -96,14 +103,16 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
   const uint32_t bar_tfull = bar_empty + 8 * S, bar_tempty = bar_tfull + 16;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 8 * (2 * S + 4));
   float* s_head = reinterpret_cast<float*>(smem + 512);               // [ncls*32 + ncls] <= 8*33
+  [[maybe_unused]] const uint32_t bar_pfull = smem_u32(smem) + 1600;   // CG2 leader: the peer's stage has landed (S <= 24)
   const uint32_t a_base = smem_u32(smem) + C::HDR;
   const uint32_t b_base = a_base + S * C::A_STAGE;
   const PPLayout& L = P.L;
 
   if (threadIdx.x == 0) {
     // PAIR: a stage is free when the MMAs of BOTH CTAs have retired (the peer writes half of it)
-    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, PAIR ? 2 : 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, 4); }
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, PAIR == 1 ? 2 : 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, CG2 ? 8 : 4); }
+    if (CG2) for (int i = 0; i < S; ++i) mbar_init(bar_pfull + 8 * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (P.head_w != nullptr) {
@@ -112,15 +121,20 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
       s_head[i] = i < n ? P.head_w[i] : P.head_b[i - n];
   }
   if (warp == 4) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "n"(C::TMEM_COLS));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (CG2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(C::TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(C::TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   if (PAIR) cluster_sync();                  // the peer's barriers exist before anything is multicast to them
   const uint32_t tmem_base = *tmem_slot;
+  [[maybe_unused]] const uint32_t lead_tempty = CG2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
 
   if (warp == 4) {
     // ===================== producer: contiguous bulk copies, issued by ONE lane =====================
@@ -141,7 +155,7 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
           for (int ky0 = 0; ky0 < 3; ky0 += C::KYS) {
             const uint32_t full = bar_full + 8 * s;
             mbar_wait(bar_empty + 8 * s, ph ^ 1);
-            mbar_expect_tx(full, C::A_STAGE + (load_b ? C::B_STAGE : 0));
+            mbar_expect_tx(full, C::A_STAGE + (load_b ? B_ST : 0));
             const uint32_t a_st = a_base + s * C::A_STAGE;
 #pragma unroll
             for (int kyi = 0; kyi < C::KYS; ++kyi)
@@ -155,10 +169,17 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
                            C::A_SEG_BYTES, full);
               }
             if (load_b) {
-              const act_t* wsrc = wsrc_kb + (size_t)ky0 * 3 * (KC * BN);
-              const uint32_t wdst = b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
-              if (PAIR) bulk_g2s_mcast(wdst + cta_rank * (C::B_STAGE / 2), wsrc + cta_rank * (C::B_STAGE / 4), C::B_STAGE / 2, full, 3);
-              else bulk_g2s(wdst, wsrc, C::B_STAGE, full);
+              if constexpr (CG2) {
+                // w2: [n-tile][k-block][stage][rank][...]: this CTA's half of the stage is one contiguous piece
+                const size_t st_idx = ((size_t)nt * P.kbn + kb) * (3 / C::KYS) + ky0 / C::KYS;
+                bulk_g2s(b_base + (P.b_resident ? (kb * (3 / C::KYS) + ky0 / C::KYS) : s) * B_ST,
+                         P.w + (st_idx * 2 + cta_rank) * (size_t)(B_ST / 2), B_ST, full);
+              } else {
+                const act_t* wsrc = wsrc_kb + (size_t)ky0 * 3 * (KC * BN);
+                const uint32_t wdst = b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
+                if (PAIR) bulk_g2s_mcast(wdst + cta_rank * (C::B_STAGE / 2), wsrc + cta_rank * (C::B_STAGE / 4), C::B_STAGE / 2, full, 3);
+                else bulk_g2s(wdst, wsrc, C::B_STAGE, full);
+              }
             }
             if (++s == S) { s = 0; ph ^= 1; }
           }
@@ -166,13 +187,26 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
         first = false;
       }
     }
+  } else if (CG2 && warp == 5 && cta_rank != 0) {
+    // ===================== CG2 peer: relay "my stage has landed" to the leader, whose MMAs read it =====================
+    const uint32_t lead_pfull = mapa_u32(bar_pfull, 0);
+    int s = 0; uint32_t ph = 0;
+    int nt, mt, b;
+    for (int it = 0; tc_item<PAIR>(P, it, cta_rank, nt, mt, b); ++it)
+      for (int i = 0; i < P.kbn * (3 / C::KYS); ++i) {
+        mbar_wait(bar_full + 8 * s, ph);
+        if (lane == 0) mbar_arrive_cluster(lead_pfull + 8 * s);
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1; }
+      }
   } else if (warp == 5) {
     // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues =====================
     // (under a plain `lane == 0` branch every UTCHMMA is wrapped in an elect-and-branch loop of ~16 dependent
     //  uniform-datapath instructions, and this warp paces the tensor pipe)
     {
       constexpr uint32_t IDESC = (1u << 4) | (UB_MMA_FMT << 7) | (UB_MMA_FMT << 10) | ((uint32_t)(BN >> 3) << 17) |
-                                 ((uint32_t)(TILE_M >> 4) << 24);
+                                 ((uint32_t)((CG2 ? 2 * TILE_M : TILE_M) >> 4) << 24);
+      constexpr int BNH = CG2 ? BN / 2 : BN;                      // rows of B in this CTA's shared memory
       int s = 0; uint32_t ph = 0;
       int nt, mt, b;
       for (int it = 0; tc_item<PAIR>(P, it, cta_rank, nt, mt, b); ++it) {
@@ -184,9 +218,11 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
 #pragma unroll 1
           for (int ky0 = 0; ky0 < 3; ky0 += C::KYS) {
             mbar_wait(bar_full + 8 * s, ph);
+            if (CG2) mbar_wait(bar_pfull + 8 * s, ph);     // (a cluster-scope acquire here costs ~500 clk per stage in the issuing thread: 2.4x slower layers)
             tc_fence_after();
             const uint32_t a_st = a_base + s * C::A_STAGE;
-            const uint32_t b_st = b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
+            const uint32_t b_st = CG2 ? b_base + (P.b_resident ? (kb * (3 / C::KYS) + ky0 / C::KYS) : s) * B_ST
+                                      : b_base + (P.b_resident ? kb * C::B_KB + ky0 * C::B_KY : s * C::B_STAGE);
             if (elect_one()) {
 #pragma unroll
               for (int kyi = 0; kyi < C::KYS; ++kyi)
@@ -196,13 +232,18 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
 #pragma unroll
                   for (int k16 = 0; k16 < KC / 16; ++k16) {
                     const uint64_t ad = make_desc(a_tap + 2 * k16 * C::A_SEG_BYTES, C::A_SEG_BYTES, 128);
-                    const uint64_t bd = make_desc(b_st + (kyi * 3 + kx) * C::B_TAP + 2 * k16 * BN * 16, BN * 16, 128);
-                    tc_mma(d_tmem, ad, bd, IDESC, (kb | ky0 | kyi | kx | k16) != 0);
+                    const uint64_t bd = make_desc(b_st + (kyi * 3 + kx) * (KC * BNH * 2) + 2 * k16 * BNH * 16, BNH * 16, 128);
+                    if (CG2) tc_mma_pair(d_tmem, ad, bd, IDESC, (kb | ky0 | kyi | kx | k16) != 0);
+                    else tc_mma(d_tmem, ad, bd, IDESC, (kb | ky0 | kyi | kx | k16) != 0);
                   }
                 }
-              if (PAIR) tc_commit_mcast(bar_empty + 8 * s, 3);   // frees the stage (in both CTAs) when these MMAs retire
+              if (CG2) tc_commit_pair(bar_empty + 8 * s, 3);     // frees the stage in both CTAs when these MMAs retire
+              else if (PAIR) tc_commit_mcast(bar_empty + 8 * s, 3);
               else tc_commit(bar_empty + 8 * s);
-              if (kb == P.kbn - 1 && ky0 + C::KYS == 3) tc_commit(bar_tfull + 8 * buf);   // accumulator ready for the epilogue
+              if (kb == P.kbn - 1 && ky0 + C::KYS == 3) {        // accumulator ready for the epilogue (CG2: of both CTAs)
+                if (CG2) tc_commit_pair(bar_tfull + 8 * buf, 3);
+                else tc_commit(bar_tfull + 8 * buf);
+              }
             }
             __syncwarp();
             if (++s == S) { s = 0; ph ^= 1; }
@@ -271,7 +312,9 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+      if (lane == 0) {
+        if (CG2) mbar_arrive_cluster(lead_tempty + 8 * buf); else mbar_arrive(bar_tempty + 8 * buf);
+      }
     }
   }
 
@@ -280,40 +323,50 @@ __global__ void __launch_bounds__(192, 1) k_conv_tc(const __grid_constant__ TcPa
   if (PAIR) cluster_sync();                  // no CTA leaves while its peer may still multicast to it
   if (warp == 4) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS));
+    if (CG2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::TMEM_COLS));
   }
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 
+// UB_TC_PAIR: 0 = no clusters, 1 = multicast weight stages, 2 (default) = cta_group::2 MMAs over CTA pairs
+int tc_pair_mode() {
+  static const int mode = getenv("UB_TC_PAIR") ? atoi(getenv("UB_TC_PAIR")) : 2;
+  return mode;
+}
+
 template <int BN, int KC, bool SHIFT_A>
-int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
+int launch_cfg(ub_ctx* ctx, TcParams& P, const act_t* w2, cudaStream_t st, bool init_only) {
   using C = Cfg<BN, KC, SHIFT_A>;
-  auto kern = k_conv_tc<BN, KC, SHIFT_A, false>;
-  auto kern_pair = k_conv_tc<BN, KC, SHIFT_A, true>;
+  auto kern = k_conv_tc<BN, KC, SHIFT_A, 0>;
+  auto kern_pair = k_conv_tc<BN, KC, SHIFT_A, 1>;
+  auto kern_cg2 = k_conv_tc<BN, KC, SHIFT_A, 2>;
   if (init_only) {
     UB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     UB_CUDA(ctx, cudaFuncSetAttribute(kern_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
+    UB_CUDA(ctx, cudaFuncSetAttribute(kern_cg2, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET));
     return UB_OK;
   }
+  const long long M = (long long)P.B * P.L.ntiles;
+  const bool cg2 = tc_pair_mode() == 2 && w2 != nullptr && BN >= 64 && M >= 2 && ctx->sm_count >= 2;
+  const int b_stage = cg2 ? C::B_STAGE / 2 : C::B_STAGE;            // per CTA
   // weights resident in shared memory when they fit beside >= 3 activation stages
-  const int resident_bytes = P.kbn * C::B_KB;
+  const int resident_bytes = P.kbn * (cg2 ? C::B_KB / 2 : C::B_KB);
   int stages;
   if (P.n_ntiles == 1 && C::HDR + resident_bytes + 3 * (3 / C::KYS) * C::A_STAGE <= SMEM_BUDGET) {
     P.b_resident = 1;
     stages = (SMEM_BUDGET - C::HDR - resident_bytes) / C::A_STAGE;
   } else {
     P.b_resident = 0;
-    stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + C::B_STAGE);
+    stages = (SMEM_BUDGET - C::HDR) / (C::A_STAGE + b_stage);
   }
   if (stages > 24) stages = 24;                // barrier header: 8 * (2 * S + 4) bytes below the head weights at +512
   if (stages < 2) return ub_fail(ctx, UB_ERR_ARG, "conv_tc: BN=%d KC=%d does not fit 2 stages", BN, KC);
   P.num_stages = stages;
-  const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * C::B_STAGE);
-  // streamed weights: CTA pairs (clusters of 2) share every weight stage by multicast
-  static const int pair_env = getenv("UB_TC_PAIR") ? atoi(getenv("UB_TC_PAIR")) : 1;
-  const long long M = (long long)P.B * P.L.ntiles;
-  if (!P.b_resident && pair_env && M >= 2 && ctx->sm_count >= 2) {
+  const int smem = C::HDR + stages * C::A_STAGE + (P.b_resident ? resident_bytes : stages * b_stage);
+  // CTA pairs (clusters of 2): cta_group::2 MMAs, or (streamed weights only) every weight stage shared by multicast
+  if (cg2 || (!P.b_resident && tc_pair_mode() == 1 && M >= 2 && ctx->sm_count >= 2)) {
     const long long pairs = (M + 1) / 2 * P.n_ntiles, max_pairs = ctx->sm_count / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * (pairs < max_pairs ? pairs : max_pairs)));
@@ -324,7 +377,8 @@ int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern_pair, P));
+    if (cg2) { P.w = w2; UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern_cg2, P)); }
+    else UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern_pair, P));
     UB_CHECK_LAUNCH(ctx);
     return UB_OK;
   }
@@ -335,9 +389,9 @@ int launch_cfg(ub_ctx* ctx, TcParams& P, cudaStream_t st, bool init_only) {
 }
 
 template <bool SHIFT_A>
-int dispatch(ub_ctx* ctx, int bn, int kc, TcParams& P, cudaStream_t st, bool init_only) {
+int dispatch(ub_ctx* ctx, int bn, int kc, TcParams& P, const act_t* w2, cudaStream_t st, bool init_only) {
 #define UB_CASE(BN_, KC_) \
-  if (bn == BN_ && kc == KC_) return launch_cfg<BN_, KC_, SHIFT_A>(ctx, P, st, init_only);
+  if (bn == BN_ && kc == KC_) return launch_cfg<BN_, KC_, SHIFT_A>(ctx, P, w2, st, init_only);
   UB_CASE(32, 16) UB_CASE(32, 32) UB_CASE(64, 16) UB_CASE(64, 32) UB_CASE(128, 16) UB_CASE(128, 32)
   UB_CASE(256, 16)
 #undef UB_CASE
@@ -351,9 +405,9 @@ static const int kTileTable[][2] = {{32, 16}, {32, 32}, {64, 16}, {64, 32}, {128
 int conv_tc_init(ub_ctx* ctx) {
   TcParams P{};
   for (auto& t : kTileTable) {
-    int r = dispatch<true>(ctx, t[0], t[1], P, nullptr, true);
+    int r = dispatch<true>(ctx, t[0], t[1], P, nullptr, nullptr, true);
     if (r != UB_OK) return r;
-    r = dispatch<false>(ctx, t[0], t[1], P, nullptr, true);
+    r = dispatch<false>(ctx, t[0], t[1], P, nullptr, nullptr, true);
     if (r != UB_OK) return r;
   }
   return UB_OK;
@@ -370,6 +424,7 @@ int conv3x3_tc(ub_ctx* ctx, const ConvLayer& Lr, const ConvArgs& a, cudaStream_t
   if (a.head_w && (Lr.cout != 32 || Lr.bn != 32)) return ub_fail(ctx, UB_ERR_ARG, "fused head needs cout == bn == 32");
   TimeScope ts(ctx, UB_T_CONV, st);
   // conv_impl 0: shifted-descriptor A operand (3 staged segments); 2: nine aligned segments
-  return ctx->conv_impl == 2 ? dispatch<false>(ctx, Lr.bn, Lr.kc, P, st, false)
-                             : dispatch<true>(ctx, Lr.bn, Lr.kc, P, st, false);
+  // (the cta_group::2 layout of the weights exists for the shifted-descriptor kernel only)
+  return ctx->conv_impl == 2 ? dispatch<false>(ctx, Lr.bn, Lr.kc, P, nullptr, st, false)
+                             : dispatch<true>(ctx, Lr.bn, Lr.kc, P, a.head_w ? nullptr : Lr.w2, st, false);
 }
