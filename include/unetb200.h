@@ -241,7 +241,9 @@ int ub_pipeline_submit_src(ub_ctx* ctx, const uint8_t* src_bgr_host, int B, int 
                            const ub_roi* roi, const ub_burr_params* params, int32_t* frame_stats_host, int slot);
 
 /* ---- run-time switches and counters ------------------------------------------------- */
-/* name = "overlap" (1: gray / edge map on a second stream beside the network, default), "check_saturation" (1: every conv
+/* name = "overlap" (1: gray / edge map on a second stream beside the network, default), "fuse_block0" (1: the first
+ * encoder block -- both convs and the pool, unetpp.py:23-26,105 -- runs as one kernel, default; 0: three launches, for A/B
+ * and parity checks), "check_saturation" (1: every conv
  * epilogue counts the outputs it clamps to the largest finite 16-bit value; 0: off.  ub_set_weights arms the check for the
  * first forward after it, so a checkpoint loaded through infer_two_stage_burr.py:214-217 whose activations overflow the
  * operand type is reported once at no steady-state cost). */

@@ -112,6 +112,30 @@ def test_fused_pool_equals_maxpool_of_layer_output(ctx, hw):
         assert torch.equal(p, F.max_pool2d(a, 2)), f"level {lvl}"
 
 
+@pytest.mark.parametrize("hw", [(128, 160), (64, 64), (48, 80), (16, 16), (32, 32), (112, 48)])
+def test_fused_block_equals_two_layers(ctx, hw):
+    """ConvBlock conv0_0 + MaxPool2d (src/models/unetpp.py:23-26,105) as ONE kernel whose 32-channel intermediate stays in
+    shared memory (csrc/conv_block.cu) against the three launches it replaces (ub_set_option "fuse_block0" 0): block
+    output, pooled plane and final logits must be equal bit for bit -- ragged last 28-column tile, one-tile images and
+    images narrower than a tile included."""
+    g = torch.Generator().manual_seed(21 + hw[0])
+    x = (torch.rand(2, 3, hw[0], hw[1], generator=g)).cuda()
+    ctx.forward(x)                                              # the first forward after set_weights runs the checked per-layer path
+    got = {}
+    for fuse in (0, 1):
+        ctx.set_option("fuse_block0", fuse)
+        n0 = ctx.launch_count()
+        y = ctx.forward(x)
+        got[fuse] = (ctx.debug_activation(2, 2, 32, hw[0], hw[1]).clone(), ctx.debug_activation(3, 2, 32, hw[0] // 2, hw[1] // 2).clone(),
+                     y.clone(), ctx.launch_count() - n0)
+    ctx.set_option("fuse_block0", 1)
+    assert got[0][3] - got[1][3] == 1, "the fused path must save exactly one launch"
+    assert float(got[0][0].max()) > 0
+    for k, name in enumerate(("block output", "pooled plane", "logits")):
+        a, b = got[0][k], got[1][k]
+        assert torch.equal(a, b), f"{name}: {int((a != b).sum())} of {a.numel()} values differ, max {float((a - b).abs().max())}"
+
+
 @pytest.mark.parametrize("li,hw", [(16, (128, 160)), (16, (72, 92)), (16, (36, 60)), (16, (16, 16)),
                                    (14, (64, 80)), (14, (36, 44)), (14, (8, 20))])
 def test_fused_upsample_equals_materialised(ctx, sd, li, hw):

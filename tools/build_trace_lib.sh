@@ -4,7 +4,7 @@
 set -e
 cd "$(dirname "$0")/../unet-_b200/csrc"
 mkdir -p ../../build/trace
-for f in api conv_tc conv_rows tmap conv_simt net_glue preprocess stage2 enhance; do
+for f in api conv_tc conv_rows conv_block tmap conv_simt net_glue preprocess stage2 enhance; do
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC \
     -DUB_ROWS_TRACE -c $f.cu -o ../../build/trace/$f.o &
 done

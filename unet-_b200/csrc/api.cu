@@ -129,6 +129,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   if ((e = cudaGetLastError()) != cudaSuccess) return ub_fail(nullptr, UB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
   ub_ctx* c = new ub_ctx();
   if (const char* ov = getenv("UB_OVERLAP")) c->overlap = atoi(ov);
+  if (const char* fb = getenv("UB_FUSE_BLOCK0")) c->fuse_block0 = atoi(fb);
   c->device = device; c->sm_count = prop.multiProcessorCount;
   c->max_batch = max_batch; c->frame_h = frame_h; c->frame_w = frame_w; c->net_h = net_h; c->net_w = net_w;
   c->num_classes = num_classes;
@@ -151,7 +152,7 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   for (int i = 0; i < 3 && !r; ++i) r = dmalloc(c, &c->d_mask[i], fpix);
   for (int i = 0; i < 4 && !r; ++i) r = dmalloc(c, &c->d_tmp[i], fpix);
   if (r) return fail(r);
-  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK || (r = enhance_init(c)) != UB_OK) return fail(r);
+  if ((r = conv_tc_init(c)) != UB_OK || (r = conv_rows_init(c)) != UB_OK || (r = conv_block_init(c)) != UB_OK || (r = enhance_init(c)) != UB_OK) return fail(r);
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
@@ -296,6 +297,7 @@ int ub_set_option(ub_ctx* ctx, const char* name, int value) {
   NEED_CTX(ctx);
   if (!name) return ub_fail(ctx, UB_ERR_ARG, "null option name");
   if (!strcmp(name, "overlap")) ctx->overlap = value != 0;
+  else if (!strcmp(name, "fuse_block0")) { ctx->fuse_block0 = value != 0; step_graphs_free(ctx); }
   else if (!strcmp(name, "check_saturation")) { ctx->sat_check = value != 0; if (!value) ctx->sat_check_once = 0; }
   else return ub_fail(ctx, UB_ERR_ARG, "unknown option \"%s\"", name);
   return UB_OK;

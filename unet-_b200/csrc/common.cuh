@@ -144,6 +144,7 @@ struct ub_ctx {
   int slot_batch[2] = {0, 0};
   uint8_t* d_src[2] = {nullptr, nullptr};   // ub_pipeline_submit_src: raw source frames per slot (allocated on first use)
   size_t src_bytes = 0;
+  int fuse_block0 = 1;                  // conv0_0 (both convs + pool) as one kernel (conv_block.cu; UB_FUSE_BLOCK0 / ub_set_option "fuse_block0")
   int overlap = 1;                      // gray + edge map on the aux stream beside the network (UB_OVERLAP / ub_set_option)
   int sat_check = 0;                    // conv epilogues count outputs that hit the 16-bit maximum (ub_set_option "check_saturation")
   int sat_check_once = 0;               // ... for the next forward only (armed by ub_set_weights)
@@ -198,6 +199,11 @@ int conv3x3_rows(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_
 int conv_rows_init(ub_ctx* ctx);
 bool conv_rows_can_pool(const ub_ctx* ctx, const ConvLayer& L);   // the layer's kernel has a fused-pool variant
 bool conv_rows_can_upsample(const ub_ctx* ctx, const ConvLayer& L);   // ... a fused-upsample variant (ConvArgs::up1)
+// conv_block.cu: ConvBlock conv0_0 (conv1 -> conv2 -> 2x2 max-pool) in one kernel, intermediate kept in shared memory
+int conv_block_init(ub_ctx* ctx);
+bool conv_block_can_fuse(const ub_ctx* ctx, const ConvLayer& l1, const ConvLayer& l2, int H, int W);
+int conv_block0(ub_ctx* ctx, const ConvLayer& l1, const ConvLayer& l2, const act_t* src, act_t* out, act_t* pool_out,
+                int B, int H, int W, cudaStream_t st);
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // activation buffers (ub_ctx::act): channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu

@@ -95,28 +95,6 @@ struct RCfg {
   static constexpr int HDR = 1024;                             // barriers, TMEM slot, bias
 };
 
-__device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "r"(lo), "r"(hi));
-  return r;
-}
-__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-// relu + saturate-to-finite + round to two 16-bit activations (lo in the low half)
-__device__ __forceinline__ uint32_t relu_pack(uint64_t v) {
-  uint32_t lo, hi, r;
-  asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
-#ifdef UB_ACT_BF16
-  asm("cvt.rn.relu.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
-#else
-  asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
-#endif
-  return r;
-}
-
 // Interpolation warp of a UPS kernel.  The eight warps form two teams that take alternate source-1 stages (so two stages
 // are interpolated concurrently); inside a team a warp = (pair of chunks of the k-block, half of the box rows), lane = box
 // column, NR = rows per warp = 2*mt+1.  A thread runs the two chunks as two independent dependency chains (the walk is
@@ -533,9 +511,14 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
       const int ncls = NCLS == 8 ? P.ncls : NCLS;
       float lg[NL];
       [[maybe_unused]] uint32_t mine[8];                       // POOL: column-pooled channels this warp will store
+      [[maybe_unused]] uint64_t lg2[3];                        // NCLS == 3: (bias, 0) + packed partial sums of even / odd channels
       if (head) {
 #pragma unroll
         for (int c = 0; c < NL; ++c) lg[c] = c < ncls ? P.head[ncls * 32 + c] : 0.f;
+        if constexpr (NCLS == 3) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) lg2[c] = pack2(__float_as_uint(lg[c]), 0u);
+        }
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -567,9 +550,17 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
             uint32_t lo, hi;
             asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
             const float f0 = fmaxf(__uint_as_float(lo), 0.f), f1 = fmaxf(__uint_as_float(hi), 0.f);   // ReLU; fp32 feeds the head directly
+            if constexpr (NCLS == 3) {
+              // packed f32x2 FMAs: the (even, odd) channel pair accumulates into the two halves of lg2[c], summed at the end
+              const uint64_t f01 = pack2(__float_as_uint(f0), __float_as_uint(f1));
 #pragma unroll
-            for (int c = 0; c < NL; ++c)
-              if (NCLS != 8 || c < ncls) lg[c] = fmaf(P.head[c * 32 + ((c0 + j + 1) & 31)], f1, fmaf(P.head[c * 32 + ((c0 + j) & 31)], f0, lg[c]));
+              for (int c = 0; c < 3; ++c)
+                lg2[c] = fma2(pack2(__float_as_uint(P.head[c * 32 + ((c0 + j) & 31)]), __float_as_uint(P.head[c * 32 + ((c0 + j + 1) & 31)])), f01, lg2[c]);
+            } else {
+#pragma unroll
+              for (int c = 0; c < NL; ++c)
+                if (NCLS != 8 || c < ncls) lg[c] = fmaf(P.head[c * 32 + ((c0 + j + 1) & 31)], f1, fmaf(P.head[c * 32 + ((c0 + j) & 31)], f0, lg[c]));
+            }
           } else {
             hv[j >> 1] = valid ? relu_pack(v) : 0u;
           }
@@ -625,6 +616,14 @@ __global__ void __launch_bounds__(UPS ? NTHREADS + UP_WARPS * 32 : NTHREADS, 1) 
               make_uint4(__vmaxu2(mine[4], o4), __vmaxu2(mine[5], o5), __vmaxu2(mine[6], o6), __vmaxu2(mine[7], o7));
         }
         pbuf ^= 1;
+      }
+      if constexpr (NCLS == 3) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          uint32_t lo, hi;
+          asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(lg2[c]));
+          lg[c] = __uint_as_float(lo) + __uint_as_float(hi);
+        }
       }
       if (head && valid) {
         const size_t hw = (size_t)L.H * L.W, pix = (size_t)y * L.W + x;

@@ -219,6 +219,17 @@ static int run_conv(ub_ctx* ctx, int li, const act_t* s0, const act_t* s1,
 
 #define RUN(x) do { int r__ = (x); if (r__ != UB_OK) return r__; } while (0)
 
+// The fused-pool epilogues write the interior of the pooled plane only: its zero border and over-read tail are set here,
+// once per shape (the P buffers have no other writer).
+static int pool_border(ub_ctx* ctx, int pslot, act_t* pooled, int C, int H, int W, cudaStream_t st) {
+  int* hw = ctx->pool_border_hw[pslot];
+  if (hw[0] != H || hw[1] != W) {
+    UB_CUDA(ctx, cudaMemsetAsync(pooled, 0, pp_bytes(ctx->max_batch, C, ctx->net_h >> (pslot + 1), ctx->net_w >> (pslot + 1)), st));
+    hw[0] = H; hw[1] = W;
+  }
+  return UB_OK;
+}
+
 // conv2 of an encoder block followed by MaxPool2d(2,2) (unetpp.py:105-108).  Where the layer's kernel has the fused
 // variant the pool is written from the conv epilogue (interior only: the pooled plane's zero border and over-read tail
 // are set here, once per shape -- the P buffers have no other writer); otherwise the pool kernel runs.
@@ -228,11 +239,7 @@ static int run_conv_pool(ub_ctx* ctx, int li, int pslot, const act_t* src, act_t
     RUN(run_conv(ctx, li, src, nullptr, out, B, H, W, st));
     return maxpool2_pp(ctx, out, B, C, H, W, pooled, st);
   }
-  int* hw = ctx->pool_border_hw[pslot];
-  if (hw[0] != H || hw[1] != W) {
-    UB_CUDA(ctx, cudaMemsetAsync(pooled, 0, pp_bytes(ctx->max_batch, C, ctx->net_h >> (pslot + 1), ctx->net_w >> (pslot + 1)), st));
-    hw[0] = H; hw[1] = W;
-  }
+  RUN(pool_border(ctx, pslot, pooled, C, H, W, st));
   return run_conv(ctx, li, src, nullptr, out, B, H, W, st, nullptr, nullptr, false, pooled);
 }
 
@@ -257,8 +264,16 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const 
   if (frames) RUN(preprocess_frames(ctx, frames, B, fh, fw, H, W, A[A_XIN], nullptr, nullptr, st));
   else RUN(nchw_to_pp(ctx, x_nchw, B, 3, H, W, A[A_XIN], 16, st));
   // encoder (unetpp.py:104-108)
-  RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));
-  RUN(run_conv_pool(ctx, 1, 0, A[A_T0], A[A_X00], A[A_P0], 32, B, H, W, st));
+  // conv0_0: one kernel for conv1 -> conv2 -> pool where the shapes allow (the armed saturation check counts inside the
+  // per-layer kernels, so that one forward takes them)
+  const bool sat_on = ctx->sat_check || ctx->sat_check_once;
+  if (!sat_on && conv_block_can_fuse(ctx, ctx->conv[0], ctx->conv[1], H, W)) {
+    RUN(pool_border(ctx, 0, A[A_P0], 32, H, W, st));
+    RUN(conv_block0(ctx, ctx->conv[0], ctx->conv[1], A[A_XIN], A[A_X00], A[A_P0], B, H, W, st));
+  } else {
+    RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));
+    RUN(run_conv_pool(ctx, 1, 0, A[A_T0], A[A_X00], A[A_P0], 32, B, H, W, st));
+  }
   RUN(run_conv(ctx, 2, A[A_P0], nullptr, A[A_T1], B, h1, w1, st));
   RUN(run_conv_pool(ctx, 3, 1, A[A_T1], A[A_X10], A[A_P1], 64, B, h1, w1, st));
   RUN(run_conv(ctx, 4, A[A_P1], nullptr, A[A_T2], B, h2, w2, st));
