@@ -152,6 +152,9 @@ def burrs_standard(gray, mask_cable, config=None, stages=None):
     cfg = config or {"min_area": 30, "max_area": 800}          # :61-67
     if mask_cable.max() == 0:                                    # :69-70
         return np.zeros_like(mask_cable)
+    contours, _ = cv2.findContours(mask_cable, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)   # :73-75 (never empty here; kept so
+    if len(contours) == 0:                                       # that the timed reference arm does the reference's work)
+        return np.zeros_like(mask_cable)
     band = _band(mask_cable, 8)                                  # :78-81
     blur = cv2.GaussianBlur(gray, (5, 5), 1.0)                   # :85
     edges = cv2.Canny(blur, 50, 150)                             # :86
@@ -170,6 +173,9 @@ def burrs_enhanced(gray, mask_cable, config=None, stages=None):
     """detect_burrs_enhanced, infer_enhanced_burr.py:69-138."""
     cfg = config or ENHANCED_CONFIG
     if mask_cable.max() == 0:                                    # :73-74
+        return np.zeros_like(mask_cable)
+    contours, _ = cv2.findContours(mask_cable, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)   # :77-79
+    if len(contours) == 0:
         return np.zeros_like(mask_cable)
     band = _band(mask_cable, 25)                                 # :82-85
     blur = cv2.GaussianBlur(gray, (5, 5), 1.0)                   # :89

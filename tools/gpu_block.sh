@@ -2,7 +2,7 @@
 # Fused conv0_0 block: parity tests (each under its own timeout: a protocol bug in a persistent kernel hangs), then A/B bench.
 TAG=${1:-r02e}
 mkdir -p gpurun_out
-timeout 180 python -m pytest tests/test_gpu_net.py -m gpu -x -q --timeout 60 -k "fused_block" > gpurun_out/${TAG}_block_tests.log 2>&1
+timeout 180 python -m pytest tests/test_gpu_net.py -m gpu -x -q --timeout 60 -k "fused_block or forward_on_frames or pipeline_vs_oracle" > gpurun_out/${TAG}_block_tests.log 2>&1
 rc=$?; echo "block tests exit $rc"; tail -15 gpurun_out/${TAG}_block_tests.log
 if [ $rc -ne 0 ]; then exit 0; fi
 timeout 600 python -m pytest tests/test_gpu_net.py tests/test_gpu_configs.py -m gpu -x -q --timeout 120 > gpurun_out/${TAG}_net_tests.log 2>&1

@@ -174,7 +174,7 @@ void ub_destroy(ub_ctx* c) {
   step_graphs_free(c);
   cudaFree(c->d_src[0]); cudaFree(c->d_src[1]); cudaFree(c->d_sat);
   for (auto& p : c->act) cudaFree(p);
-  for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.w2); cudaFree(L.bias); }
+  for (auto& L : c->conv) { cudaFree(L.w); cudaFree(L.w2); cudaFree(L.wx); cudaFree(L.bias); }
   cudaFree(c->head_w); cudaFree(c->head_b);
   cudaFree(c->d_frames); cudaFree(c->d_gray); cudaFree(c->d_pred);
   for (auto& p : c->d_mask) cudaFree(p);
@@ -271,6 +271,20 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* t, int n) {
     L.cin0 = d.cin0; L.cin1 = d.cin1; L.cout = d.cout; L.kc = d.kc; L.bn = d.bn; L.fold = d.fold;
     if (!L.w) RUN(dmalloc(ctx, &L.w, wp.size()));
     if (!L.bias) RUN(dmalloc(ctx, &L.bias, bias.size()));
+    if (li == 0) {                 // x-taps folded into K (k = kx*3 + c) for the x-im2col input of conv_block.cu: [ky][2][32][8]
+      std::vector<act_t> wx((size_t)3 * 16 * d.cout, f2a(0.f));
+      for (int co = 0; co < d.cout; ++co) {
+        const double scale = (double)g[co] / sqrt((double)var[co] + 1e-5);
+        for (int ky = 0; ky < 3; ++ky)
+          for (int kx = 0; kx < 3; ++kx)
+            for (int c = 0; c < d.real_cin0; ++c) {
+              const int k = kx * 3 + c;
+              wx[(((size_t)ky * 2 + k / 8) * d.cout + co) * 8 + k % 8] = f2a((float)((double)w[((size_t)co * cin_real + c) * 9 + ky * 3 + kx] * scale));
+            }
+      }
+      if (!L.wx) RUN(dmalloc(ctx, &L.wx, wx.size()));
+      UB_CUDA(ctx, cudaMemcpy(L.wx, wx.data(), wx.size() * sizeof(act_t), cudaMemcpyHostToDevice));
+    }
     if (d.fold || tc_pair) {
       if (!L.w2) RUN(dmalloc(ctx, &L.w2, wp2.size()));
       UB_CUDA(ctx, cudaMemcpy(L.w2, wp2.data(), wp2.size() * sizeof(act_t), cudaMemcpyHostToDevice));

@@ -90,6 +90,8 @@ struct ConvLayer {
   // fold layers, CTA-pair kernels: the same weights split by halves of N' = 3*cout,
   // [half][kblock][ky][kc/8][N'/2][8] (each CTA of a pair holds one half, contiguous)
   act_t* w2 = nullptr;
+  // layer 0 only: x-taps folded into K for the x-im2col input, [ky][2 chunks][32][8] with k = kx*3 + c (conv_block.cu)
+  act_t* wx = nullptr;
   float* bias = nullptr;
   float bias_host[64] = {0};   // host mirror of the first 64 biases (conv_rows passes them as kernel parameters)
 };
@@ -203,7 +205,7 @@ bool conv_rows_can_upsample(const ub_ctx* ctx, const ConvLayer& L);   // ... a f
 int conv_block_init(ub_ctx* ctx);
 bool conv_block_can_fuse(const ub_ctx* ctx, const ConvLayer& l1, const ConvLayer& l2, int H, int W);
 int conv_block0(ub_ctx* ctx, const ConvLayer& l1, const ConvLayer& l2, const act_t* src, act_t* out, act_t* pool_out,
-                int B, int H, int W, cudaStream_t st);
+                int B, int H, int W, unsigned long long* sat, cudaStream_t st);
 int run_conv_layer(ub_ctx* ctx, const ConvLayer& L, const ConvArgs& a, cudaStream_t st);   // picks the kernel
 
 // activation buffers (ub_ctx::act): channels and pyramid level (spatial = net >> level); order = enum in net_glue.cu
@@ -212,6 +214,7 @@ static const int kActL[23] = {0, 0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4, 4, 3, 3,
 
 // net_glue.cu
 int nchw_to_pp(ub_ctx*, const float* x, int B, int C, int H, int W, act_t* out, int Cpad, cudaStream_t);
+int nchw_to_xi(ub_ctx*, const float* x, int B, int H, int W, act_t* out, cudaStream_t);   // 3-channel input -> x-im2col PP (16 channels)
 int pp_to_nchw(ub_ctx*, const act_t* in, int B, int C, int H, int W, float* out, cudaStream_t);
 int maxpool2_pp(ub_ctx*, const act_t* in, int B, int C, int H, int W, act_t* out, cudaStream_t);
 int upsample2_pp(ub_ctx*, const act_t* in, int B, int C, int H, int W, act_t* out, cudaStream_t);
@@ -222,7 +225,7 @@ int net_forward_pp(ub_ctx*, int B, int H, int W, const float* x_nchw, const uint
 
 // preprocess.cu
 int preprocess_frames(ub_ctx*, const uint8_t* frames, int B, int H, int W, int nh, int nw,
-                      act_t* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t);
+                      act_t* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t, bool xi = false);   // xi: x-im2col network input (conv_block.cu)
 int masks_from_pred(ub_ctx*, const uint8_t* pred, int B, int nh, int nw, int H, int W, ub_roi roi,
                     uint8_t* cable, uint8_t* tape, int32_t* stats, cudaStream_t);
 int argmax_logits(ub_ctx*, const float* logits, int B, int C, int nh, int nw, uint8_t* pred, cudaStream_t);

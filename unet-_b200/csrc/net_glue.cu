@@ -30,6 +30,26 @@ __global__ void k_nchw_to_pp(const float* __restrict__ x, int B, int C, int H, i
   *reinterpret_cast<uint4*>(out + pp_off(b, chunk, nchunks, L.Ppl, L.G + q)) = v;
 }
 
+// fp32 NCHW (3 channels) -> x-im2col PP: channel k = kx*3 + c of position (y,x) = x[c][y][x + kx - 1], zero outside
+__global__ void k_nchw_to_xi(const float* __restrict__ x, int B, int H, int W, act_t* __restrict__ out, PPLayout L) {
+  int q = blockIdx.x * blockDim.x + threadIdx.x;
+  int chunk = blockIdx.y, b = blockIdx.z;
+  if (q >= L.ntiles * 128) return;
+  int yy = q / L.pitch, xx = q - yy * L.pitch;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (q < L.npos && yy >= 1 && yy <= H && xx >= 1 && xx <= W) {
+    act_t h[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = chunk * 8 + j, kx = k / 3, c = k - kx * 3, xs = xx - 1 + kx - 1;
+      const float f = (k < 9 && xs >= 0 && xs < W) ? x[(((size_t)b * 3 + c) * H + (yy - 1)) * W + xs] : 0.f;
+      h[j] = f2a(f);
+    }
+    v = *reinterpret_cast<uint4*>(h);
+  }
+  *reinterpret_cast<uint4*>(out + pp_off(b, chunk, 2, L.Ppl, L.G + q)) = v;
+}
+
 __global__ void k_pp_to_nchw(const act_t* __restrict__ in, int B, int C, int H, int W,
                              float* __restrict__ out, int nchunks, PPLayout L) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -159,6 +179,15 @@ int nchw_to_pp(ub_ctx* ctx, const float* x, int B, int C, int H, int W, act_t* o
   return UB_OK;
 }
 
+int nchw_to_xi(ub_ctx* ctx, const float* x, int B, int H, int W, act_t* out, cudaStream_t st) {
+  PPLayout L = pp_layout(H, W);
+  TimeScope ts(ctx, UB_T_GLUE, st);
+  dim3 grid(cdiv(L.ntiles * 128, 256), 2, B);
+  k_nchw_to_xi<<<grid, 256, 0, st>>>(x, B, H, W, out, L);
+  UB_CHECK_LAUNCH(ctx);
+  return UB_OK;
+}
+
 int pp_to_nchw(ub_ctx* ctx, const act_t* in, int B, int C, int H, int W, float* out,
                cudaStream_t st) {
   PPLayout L = pp_layout(H, W);
@@ -261,15 +290,16 @@ int net_forward_pp(ub_ctx* ctx, int B, int H, int W, const float* x_nchw, const 
   const int h1 = H / 2, w1 = W / 2, h2 = H / 4, w2 = W / 4, h3 = H / 8, w3 = W / 8, h4 = H / 16, w4 = W / 16;
   // (Running the high-resolution levels a few frames at a time so that their intermediates stay inside the 126 MB
   //  L2 was tried and is slower: the small launches cost more than the residency gains, profiles/r01_conv.md.)
-  if (frames) RUN(preprocess_frames(ctx, frames, B, fh, fw, H, W, A[A_XIN], nullptr, nullptr, st));
+  // conv0_0 as one kernel where the shapes allow: its first conv takes the input in x-im2col form
+  const bool sat_on = ctx->sat_check || ctx->sat_check_once;
+  const bool fuse0 = conv_block_can_fuse(ctx, ctx->conv[0], ctx->conv[1], H, W);
+  if (frames) RUN(preprocess_frames(ctx, frames, B, fh, fw, H, W, A[A_XIN], nullptr, nullptr, st, fuse0));
+  else if (fuse0) RUN(nchw_to_xi(ctx, x_nchw, B, H, W, A[A_XIN], st));
   else RUN(nchw_to_pp(ctx, x_nchw, B, 3, H, W, A[A_XIN], 16, st));
   // encoder (unetpp.py:104-108)
-  // conv0_0: one kernel for conv1 -> conv2 -> pool where the shapes allow (the armed saturation check counts inside the
-  // per-layer kernels, so that one forward takes them)
-  const bool sat_on = ctx->sat_check || ctx->sat_check_once;
-  if (!sat_on && conv_block_can_fuse(ctx, ctx->conv[0], ctx->conv[1], H, W)) {
+  if (fuse0) {
     RUN(pool_border(ctx, 0, A[A_P0], 32, H, W, st));
-    RUN(conv_block0(ctx, ctx->conv[0], ctx->conv[1], A[A_XIN], A[A_X00], A[A_P0], B, H, W, st));
+    RUN(conv_block0(ctx, ctx->conv[0], ctx->conv[1], A[A_XIN], A[A_X00], A[A_P0], B, H, W, sat_on ? ctx->d_sat : nullptr, st));
   } else {
     RUN(run_conv(ctx, 0, A[A_XIN], nullptr, A[A_T0], B, H, W, st));
     RUN(run_conv_pool(ctx, 1, 0, A[A_T0], A[A_X00], A[A_P0], 32, B, H, W, st));

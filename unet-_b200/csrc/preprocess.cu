@@ -96,12 +96,16 @@ struct SrcRot {
 constexpr int PRE_ROWS = 8, PRE_T = 288;              // 2 * 288 covers the 514-position pitch of a 512-wide plane
 static_assert(PRE_T >= 256 + PRE_ROWS, "threads 256.. load the row coefficients");
 constexpr int PRE_SMEM_MAX = 160 * 1024;
-template <bool STAGED, bool NCHW>
+// XI: the network input is written in the "x-im2col" form conv_block.cu consumes: channel k = kx*3 + c of position (y, x)
+// holds colour c of pixel (y, x + kx - 1) (zero outside the image), k = 0..8 of 16, so the first conv needs no x-taps.
+// The group's rows are collected in shared memory (8 B per position) and written out with their neighbours.
+template <bool STAGED, bool NCHW, bool XI = false>
 __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict__ frames, int B, int H, int W, int nh, int nw,
                                                     const int4* __restrict__ ty, const int4* __restrict__ tx,
                                                     act_t* __restrict__ x_pp, float* __restrict__ x_nchw, PPLayout L,
                                                     int stage_bytes) {
   extern __shared__ __align__(16) uint8_t s_src[];
+  [[maybe_unused]] uint2* s_xi = reinterpret_cast<uint2*>(s_src + stage_bytes);     // [PRE_ROWS][pitch] (r|g<<16, b)
   __shared__ act_t s_lut[256];
   __shared__ int4 s_ty[PRE_ROWS];                                // the group's row coefficients (read once per position below)
   if (threadIdx.x < 256) s_lut[threadIdx.x] = f2a(__fdiv_rn((float)threadIdx.x, 255.0f));
@@ -183,11 +187,31 @@ __global__ void __launch_bounds__(PRE_T) k_preprocess(const uint8_t* __restrict_
         v.x = h[0] | (h[1] << 16);
         v.y = h[2];                                              // channels 3..7 are zero (+0.0 in either 16-bit format)
       }
-      if (dstp) *reinterpret_cast<uint4*>(dstp + (size_t)(yy * L.pitch + xx) * 8) = v;
+      if (XI) s_xi[(yy - y0) * L.pitch + xx] = make_uint2(v.x, v.y);
+      else if (dstp) *reinterpret_cast<uint4*>(dstp + (size_t)(yy * L.pitch + xx) * 8) = v;
+    }
+  }
+  if constexpr (XI) {
+    __syncthreads();
+    const size_t chunk1 = (size_t)L.Ppl * 8;
+    for (int i = threadIdx.x; i < (y1 - y0) * L.pitch; i += PRE_T) {
+      const int r = i / L.pitch, xx = i - r * L.pitch;
+      uint4 c0 = make_uint4(0, 0, 0, 0), c1 = make_uint4(0, 0, 0, 0);
+      if (xx >= 1 && xx <= nw) {                                 // border positions stay zero
+        const uint2 m = s_xi[i], l = s_xi[i - 1], rt = s_xi[i + 1];     // borders of the row hold zeros
+        c0.x = l.x; c0.y = (l.y & 0xffffu) | (m.x << 16); c0.z = (m.x >> 16) | (m.y << 16); c0.w = rt.x;
+        c1.x = rt.y & 0xffffu;
+      }
+      act_t* o = dstp + (size_t)((y0 + r) * L.pitch + xx) * 8;
+      *reinterpret_cast<uint4*>(o) = c0;
+      *reinterpret_cast<uint4*>(o + chunk1) = c1;
     }
   }
   if (dstp && blockIdx.x + 1 == gridDim.x)                        // the tile padding behind the plane
-    for (int q = L.npos + threadIdx.x; q < L.ntiles * 128; q += PRE_T) *reinterpret_cast<uint4*>(dstp + (size_t)q * 8) = make_uint4(0, 0, 0, 0);
+    for (int q = L.npos + threadIdx.x; q < L.ntiles * 128; q += PRE_T) {
+      *reinterpret_cast<uint4*>(dstp + (size_t)q * 8) = make_uint4(0, 0, 0, 0);
+      if (XI) *reinterpret_cast<uint4*>(dstp + (size_t)L.Ppl * 8 + (size_t)q * 8) = make_uint4(0, 0, 0, 0);
+    }
 }
 
 // cv2.cvtColor(BGR2GRAY) (infer_two_stage_burr.py:317): (3735 B + 19235 G + 9798 R + 2^14) >> 15
@@ -351,7 +375,7 @@ __global__ void k_stats_init(int32_t* stats, int B) {
 }  // namespace
 
 int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, int nh, int nw,
-                      act_t* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t st) {
+                      act_t* x_pp, float* x_nchw, uint8_t* gray, cudaStream_t st, bool xi) {
   if (x_pp || x_nchw) {
     const int4 *ty, *tx;
     int r = get_table(ctx, H, nh, false, &ty, st); if (r) return r;
@@ -362,11 +386,16 @@ int preprocess_frames(ub_ctx* ctx, const uint8_t* frames, int B, int H, int W, i
     // source rows under PRE_ROWS output rows: the taps of the first and last row are (PRE_ROWS-1)*H/nh apart, + the second tap
     const size_t stage = ((size_t)((PRE_ROWS - 1) * (size_t)H / nh + 3) * W * 3 + 32 + 15) & ~(size_t)15;
     static const int staged_env = getenv("UB_PRE_STAGED") ? atoi(getenv("UB_PRE_STAGED")) : 1;
+    const size_t xi_bytes = xi ? (size_t)PRE_ROWS * L.pitch * sizeof(uint2) : 0;
     auto launch = [&](auto kern, size_t smem) {
-      if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_MAX);
-      kern<<<grid, PRE_T, smem, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, (int)smem);
+      if (smem + xi_bytes > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_MAX + 40 * 1024);
+      kern<<<grid, PRE_T, smem + xi_bytes, st>>>(frames, B, H, W, nh, nw, ty, tx, x_pp, x_nchw, L, (int)smem);
     };
-    if (staged_env && stage <= (size_t)PRE_SMEM_MAX) {
+    if (xi) {
+      if (!x_pp || x_nchw || xi_bytes > 40 * 1024) return ub_fail(ctx, UB_ERR_ARG, "preprocess: x-im2col output needs a PP destination and a plane at most 638 wide");
+      if (staged_env && stage <= (size_t)PRE_SMEM_MAX) launch(k_preprocess<true, false, true>, stage);
+      else launch(k_preprocess<false, false, true>, 0);
+    } else if (staged_env && stage <= (size_t)PRE_SMEM_MAX) {
       if (x_nchw) launch(k_preprocess<true, true>, stage); else launch(k_preprocess<true, false>, stage);
     } else {
       if (x_nchw) launch(k_preprocess<false, true>, 0); else launch(k_preprocess<false, false>, 0);
