@@ -116,6 +116,26 @@ int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, in
 int ub_overlay(ub_ctx* ctx, const uint8_t* frames_bgr_dev, const uint8_t* mask_cable_dev, const uint8_t* mask_tape_dev,
                const uint8_t* mask_burr_dev, int B, int H, int W, const ub_roi* roi, uint8_t* out_bgr_dev, void* stream);
 
+/* The contour half of visualize_two_stage (infer_two_stage_burr.py:160-165; infer_enhanced_burr.py:181-187):
+ * cv2.findContours(mask, RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(img, contours, -1, (b,g,r), 2) in place on
+ * frames u8 [B,H,W,3] BGR, mask u8 [B,H,W] (non-zero = set) -- byte-identical to OpenCV's result: the exterior background
+ * is flooded per frame in shared memory, every foreground pixel next to it paints the thickness-2 stamps of its border
+ * steps (csrc/annotate.cu).  Thickness 2 only (cable and tape; the burr contours' thickness 3 stays with cv2 on the host:
+ * OpenCV's odd-thickness rasteriser is not translation invariant near the image border).  (H+2) x (W/32+2) x 8 bytes must
+ * fit 200 KB of shared memory (any frame up to 800 x 448 / 1024 x 576). */
+int ub_draw_contours(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* mask_dev, int B, int H, int W, int b, int g, int r, void* stream);
+
+/* Paints what the host rasterised -- the ROI box and label (infer_two_stage_burr.py:156-158), Hershey text -- over frames
+ * u8 [B,H,W,3] on the device: frames[q] = colour[layer[q] - 1] where layer[q] is 1, 2 or 3.  layer u8 [H,W] shared by the
+ * batch (per_frame = 0) or [B,H,W]; bgr9: three BGR triples in HOST memory. */
+int ub_paint_layer(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* layer_dev, int per_frame, int B, int H, int W,
+                   const uint8_t* bgr9_host, void* stream);
+
+/* The 5x5 stamp (bit (dy+2)*5 + dx+2) ub_draw_contours paints for a unit border step in chain-code direction `code` (0..7:
+ * E, NE, N, NW, W, SW, S, SE) or for a single point (code 8) at `thickness` 2; 0 for anything else.  Lets the CPU tests
+ * compare the tables with cv2.line of the installed OpenCV.  No context, no device. */
+unsigned int ub_contour_stamp(int thickness, int code);
+
 /* compute_diameter_metrics (src/utils/geometry_enhanced.py:113-187): pred u8 [B,H,W] class ids -> out int32 [B][8] =
  * { dc_px, dt_px (binary32 bit patterns: medians of the Gaussian-smoothed row widths of the largest cable / tape
  * component over the rows where both are > 0; 0 when valid_rows < min_valid_rows), valid_rows, cable_area, tape_area

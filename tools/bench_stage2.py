@@ -48,17 +48,18 @@ def measure(B=512, reps=10, log=None):
     rows = [
         ("ub_overlay: 4 x addWeighted blend (LUT kernel)", lambda: ctx.overlay(frames3, mask, mask_t, mask_b, roi), 9 * P),
         ("ub_preprocess gray only: BGR2GRAY", lambda: ctx.preprocess(frames3, want_x=False, want_gray=True), 4 * P),
-        ("ub_gaussian5: k_edge_fused<2>", lambda: ctx.gaussian5(gray), 2 * P),
-        ("ub_blur_canny: k_edge_fused<1> + union-find hysteresis", lambda: ctx.blur_canny(gray, 50, 150), 2 * P),
-        ("ub_burr: edges + band + morphology + CCL + filter", lambda: ctx.burr(gray, mask), 3 * P),
+        ("ub_gaussian5: GaussianBlur 5x5 (k_blur5_cols)", lambda: ctx.gaussian5(gray), 2 * P),
+        ("ub_blur_canny: k_edge_fused<1> + flood hysteresis (k_hyst_frame)", lambda: ctx.blur_canny(gray, 50, 150), 2 * P),
+        ("ub_burr: edges + hysteresis + morphology chain (k_burr_chain_cols) + CCL + filter", lambda: ctx.burr(gray, mask), 3 * P),
         ("ub_ccl: connectedComponentsWithStats, labels in OpenCV order + stats", lambda: ctx.ccl(cand), 5 * P),
         ("ub_diameter_metrics: 2 x (CCL + largest component + row extents) + smoothing + medians", lambda: ctx.diameter_metrics(preds), P),
         ("ub_analyze_defects: 3 x CCL + CLOSE 5x5 + class histogram", lambda: ctx.analyze_defects(preds), P),
-        ("ub_morph close 3x3 (k_morph_words)", lambda: ctx.morph("close", 3, mask), 2 * P),
-        ("ub_morph dilate 8x8 (k_morph_words)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
+        ("ub_morph close 3x3 (k_morph_cols)", lambda: ctx.morph("close", 3, mask), 2 * P),
+        ("ub_morph dilate 8x8 (k_morph_cols)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
     ]
     out = {"frames": B, "hw": [H, W], "hbm_peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(pk) else "fallback",
-           "edge_fused": os.environ.get("UB_EDGE_FUSED", "1"), "ops": []}
+           "edge_fused": os.environ.get("UB_EDGE_FUSED", "1"),
+           "env": {k: os.environ[k] for k in ("UB_BLUR_COLS", "UB_MORPH_WORDS", "UB_BURR_COLS", "UB_EDGE_COLS") if k in os.environ}, "ops": []}
     for name, fn, nbytes in rows:
         ms = timed(fn)
         gbs = nbytes * B / ms / 1e6

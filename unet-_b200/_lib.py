@@ -56,6 +56,9 @@ SIGNATURES = {
     "ub_normalize_frames": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P]),
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
     "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
+    "ub_draw_contours": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "ub_paint_layer": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P]),
+    "ub_contour_stamp": (C.c_uint, [_I, _I]),
     "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_analyze_defects": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_width_profiles": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -247,6 +250,21 @@ class Context:
                                      self._dev(mask_tape, torch.uint8), self._dev(mask_burr, torch.uint8), b, h, w,
                                      C.byref(r), out.data_ptr(), self.stream))
         return out
+
+    def draw_contours(self, frames, mask, bgr):
+        """cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(.., bgr, 2) in place: frames u8 [B,H,W,3], mask u8 [B,H,W]."""
+        b, h, w, _ = frames.shape
+        self._check(lib().ub_draw_contours(self._h, self._dev(frames, torch.uint8), self._dev(mask, torch.uint8), b, h, w,
+                                           int(bgr[0]), int(bgr[1]), int(bgr[2]), self.stream))
+        return frames
+
+    def paint_layer(self, frames, layer, colours):
+        """frames[q] = colours[layer[q] - 1] where layer[q] != 0, in place; layer u8 [H,W] (shared) or [B,H,W]; up to three BGR colours."""
+        b, h, w, _ = frames.shape
+        c9 = (C.c_uint8 * 9)(*([int(v) for c in colours for v in c] + [0] * 9)[:9])
+        self._check(lib().ub_paint_layer(self._h, self._dev(frames, torch.uint8), self._dev(layer, torch.uint8), int(layer.dim() == 3),
+                                         b, h, w, c9, self.stream))
+        return frames
 
     def diameter_metrics(self, pred, cable_cls=1, tape_cls=2, min_area=50, min_valid_rows=20):
         """pred u8 [B,H,W] class ids -> int32 [B,8] (dc_px / dt_px as float32 bit patterns, valid_rows, cable_area, tape_area)."""

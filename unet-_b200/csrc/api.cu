@@ -45,7 +45,10 @@ int overlay_impl(ub_ctx*, const uint8_t*, const uint8_t*, const uint8_t*, const 
 int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t);
 int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
 int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
-int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t);
+int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t, int phase = 0);
+int draw_contours_impl(ub_ctx*, uint8_t*, const uint8_t*, int, int, int, int, int, int, cudaStream_t);
+int paint_layer_impl(ub_ctx*, uint8_t*, const uint8_t*, int, int, int, int, const uint8_t*, cudaStream_t);
+uint32_t contour_stamp(int, int);
 int diameter_metrics(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int analyze_defects(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int width_profiles(ub_ctx*, const uint8_t*, int, int, int, int, int, float*, cudaStream_t);
@@ -385,6 +388,22 @@ int ub_overlay(ub_ctx* ctx, const uint8_t* frames, const uint8_t* mc, const uint
   return overlay_impl(ctx, frames, mc, mt, mb, B, H, W, *roi, out, as_stream(stream));
 }
 
+int ub_draw_contours(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B, int H, int W, int b, int g, int r, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || !mask) return ub_fail(ctx, UB_ERR_ARG, "ub_draw_contours: null pointer");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return draw_contours_impl(ctx, frames, mask, B, H, W, b, g, r, as_stream(stream));
+}
+
+int ub_paint_layer(ub_ctx* ctx, uint8_t* frames, const uint8_t* layer, int per_frame, int B, int H, int W, const uint8_t* bgr9, void* stream) {
+  NEED_CTX(ctx);
+  if (!frames || !layer || !bgr9) return ub_fail(ctx, UB_ERR_ARG, "ub_paint_layer: null pointer");
+  RUN(check_frame_shape(ctx, B, H, W));
+  return paint_layer_impl(ctx, frames, layer, per_frame, B, H, W, bgr9, as_stream(stream));
+}
+
+unsigned int ub_contour_stamp(int thickness, int code) { return contour_stamp(thickness, code); }
+
 int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int min_area,
                         int min_valid_rows, int32_t* out, void* stream) {
   NEED_CTX(ctx);
@@ -564,9 +583,19 @@ int ub_pipeline(ub_ctx* ctx, const uint8_t* frames, int B, int variant, const ub
     UB_CUDA(ctx, cudaStreamWaitEvent(sa, ctx->ev_fork, 0));
   }
   RUN(preprocess_frames(ctx, frames, B, H, W, nh, nw, nullptr, nullptr, ctx->d_gray, sa));          // gray only
-  RUN(burr_edges(ctx, variant, ctx->d_gray, B, H, W, p, sa));
-  if (overlap_env) UB_CUDA(ctx, cudaEventRecord(ctx->ev_join, sa));
+  // hyst_late: the short-CTA stencils run beside the network, the per-frame hysteresis flood (one long-running CTA per frame) only
+  // once the last conv kernel has been issued -- beside k_masks -- so that it never holds an SM a persistent conv kernel needs
+  static const int late_env = getenv("UB_HYST_LATE") ? atoi(getenv("UB_HYST_LATE")) : 1;
+  const bool late = overlap_env && late_env;
+  RUN(burr_edges(ctx, variant, ctx->d_gray, B, H, W, p, sa, late ? 1 : 0));
+  if (overlap_env && !late) UB_CUDA(ctx, cudaEventRecord(ctx->ev_join, sa));
   RUN(net_forward_pp(ctx, B, nh, nw, nullptr, frames, H, W, nullptr, ctx->d_pred, st));               // preprocess fused per sub-batch
+  if (late) {
+    UB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
+    UB_CUDA(ctx, cudaStreamWaitEvent(sa, ctx->ev_fork, 0));
+    RUN(burr_edges(ctx, variant, ctx->d_gray, B, H, W, p, sa, 2));
+    UB_CUDA(ctx, cudaEventRecord(ctx->ev_join, sa));
+  }
   RUN(masks_from_pred(ctx, ctx->d_pred, B, nh, nw, H, W, r, cable, tape, frame_stats, st));
   if (overlap_env) UB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join, 0));
   RUN(burr_finish(ctx, cable, B, H, W, p, burr, frame_stats + 3, 4, st));

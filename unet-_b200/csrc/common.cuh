@@ -241,7 +241,7 @@ int sharpen3(ub_ctx*, const uint8_t* src, uint8_t* dst, int B, int H, int W, cud
 int enhance_frames(ub_ctx*, const uint8_t* frames, uint8_t* out, int B, int H, int W, cudaStream_t);
 
 // stage2.cu
-int burr_edges(ub_ctx*, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& p, cudaStream_t);
+int burr_edges(ub_ctx*, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& p, cudaStream_t, int phase = 0);
 int burr_finish(ub_ctx*, const uint8_t* mask, int B, int H, int W, const ub_burr_params& p, uint8_t* burr,
                 int32_t* burr_px, int px_stride, cudaStream_t);
 int burr_stage(ub_ctx*, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,

@@ -245,6 +245,7 @@ __global__ void __launch_bounds__(256) k_edge_fused(const uint8_t* __restrict__ 
     const size_t wb = ((size_t)blockIdx.z * H + y) * Wd + wg;
     bits[wb] = cand;
     strong[wb] = str;
+    if (!lab_all) continue;                       // hysteresis by flood (k_hyst_frame): no union-find entries
     int* l = lab_all + fbase + (size_t)y * W + 32 * wg;
     uint32_t cbits = cand;
     while (cbits) {

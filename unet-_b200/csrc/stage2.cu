@@ -5,6 +5,7 @@
 #include <limits.h>
 #include <stdlib.h>
 #include <math.h>
+#include <utility>
 #include "stage2_kernels.cuh"
 
 namespace s2 {
@@ -276,6 +277,10 @@ __device__ __forceinline__ void store_bits_as_bytes(uint8_t* __restrict__ o, uin
     for (int k = 0; k < nvalid && k < 32; ++k) o[k] = ((word >> k) & 1u) ? (uint8_t)value : 0;
   }
 }
+
+}  // namespace s2
+#include "cols_kernels.cuh"
+namespace s2 {
 
 // Canny hysteresis: flag[root] = 1 for components holding a strong pixel, then keep flagged runs
 __global__ void __launch_bounds__(256) k_cclb_hyst_mark(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ strong,
@@ -549,6 +554,50 @@ static bool make_footprint(int k, Footprint& fp) {
   return true;
 }
 
+// the rows of a footprint ordered so that every run contains the one before it (k_morph_cols extends one accumulated word
+// run by run); false when the runs are not nested (never for cv2's ellipses)
+static bool sort_footprint(const Footprint& fp, Footprint& out) {
+  out = fp;
+  for (int i = 1; i < out.nrows; ++i)                          // insertion sort by run width
+    for (int j = i; j > 0 && (out.xb[j] - out.xa[j]) < (out.xb[j - 1] - out.xa[j - 1]); --j) {
+      std::swap(out.dy[j], out.dy[j - 1]); std::swap(out.xa[j], out.xa[j - 1]); std::swap(out.xb[j], out.xb[j - 1]);
+    }
+  for (int j = 1; j < out.nrows; ++j)
+    if (out.xa[j] > out.xa[j - 1] || out.xb[j] < out.xb[j - 1]) return false;
+  return out.top + out.bottom + 1 <= 32 && out.nrows >= 1;
+}
+
+// does the compile-time table FpT<K> equal the sorted run-time footprint of size K ?
+template <int K>
+static bool fp_table_matches(const Footprint& fs) {
+  using F = FpT<K>;
+  if (fs.nrows != F::N || fs.top != F::TOP || fs.bottom != F::BOT) return false;
+  for (int j = 0; j < F::N; ++j)
+    if (fs.dy[j] != F::dy(j) || fs.xa[j] != F::xa(j) || fs.xb[j] != F::xb(j)) return false;
+  return true;
+}
+static bool fp_table_ok(int k, const Footprint& fs) {
+  switch (k) {
+    case 2: return fp_table_matches<2>(fs);
+    case 3: return fp_table_matches<3>(fs);
+    case 5: return fp_table_matches<5>(fs);
+    case 8: return fp_table_matches<8>(fs);
+    case 25: return fp_table_matches<25>(fs);
+    default: return false;
+  }
+}
+
+template <int K>
+static void launch_morph_cols(int op, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const uint8_t* src, uint8_t* dst, int H, int W,
+                              const Footprint& fs, int value, int nstrips, int nblk, int R, int RS) {
+  switch (op) {
+    case 0: k_morph_cols<0, K><<<grid, block, smem, st>>>(src, dst, H, W, fs, (uint32_t)value, nstrips, nblk, R, RS); break;
+    case 1: k_morph_cols<1, K><<<grid, block, smem, st>>>(src, dst, H, W, fs, (uint32_t)value, nstrips, nblk, R, RS); break;
+    case 2: k_morph_cols<2, K><<<grid, block, smem, st>>>(src, dst, H, W, fs, (uint32_t)value, nstrips, nblk, R, RS); break;
+    default: k_morph_cols<3, K><<<grid, block, smem, st>>>(src, dst, H, W, fs, (uint32_t)value, nstrips, nblk, R, RS); break;
+  }
+}
+
 static int morph_once(ub_ctx* ctx, bool dil, int k, const uint8_t* src, uint8_t* dst, int B, int H, int W, int value,
                       const uint8_t* notmask, cudaStream_t st) {
   Footprint fp;
@@ -575,11 +624,36 @@ static void launch_morph_words(int op, dim3 grid, cudaStream_t st, const uint8_t
 // op: 0 dilate, 1 erode, 2 close (dilate->erode), 3 open (erode->dilate); tmp only for the per-pixel fallback (UB_MORPH_WORDS=0)
 int morph_op(ub_ctx* ctx, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* tmp, int B, int H, int W, int value, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_STENCIL, st);
-  static const int words_env = getenv("UB_MORPH_WORDS") ? atoi(getenv("UB_MORPH_WORDS")) : 1;
+  static const int words_env = getenv("UB_MORPH_WORDS") ? atoi(getenv("UB_MORPH_WORDS")) : 2;   // 2: column-walking, 1: tiled words, 0: per pixel
   if (op < 0 || op > 3) return ub_fail(ctx, UB_ERR_ARG, "bad morph op %d", op);
   if (words_env) {
     Footprint fp;
     if (!make_footprint(k, fp)) return ub_fail(ctx, UB_ERR_ARG, "ellipse size %d unsupported (1..25)", k);
+    Footprint fs;
+    if (words_env >= 2 && sort_footprint(fp, fs)) {           // column-walking kernel (cols_kernels.cuh)
+      const int nrings = op >= 2 ? 2 : 1, reach = nrings * (fp.top + fp.bottom);
+      int RS = 4;
+      while (RS < fp.top + fp.bottom + 1) RS *= 2;
+      const int warps = (size_t)8 * nrings * RS * 128 <= 48 * 1024 ? 8 : 4;
+      const int Wd = (W + 31) / 32, nstrips = cdiv(Wd, MC_VALID);
+      int R = reach * 2 > 32 ? reach * 2 : 32;
+      if (R > H) R = H;
+      const int nblk = cdiv(H, R);
+      const dim3 grid(cdiv(nstrips * nblk, warps), 1, B), block(32, warps);
+      const size_t smem = (size_t)warps * nrings * RS * 128;
+      static const int tab_env = getenv("UB_MORPH_TABLES") ? atoi(getenv("UB_MORPH_TABLES")) : 1;
+      const int kt = tab_env && fp_table_ok(k, fs) ? k : 0;      // a compile-time footprint when the size is one of the reference's
+      switch (kt) {
+        case 2: launch_morph_cols<2>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+        case 3: launch_morph_cols<3>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+        case 5: launch_morph_cols<5>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+        case 8: launch_morph_cols<8>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+        case 25: launch_morph_cols<25>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+        default: launch_morph_cols<0>(op, grid, block, smem, st, src, dst, H, W, fs, value, nstrips, nblk, R, RS); break;
+      }
+      UB_CHECK_LAUNCH(ctx);
+      return UB_OK;
+    }
     const int halo = (op >= 2 ? 2 : 1) * (k / 2);          // rows the operator reaches above / below (anchor k/2)
     dim3 grid(cdiv(W, FM_W), cdiv(H, FM_TH), B);
     if (halo <= 4) launch_morph_words<4>(op, grid, st, src, dst, H, W, fp, value);
@@ -629,6 +703,22 @@ static dim3 edge_fused_grid(int B, int H, int W) { return dim3(cdiv(W, EF_TW), c
 
 int gaussian5(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t st) {
   TimeScope ts(ctx, UB_T_STENCIL, st);
+  static const int cols_env = getenv("UB_BLUR_COLS") ? atoi(getenv("UB_BLUR_COLS")) : 1;
+  if (cols_env && edge_fused_ok(src, dst, W)) {                // column-walking kernel (cols_kernels.cuh)
+    const int nstrips = cdiv(W / 4, BC_VALID), spc = nstrips < 8 ? nstrips : 8, gx = cdiv(nstrips, spc);
+    // rows per warp: a multiple of five (the register window's period) that balances the 4-row halo against whole waves
+    // of CTAs (2048 threads per SM)
+    const long slots = (long)ctx->sm_count * (2048 / (32 * spc));
+    int R = 5; double best = 1e30;
+    for (int r = 10; r <= 160; r += 5) {
+      const long ctas = (long)B * gx * cdiv(H, r);
+      const double cost = (double)((ctas + slots - 1) / slots) * (r + 4 + 6);    // + a fixed start-up term per CTA
+      if (cost < best) { best = cost; R = r; }
+    }
+    k_blur5_cols<<<dim3(gx, cdiv(H, R), B), dim3(32, spc), 0, st>>>(src, dst, H, W, nstrips, R);
+    UB_CHECK_LAUNCH(ctx);
+    return UB_OK;
+  }
   if (edge_fused_ok(src, dst, W)) {
     k_edge_fused<2><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, dst, nullptr, nullptr, nullptr, H, W, (W + 31) / 32, 0, 0);
     UB_CHECK_LAUNCH(ctx);
@@ -641,17 +731,40 @@ int gaussian5(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W
 
 // cv2.Canny: candidates (stencil) then hysteresis (union-find).  cand: u8 scratch, lab: i32 scratch.
 // blur != 0: src is the gray plane and the 5x5 blur is done inside the fused kernel (GaussianBlur + Canny of the burr stage).
-static int canny_fused(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int* lab, int B, int H, int W, int low, int high, int blur, cudaStream_t st) {
+// phase: 0 = candidates + hysteresis, 1 = the candidate kernel only, 2 = the hysteresis only (ub_pipeline runs the per-frame flood
+// CTAs after the network so that no long-running CTA holds an SM a persistent conv kernel is waiting for); the union-find
+// path does all its work in phase 1
+static int canny_fused(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int* lab, int B, int H, int W, int low, int high, int blur, cudaStream_t st,
+                       int phase = 0) {
   const int Wd = (W + 31) / 32;
   const size_t nwords = (size_t)B * H * Wd;
   uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
   uint32_t* strong = bits + nwords;
   uint8_t* flag = reinterpret_cast<uint8_t*>(ctx->d_comp);
-  {
+  // hysteresis as an in-shared-memory flood, one CTA per frame, when both bit planes of a frame fit (cols_kernels.cuh)
+  static const int hyst_env = getenv("UB_HYST_FRAME") ? atoi(getenv("UB_HYST_FRAME")) : 1;
+  const size_t hf_smem = (size_t)2 * (H + 2) * (Wd + 2) * sizeof(uint32_t);
+  const bool hyst_frame = hyst_env && hf_smem <= 200 * 1024;
+  if (hyst_frame) lab = nullptr;                              // no union-find entries wanted from the edge kernel
+  if (phase == 2 && !hyst_frame) return UB_OK;
+  if (phase != 2) {
     TimeScope ts(ctx, UB_T_STENCIL, st);
     if (blur) k_edge_fused<1><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, nullptr, bits, strong, lab, H, W, Wd, low, high);
     else k_edge_fused<0><<<edge_fused_grid(B, H, W), 256, 0, st>>>(src, nullptr, bits, strong, lab, H, W, Wd, low, high);
     UB_CHECK_LAUNCH(ctx);
+  }
+  if (hyst_frame && phase == 1) return UB_OK;
+  if (hyst_frame) {
+    TimeScope ts(ctx, UB_T_CCL, st);
+    static bool attr_set[64] = {false};
+    if (ctx->device >= 0 && ctx->device < 64 && !attr_set[ctx->device]) {
+      UB_CUDA(ctx, cudaFuncSetAttribute(k_hyst_frame, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_set[ctx->device] = true;
+    }
+    int nthr = H * Wd >= 4096 ? 1024 : (H * Wd >= 1024 ? 512 : 128);
+    k_hyst_frame<<<B, nthr, hf_smem, st>>>(bits, strong, dst, H, W, Wd);
+    UB_CHECK_LAUNCH(ctx);
+    return UB_OK;
   }
   TimeScope ts(ctx, UB_T_CCL, st);
   dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
@@ -697,8 +810,9 @@ int canny(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, uint8_t* cand, int* lab
 }
 
 // GaussianBlur((5,5),1.0) -> Canny(low, high); scratch: d_tmp[0] (blurred plane), d_tmp[2], d_lab[0..1], d_comp
-int blur_canny(ub_ctx* ctx, const uint8_t* gray, uint8_t* dst, int B, int H, int W, int low, int high, cudaStream_t st) {
-  if (edge_fused_ok(gray, gray, W)) return canny_fused(ctx, gray, dst, ctx->d_lab[0], B, H, W, low, high, 1, st);
+int blur_canny(ub_ctx* ctx, const uint8_t* gray, uint8_t* dst, int B, int H, int W, int low, int high, cudaStream_t st, int phase) {
+  if (edge_fused_ok(gray, gray, W)) return canny_fused(ctx, gray, dst, ctx->d_lab[0], B, H, W, low, high, 1, st, phase);
+  if (phase == 2) return UB_OK;
   RUN(gaussian5(ctx, gray, ctx->d_tmp[0], B, H, W, st));
   return canny(ctx, ctx->d_tmp[0], dst, ctx->d_tmp[2], ctx->d_lab[0], B, H, W, low, high, st);
 }
@@ -794,20 +908,24 @@ int ccl_export(ub_ctx* ctx, const uint8_t* src, int B, int H, int W, int* labels
 
 // First half of the burr stage: the edge map, which depends on the gray frame only (not on the net's masks), so
 // ub_pipeline runs it on a second stream beside the network.  Result in ctx->d_tmp[1].
-int burr_edges(ub_ctx* ctx, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& P, cudaStream_t st) {
+// phase: 0 = everything, 1 = what can run beside the network without holding SMs for long (gray-only stencils),
+// 2 = the rest (per-frame hysteresis flood, the enhanced variant's extra edge maps); see canny_fused
+int burr_edges(ub_ctx* ctx, int variant, const uint8_t* gray, int B, int H, int W, const ub_burr_params& P, cudaStream_t st, int phase) {
   uint8_t* t1 = ctx->d_tmp[1];
-  if (variant == UB_VARIANT_LAPLACIAN)        // src/refactor/burr_detector.py:44-51: wrapped |Laplacian| > threshold, nothing else
+  if (variant == UB_VARIANT_LAPLACIAN) {      // src/refactor/burr_detector.py:44-51: wrapped |Laplacian| > threshold, nothing else
+    if (phase == 2) return UB_OK;
     return enh_edges(ctx, gray, B, H, W, 2, 0, P.canny_low, nullptr, t1, st);
+  }
   // edges: blur -> Canny (-> | Sobel | Laplacian for the enhanced variant)        [t1]
-  RUN(blur_canny(ctx, gray, t1, B, H, W, P.canny_low, P.canny_high, st));
-  if (variant == UB_VARIANT_ENHANCED) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
+  RUN(blur_canny(ctx, gray, t1, B, H, W, P.canny_low, P.canny_high, st, phase));
+  if (variant == UB_VARIANT_ENHANCED && phase != 1) RUN(enh_edges(ctx, gray, B, H, W, 3, 50, 15, t1, t1, st));
   return UB_OK;
 }
 
 // The whole burr stage for a batch.
 int burr_stage(ub_ctx* ctx, int variant, const uint8_t* gray, const uint8_t* mask, int B, int H, int W,
                const ub_burr_params& P, uint8_t* burr, int32_t* burr_px, int px_stride, cudaStream_t st) {
-  RUN(burr_edges(ctx, variant, gray, B, H, W, P, st));
+  RUN(burr_edges(ctx, variant, gray, B, H, W, P, st, 0));
   return burr_finish(ctx, mask, B, H, W, P, burr, burr_px, px_stride, st);
 }
 
@@ -822,6 +940,46 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
   MorphChain mc;
   const bool fp_ok = make_footprint(P.band_k, mc.band) && make_footprint(P.close_k, mc.close) && make_footprint(P.open_k, mc.open);
   if (!fp_ok) return ub_fail(ctx, UB_ERR_ARG, "ellipse sizes %d/%d/%d unsupported (1..25)", P.band_k, P.close_k, P.open_k);
+  static const int cols_env = getenv("UB_BURR_COLS") ? atoi(getenv("UB_BURR_COLS")) : 1;
+  static const int packed_env0 = getenv("UB_CCL_PACKED") ? atoi(getenv("UB_CCL_PACKED")) : 1;
+  MorphChain ms;
+  if (cols_env && packed_env0 && sort_footprint(mc.band, ms.band) && sort_footprint(mc.close, ms.close) && sort_footprint(mc.open, ms.open) &&
+      P.band_k / 2 + 2 * (P.close_k / 2) + 2 * (P.open_k / 2) <= 31) {
+    // band, candidates, CLOSE, OPEN on one walk down 32-pixel-per-lane strips (cols_kernels.cuh); writes the packed candidate
+    // rows and their run starts' union-find entries directly, so k_cclb_init and the u8 candidate plane drop out
+    const int Wd = (W + 31) / 32, nstrips = cdiv(Wd, MC_VALID);
+    uint32_t* bits = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
+    {
+      TimeScope ts(ctx, UB_T_STENCIL, st);
+      int RS = 4;
+      while (RS < mc.band.top + mc.band.bottom + 1 || RS < mc.close.top + mc.close.bottom + 1 || RS < mc.open.top + mc.open.bottom + 1) RS *= 2;
+      const int warps = (size_t)8 * 6 * RS * 128 <= 48 * 1024 ? 8 : ((size_t)4 * 6 * RS * 128 <= 48 * 1024 ? 4 : 2);
+      // rows per warp: about 40 warps per SM when the batch is small (the walk is a serial chain), 32..64 rows when it is large
+      long want = ((long)B * H * nstrips + (long)ctx->sm_count * 40 - 1) / ((long)ctx->sm_count * 40);
+      int R = want < 8 ? 8 : (want > 64 ? 64 : (int)want);
+      if (R > H) R = H;
+      const int nblk = cdiv(H, R);
+      static const int tab_env = getenv("UB_MORPH_TABLES") ? atoi(getenv("UB_MORPH_TABLES")) : 1;
+      const bool tabs = tab_env && fp_table_ok(P.band_k, ms.band) && fp_table_ok(P.close_k, ms.close) && fp_table_ok(P.open_k, ms.open);
+      const dim3 grid(cdiv(nstrips * nblk, warps), 1, B), block(32, warps);
+      const size_t smem = (size_t)warps * 6 * RS * 128;
+      if (tabs && P.band_k == 8 && P.close_k == 3 && P.open_k == 2)          // infer_two_stage_burr.py:78-97
+        k_burr_chain_cols<8, 3, 2><<<grid, block, smem, st>>>(mask, t1, nullptr, bits, lab, H, W, ms, nstrips, nblk, R, RS);
+      else if (tabs && P.band_k == 25 && P.close_k == 5 && P.open_k == 3)    // infer_enhanced_burr.py:82-116
+        k_burr_chain_cols<25, 5, 3><<<grid, block, smem, st>>>(mask, t1, nullptr, bits, lab, H, W, ms, nstrips, nblk, R, RS);
+      else
+        k_burr_chain_cols<0, 0, 0><<<grid, block, smem, st>>>(mask, t1, nullptr, bits, lab, H, W, ms, nstrips, nblk, R, RS);
+      UB_CHECK_LAUNCH(ctx);
+    }
+    TimeScope ts(ctx, UB_T_CCL, st);
+    dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
+    k_cclb_merge<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd);
+    k_cclb_flatten<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
+    k_cclb_filter<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, P, burr, burr_px, px_stride);
+    UB_CHECK_LAUNCH_N(ctx, 4);
+    return UB_OK;
+  }
   if (fuse_env && 2 * (P.open_k / 2) + 2 * (P.close_k / 2) + P.band_k / 2 <= FM_HALO) {
     // band, candidates, CLOSE, OPEN in one pass over bit-packed tiles                -> t2
     TimeScope ts(ctx, UB_T_STENCIL, st);
