@@ -12,7 +12,8 @@ Same names, argument meaning and results as the reference functions:
   compute_thickness_profile src/utils/geometry_enhanced.py:190-228 (per-row delta-D profile)
   filter_cable_by_shape, constrain_tape_to_ring   src/refactor/postprocess.py:12-118 (shape constraints on the masks)
   analyze_defects         src/utils/geometry_enhanced.py:236-330 (coverage, components, hole ratio, defect areas)
-  visualize_two_stage     infer_two_stage_burr.py:130-170 (blend on the device; box, text and contours by cv2 on the host)
+  visualize_two_stage     infer_two_stage_burr.py:130-170 (blend, ROI box + label and the thickness-2 contours on the device;
+                          the burr contours' thickness 3 by cv2 on the host)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
 without touching the host.  All arithmetic runs in the CUDA library; there is no CPU path.
@@ -291,23 +292,84 @@ def overlay_blend(frame, mask_cable, mask_tape, mask_burr, roi):
     return _unbatch(out, was_np, single)
 
 
-def draw_annotations(img, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
-    """The vector part of visualize_two_stage (infer_two_stage_burr.py:156-170): ROI box + label and the three
-    contour sets, drawn by cv2 on the host over the device-blended frame (in place)."""
+_roi_layers = {}        # (H, W, roi) -> u8 [H,W] plane holding the ROI box and its label as cv2 rasterises them
+
+
+def _roi_layer(h, w, roi):
+    """cv2.rectangle(.., 2) + cv2.putText('ROI', .., FONT_HERSHEY_SIMPLEX, 0.6, .., 2) of infer_two_stage_burr.py:156-158 on a
+    blank plane (1 where they paint): both write one solid colour, so painting that colour where the plane is set equals
+    drawing them on the frame.  Rasterised once per (frame size, ROI) on the host -- a polyline and three Hershey glyphs."""
     import cv2
-    x1, y1, x2, y2 = roi
+    key = (h, w, tuple(int(v) for v in roi))
+    if key not in _roi_layers:
+        x1, y1, x2, y2 = key[2]
+        layer = np.zeros((h, w), np.uint8)
+        cv2.rectangle(layer, (x1, y1), (x2, y2), 1, 2)
+        cv2.putText(layer, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, 1, 2)
+        if len(_roi_layers) > 16:
+            _roi_layers.clear()
+        _roi_layers[key] = layer
+    return _roi_layers[key]
+
+
+def annotate_on_device(c, f, mask_cable, mask_tape, roi, draw_roi_box=True):
+    """ROI box + label and the cable / tape contours (thickness 2) of visualize_two_stage (infer_two_stage_burr.py:156-163)
+    painted in place on the CUDA frames f u8 [B,H,W,3] through context c; masks u8 [B,H,W] on the same device.
+    Returns False (nothing drawn) when a frame is larger than the per-frame flood of ub_draw_contours holds."""
+    b, h, w, _ = f.shape
+    if 2 * (h + 2) * ((w + 31) // 32 + 2) * 4 > 200 * 1024:
+        return False
     if draw_roi_box:
-        cv2.rectangle(img, (x1, y1), (x2, y2), (0, 255, 255), 2)
-        cv2.putText(img, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, (0, 255, 255), 2)
-    for mask, colour, thick in ((mask_cable, (0, 255, 0), 2), (mask_tape, (255, 0, 0), 2), (mask_burr, (255, 0, 255), 3)):
+        c.paint_layer(f, torch.from_numpy(_roi_layer(h, w, roi)).to(f.device), [(0, 255, 255)])
+    c.draw_contours(f, mask_cable.contiguous(), (0, 255, 0))
+    c.draw_contours(f, mask_tape.contiguous(), (255, 0, 0))
+    return True
+
+
+def draw_host_contours(img, mask_burr, mask_cable=None, mask_tape=None, roi=None):
+    """What stays with cv2: the burr contours (thickness 3, infer_two_stage_burr.py:165-166) -- and, for frames the device
+    path does not take, the box and the other two contour sets before them.  img numpy [H,W,3], drawn in place."""
+    import cv2
+    todo = []
+    if mask_cable is not None:
+        if roi is not None:
+            x1, y1, x2, y2 = roi
+            cv2.rectangle(img, (x1, y1), (x2, y2), (0, 255, 255), 2)
+            cv2.putText(img, "ROI", (x1 + 5, y1 + 25), cv2.FONT_HERSHEY_SIMPLEX, 0.6, (0, 255, 255), 2)
+        todo = [(mask_cable, (0, 255, 0), 2), (mask_tape, (255, 0, 0), 2)]
+    for mask, colour, thick in todo + [(mask_burr, (255, 0, 255), 3)]:
         contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_SIMPLE)
         cv2.drawContours(img, contours, -1, colour, thick)
     return img
+
+
+def draw_annotations(img, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
+    """The vector part of visualize_two_stage (infer_two_stage_burr.py:156-170) over the blended frame(s).
+    On the device: the ROI box and label (host-rasterised once per ROI, painted by ub_paint_layer) and the cable and tape
+    contours (ub_draw_contours: findContours(RETR_EXTERNAL) + drawContours(thickness 2), byte-identical to cv2).  The burr
+    contours (thickness 3, the last thing the reference draws) stay with cv2 on the host: OpenCV's odd-thickness rasteriser
+    is not translation invariant near the image border.  img: numpy or CUDA tensor, [H,W,3] / [B,H,W,3]; masks likewise
+    [H,W] / [B,H,W].  Returns numpy."""
+    f, _, single = _batched(img, 3)
+    mc, mt = (_batched(m, 2)[0].to(f.device) for m in (mask_cable, mask_tape))
+    b, h, w, _ = f.shape
+    with torch.cuda.device(f.device):
+        on_device = annotate_on_device(_ctx(f.device, b, (h, w)), f, mc, mt, roi, draw_roi_box)
+        out = f.cpu().numpy()
+    host = [(m.cpu().numpy() if isinstance(m, torch.Tensor) else np.asarray(m)) for m in (mask_burr, mask_cable, mask_tape)]
+    host = [m[None] if m.ndim == 2 else m for m in host]
+    for i in range(b):
+        if on_device:
+            draw_host_contours(out[i], host[0][i])
+        else:
+            draw_host_contours(out[i], host[0][i], host[1][i], host[2][i], roi if draw_roi_box else None)
+    return out[0] if single else out
 
 
 def visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box=True):
     """Drop-in for visualize_two_stage(frame, mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box)
     (infer_two_stage_burr.py:130-170; visualize_detection of infer_enhanced_burr.py:150-192 with the ROI as a
     tuple): numpy in, numpy out."""
-    out = overlay_blend(frame, mask_cable, mask_tape, mask_burr, roi_orig)
-    return draw_annotations(np.ascontiguousarray(out), mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box)
+    f, _, _ = _batched(frame, 3)
+    out = overlay_blend(f, mask_cable, mask_tape, mask_burr, roi_orig)          # stays on the device
+    return draw_annotations(out[0] if np.ndim(frame) == 3 else out, mask_cable, mask_tape, mask_burr, roi_orig, draw_roi_box)
