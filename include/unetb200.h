@@ -86,9 +86,11 @@ int ub_set_weights(ub_ctx* ctx, const ub_named_tensor* tensors, int n);
 int ub_forward(ub_ctx* ctx, const float* x_nchw_dev, int B, int H, int W,
                float* logits_nchw_dev, void* stream);
 
-/* Select the conv implementation: 0 = tcgen05 tensor-core kernel (default, the product
- * path), 1 = plain CUDA-core kernel kept for kernel-vs-kernel debugging. */
-int ub_set_conv_impl(ub_ctx* ctx, int impl);
+/* Debug only (like ub_debug_conv): which conv kernel this context runs.  0 = the tcgen05 tensor-core kernels (the product path,
+ * always the default), 1 = a plain CUDA-core kernel that exists as the comparator of the kernel-vs-kernel parity tests
+ * (tests/test_gpu_net.py), 2 = the tcgen05 kernel with aligned A segments.  Nothing in the library selects 1 on its own: it
+ * is not a fallback, and it cannot be switched on from the environment. */
+int ub_debug_set_conv_impl(ub_ctx* ctx, int impl);
 
 /* ---- pre / post processing around the net ---------------------------------------- */
 /* Replaces preprocess_image (infer_two_stage_burr.py:122-127) and the BGR2GRAY of :317
@@ -116,14 +118,17 @@ int ub_masks_from_logits(ub_ctx* ctx, const float* logits_dev, int B, int nh, in
 int ub_overlay(ub_ctx* ctx, const uint8_t* frames_bgr_dev, const uint8_t* mask_cable_dev, const uint8_t* mask_tape_dev,
                const uint8_t* mask_burr_dev, int B, int H, int W, const ub_roi* roi, uint8_t* out_bgr_dev, void* stream);
 
-/* The contour half of visualize_two_stage (infer_two_stage_burr.py:160-165; infer_enhanced_burr.py:181-187):
- * cv2.findContours(mask, RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(img, contours, -1, (b,g,r), 2) in place on
- * frames u8 [B,H,W,3] BGR, mask u8 [B,H,W] (non-zero = set) -- byte-identical to OpenCV's result: the exterior background
- * is flooded per frame in shared memory, every foreground pixel next to it paints the thickness-2 stamps of its border
- * steps (csrc/annotate.cu).  Thickness 2 only (cable and tape; the burr contours' thickness 3 stays with cv2 on the host:
- * OpenCV's odd-thickness rasteriser is not translation invariant near the image border).  (H+2) x (W/32+2) x 8 bytes must
- * fit 200 KB of shared memory (any frame up to 800 x 448 / 1024 x 576). */
-int ub_draw_contours(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* mask_dev, int B, int H, int W, int b, int g, int r, void* stream);
+/* The contour half of visualize_two_stage (infer_two_stage_burr.py:160-166; infer_enhanced_burr.py:181-187):
+ * cv2.findContours(mask, RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(img, contours, -1, (b,g,r), thickness) in
+ * place on frames u8 [B,H,W,3] BGR, mask u8 [B,H,W] (non-zero = set); thickness 2 (cable, tape) or 3 (burr).  The exterior
+ * background is flooded per frame in shared memory, every foreground pixel next to it paints the stamps of its border
+ * steps (csrc/annotate.cu).  Thickness 2: byte-identical to OpenCV's result.  Thickness 3: byte-identical unless a border
+ * pixel of the mask lies within one pixel of the image border, where OpenCV's polygon clipping paints extra pixels; for
+ * those frames redo[frame] is set to 1 (0 otherwise) and the caller redraws that frame's contours with cv2 on top -- a
+ * superset in the same colour, so the result is exact either way.  redo int32 [B] on the device: required for thickness
+ * 3, nullable for 2.  (H+2) x (W/32+2) x 8 bytes must fit 200 KB of shared memory (800 x 448, 1024 x 576 ...). */
+int ub_draw_contours(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* mask_dev, int B, int H, int W, int b, int g, int r,
+                     int thickness, int32_t* redo_dev, void* stream);
 
 /* Paints what the host rasterised -- the ROI box and label (infer_two_stage_burr.py:156-158), Hershey text -- over frames
  * u8 [B,H,W,3] on the device: frames[q] = colour[layer[q] - 1] where layer[q] is 1, 2 or 3.  layer u8 [H,W] shared by the
@@ -131,10 +136,10 @@ int ub_draw_contours(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* mask_d
 int ub_paint_layer(ub_ctx* ctx, uint8_t* frames_bgr_dev, const uint8_t* layer_dev, int per_frame, int B, int H, int W,
                    const uint8_t* bgr9_host, void* stream);
 
-/* The 5x5 stamp (bit (dy+2)*5 + dx+2) ub_draw_contours paints for a unit border step in chain-code direction `code` (0..7:
- * E, NE, N, NW, W, SW, S, SE) or for a single point (code 8) at `thickness` 2; 0 for anything else.  Lets the CPU tests
- * compare the tables with cv2.line of the installed OpenCV.  No context, no device. */
-unsigned int ub_contour_stamp(int thickness, int code);
+/* The stamp ub_draw_contours paints for a unit border step in chain-code direction `code` (0..7: E, NE, N, NW, W, SW, S, SE)
+ * or for a single point (code 8): thickness 2 -> 5x5, bit (dy+2)*5 + dx+2; thickness 3 -> 7x7, bit (dy+3)*7 + dx+3; 0 for
+ * anything else.  Lets the CPU tests compare the tables with cv2.line of the installed OpenCV.  No context, no device. */
+unsigned long long ub_contour_stamp(int thickness, int code);
 
 /* compute_diameter_metrics (src/utils/geometry_enhanced.py:113-187): pred u8 [B,H,W] class ids -> out int32 [B][8] =
  * { dc_px, dt_px (binary32 bit patterns: medians of the Gaussian-smoothed row widths of the largest cable / tape

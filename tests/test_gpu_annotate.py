@@ -72,6 +72,36 @@ def test_draw_contours_equals_opencv(hw):
         c.close()
 
 
+@pytest.mark.parametrize("hw", [(448, 800), (64, 96), (37, 53)])
+def test_draw_contours_thickness3(hw):
+    """Thickness 3 (the burr contours, infer_two_stage_burr.py:165-166): byte-identical to OpenCV when no border pixel of the
+    mask lies within a pixel of the image border; otherwise redo is set and OpenCV's result only ADDS pixels of the same
+    colour, so redrawing with cv2 on top gives OpenCV's image."""
+    from unet_b200 import _lib
+    h, w = hw
+    kinds = ["noise", "blobs", "lines", "nested", "speckle", "blobs", "lines", "speckle"]
+    rng = np.random.default_rng(h + w)
+    masks = np.stack([masks_of_kind(k, h, w, rng) for k in kinds])
+    masks[4:, :2] = 0; masks[4:, -2:] = 0; masks[4:, :, :2] = 0; masks[4:, :, -2:] = 0      # the last four keep clear of the border
+    frames = rng.integers(0, 256, (len(kinds), h, w, 3), dtype=np.uint8)
+    col = (255, 0, 255)
+    c = _lib.Context(0, max_batch=len(kinds), frame_hw=hw, net_hw=(16, 16))
+    try:
+        got, redo = c.draw_contours(dev(frames), dev(masks), col, thickness=3)
+        got, redo = got.cpu().numpy(), redo.cpu().numpy()
+        assert not redo[4:].any(), redo
+        for i, k in enumerate(kinds):
+            want = cv_contours(frames[i], masks[i], col, 3)
+            if not redo[i]:
+                assert np.array_equal(got[i], want), (k, i)
+            else:
+                differs = (got[i] != want).any(axis=2)
+                assert (want[differs] == np.array(col, np.uint8)).all(), (k, i)          # only pixels OpenCV paints and the device left
+                assert np.array_equal(cv_contours(got[i], masks[i], col, 3), want), (k, i)
+    finally:
+        c.close()
+
+
 def test_paint_layer():
     from unet_b200 import _lib
     h, w = 448, 800
@@ -101,8 +131,8 @@ def test_paint_layer():
 
 @pytest.mark.parametrize("box", [True, False])
 def test_visualize_two_stage_vs_oracle(box):
-    """ops.visualize_two_stage (blend, box, cable / tape contours on the device; burr contours by cv2) == the oracle's
-    restatement of the reference function on synthetic frames whose masks touch the image border."""
+    """ops.visualize_two_stage (blend, box and the three contour sets on the device; cv2 redraws the burr contours of frames whose
+    burr mask touches the border band) == the oracle's restatement of the reference function."""
     import unet_b200 as U
     from oracle import ref_pipeline as R
     rng = np.random.default_rng(11)
@@ -112,7 +142,8 @@ def test_visualize_two_stage_vs_oracle(box):
         mc = S.mask_cable_synth(448, 800)
         mt = S.mask_blobs(448, 800, seed=20 + i, fill=0.03)
         mb = S.mask_blobs(448, 800, seed=30 + i, fill=0.004)
-        mb[:3, 300:330] = 1                                  # a burr component on the top border (thickness-3 corner case)
+        if i == 0:
+            mb[:3, 300:330] = 1                              # a burr component on the top border: the redo path
         got = U.visualize_two_stage(fr[i], mc, mt, mb, roi, box)
         want = R.visualize_two_stage(fr[i], mc, mt, mb, roi, box)
         assert got.dtype == np.uint8 and np.array_equal(got, want), int((got != want).any(axis=2).sum())

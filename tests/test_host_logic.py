@@ -130,12 +130,13 @@ def test_gather_stats_gloo_world2(tmp_path):
 
 
 def test_contour_stamps_match_installed_opencv():
-    """The thickness-2 stamps hard-coded in csrc/annotate.cu are what cv2.line paints for a unit step / a single point."""
+    """The stamps hard-coded in csrc/annotate.cu are what cv2.line paints for a unit step / a single point (thickness 2, 3)."""
     import importlib.util
     spec = importlib.util.spec_from_file_location("make_stamps", os.path.join(ROOT, "tools", "make_stamps.py"))
     ms = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(ms)
     from unet_b200 import _lib
-    for code in range(9):
-        assert _lib.lib().ub_contour_stamp(2, code) == ms.stamp(2, code), code
-    assert _lib.lib().ub_contour_stamp(3, 0) == 0
+    for thickness in (2, 3):
+        for code in range(9):
+            assert _lib.lib().ub_contour_stamp(thickness, code) == ms.stamp(thickness, code), (thickness, code)
+    assert _lib.lib().ub_contour_stamp(4, 0) == 0 and _lib.lib().ub_contour_stamp(2, 9) == 0

@@ -7,7 +7,7 @@ NAME=$1; shift
 cd "$(dirname "$0")/../unet-_b200/csrc"
 OUT=../../build/$NAME
 mkdir -p $OUT
-for f in api conv_tc conv_rows conv_block tmap conv_simt net_glue preprocess stage2 enhance; do
+for f in api conv_tc conv_rows conv_block tmap conv_simt net_glue preprocess stage2 enhance annotate; do
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC \
     "$@" -c $f.cu -o $OUT/$f.o &
 done

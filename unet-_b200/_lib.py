@@ -51,14 +51,14 @@ SIGNATURES = {
     "ub_version": (_I, []),
     "ub_set_weights": (_I, [_P, C.POINTER(NamedTensor), _I]),
     "ub_forward": (_I, [_P, _P, _I, _I, _I, _P, _P]),
-    "ub_set_conv_impl": (_I, [_P, _I]),
+    "ub_debug_set_conv_impl": (_I, [_P, _I]),
     "ub_preprocess": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "ub_normalize_frames": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P]),
     "ub_masks_from_logits": (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Roi), _P, _P, _P, _P]),
     "ub_overlay": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, C.POINTER(Roi), _P, _P]),
-    "ub_draw_contours": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "ub_draw_contours": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_paint_layer": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P]),
-    "ub_contour_stamp": (C.c_uint, [_I, _I]),
+    "ub_contour_stamp": (C.c_ulonglong, [_I, _I]),
     "ub_diameter_metrics": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_analyze_defects": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "ub_width_profiles": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -205,7 +205,7 @@ class Context:
         self._check(lib().ub_set_weights(self._h, arr, len(items)))
 
     def set_conv_impl(self, impl: int):
-        self._check(lib().ub_set_conv_impl(self._h, impl))
+        self._check(lib().ub_debug_set_conv_impl(self._h, impl))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         b, c, h, w = x.shape
@@ -251,12 +251,16 @@ class Context:
                                      C.byref(r), out.data_ptr(), self.stream))
         return out
 
-    def draw_contours(self, frames, mask, bgr):
-        """cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(.., bgr, 2) in place: frames u8 [B,H,W,3], mask u8 [B,H,W]."""
+    def draw_contours(self, frames, mask, bgr, thickness=2):
+        """cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_SIMPLE) + cv2.drawContours(.., bgr, thickness) in place: frames u8
+        [B,H,W,3], mask u8 [B,H,W].  thickness 2 -> frames; thickness 3 -> (frames, redo int32 [B]): frames whose flag is set
+        must have their contours redrawn by cv2 on top (OpenCV paints extra pixels near the image border)."""
         b, h, w, _ = frames.shape
+        redo = torch.empty((b,), dtype=torch.int32, device=frames.device) if thickness == 3 else None
         self._check(lib().ub_draw_contours(self._h, self._dev(frames, torch.uint8), self._dev(mask, torch.uint8), b, h, w,
-                                           int(bgr[0]), int(bgr[1]), int(bgr[2]), self.stream))
-        return frames
+                                           int(bgr[0]), int(bgr[1]), int(bgr[2]), int(thickness),
+                                           redo.data_ptr() if redo is not None else None, self.stream))
+        return frames if redo is None else (frames, redo)
 
     def paint_layer(self, frames, layer, colours):
         """frames[q] = colours[layer[q] - 1] where layer[q] != 0, in place; layer u8 [H,W] (shared) or [B,H,W]; up to three BGR colours."""

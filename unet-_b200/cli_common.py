@@ -153,15 +153,15 @@ def load_state_dict(path):
 
 
 # ------------------------------------------------------------------------------------- drawing
-def draw_overlay(blended, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True, annotated=False):
+def draw_overlay(blended, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True, redo=None):
     """Second half of the reference's visualisation (infer_two_stage_burr.py:156-170, infer_enhanced_burr.py:177-190) over the
-    frame the device already blended (ub_overlay).  annotated: the device has also painted the ROI box and the cable / tape
-    contours (ops.annotate_on_device) -- only the burr contours (thickness 3) are left for cv2."""
+    frame the device already blended (ub_overlay).  redo: None -- nothing annotated on the device, cv2 draws box and contours;
+    0 -- the device painted everything (ops.annotate_on_device); 1 -- it did, but cv2 must redraw the burr contours on top."""
     from .ops import draw_host_contours
     img = np.ascontiguousarray(blended)
-    if annotated:
-        return draw_host_contours(img, mask_burr)
-    return draw_host_contours(img, mask_burr, mask_cable, mask_tape, roi if draw_roi_box else None)
+    if redo is None:
+        return draw_host_contours(img, mask_burr, mask_cable, mask_tape, roi if draw_roi_box else None)
+    return draw_host_contours(img, mask_burr) if redo else img
 
 
 def draw_text(img, info_text, defect_text):
@@ -233,8 +233,9 @@ class DeviceStep:
                 from .ops import annotate_on_device
                 mc, mt = masks[:, 0].contiguous(), masks[:, 1].contiguous()
                 blend = self.pipe.ctx.overlay(d, mc, mt, masks[:, 2].contiguous(), self.pipe.roi)
-                # ROI box + label and the cable / tape contours on the device too (run_loop leaves the burr contours to cv2)
-                self.annotated = annotate_on_device(self.pipe.ctx, blend, mc, mt, self.pipe.roi)
+                # ROI box + label and the three contour sets on the device too (run_loop redraws flagged frames' burr contours)
+                redo = annotate_on_device(self.pipe.ctx, blend, mc, mt, masks[:, 2].contiguous(), self.pipe.roi)
+                self.redo = redo.cpu().numpy() if redo is not None else None
                 return stats, blend.cpu().numpy(), masks.cpu().numpy()
         return stats, None, None
 
@@ -261,7 +262,8 @@ def run_loop(source, step, batch, roi, total_frames, frame_stride=1, print_inter
                 cable_px, tape_px, burr_px = (int(v) for v in stats[i, 1:4])
                 records.append((proc_no, frame_no, cable_px, tape_px, burr_px))
                 if writer is not None:
-                    img = draw_overlay(frames[i], masks[i, 0], masks[i, 1], masks[i, 2], roi, annotated=getattr(step, "annotated", False))
+                    redo = getattr(step, "redo", None)
+                    img = draw_overlay(frames[i], masks[i, 0], masks[i, 1], masks[i, 2], roi, redo=None if redo is None else int(redo[i]))
                     elapsed = time.time() - t0
                     fps_now = proc_no / elapsed if elapsed > 0 else 0
                     c, t, b = ratios(cable_px, tape_px, burr_px, roi)

@@ -13,12 +13,13 @@
 // and the next crack (p, d+2) decides.  drawContours(thickness 2) paints, for every segment between consecutive contour
 // points, a filled polygon and a disc at its end; the union over a straight run of unit steps equals the painted long
 // segment (all eight directions, any length), so the image is the union over all steps of the unit step's stamp plus the
-// disc stamp on every border pixel.  Stamps are 5x5 bit masks taken from cv2.line(thickness 2) (tools/make_stamps.py;
+// disc stamp on every border pixel.  Stamps are bit masks taken from cv2.line (tools/make_stamps.py;
 // tests/test_host_logic.py checks them against the installed OpenCV).  Checked against cv2 on random, blob, line and
 // speckle masks including ones that touch the image border (tests/test_gpu_annotate.py, tools/contour_proto.py).
-// Thickness 3 (the burr contours) is NOT done here: OpenCV's thick-line rasteriser is not translation invariant within
-// three pixels of the image border for odd thicknesses (its polygon clipping changes the outline), so the host keeps
-// cv2 for that one, sparse, contour set -- it is the last thing the reference draws, so the order is preserved.
+// Thickness 3 (the burr contours): same rule with 7x7 stamps.  OpenCV's thick-line rasteriser is not translation invariant
+// when an end point lies within one pixel of the image border (its polygon clipping then paints EXTRA pixels, never
+// fewer): for a frame with a border pixel of the mask in that two-pixel band the kernel raises redo[frame], and the caller
+// redraws that frame's contours with cv2 over the device's (a superset in the same colour) -- exact in every case.
 #include "common.cuh"
 
 namespace ann {
@@ -112,36 +113,23 @@ __global__ void __launch_bounds__(1024) k_exterior_frame(const uint8_t* __restri
   }
 }
 
-// 5x5 stamps of cv2.line(img, p, p + D[d], colour, 2) around p, bit (dy + 2) * 5 + (dx + 2); entry 8: the single point
-// (the disc drawn at every contour vertex).  Chain codes D: 0 E, 1 NE, 2 N, 3 NW, 4 W, 5 SW, 6 S, 7 SE (y down).
-#define SB(dx, dy) (1u << (((dy) + 2) * 5 + (dx) + 2))
-__constant__ uint32_t c_stamp2[9] = {
-    SB(-1, 0) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(2, 0),
-    SB(-1, -1) | SB(-1, 0) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -2) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(2, -1) | SB(2, 0),
-    SB(-1, -1) | SB(-1, 0) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0),
-    SB(-2, -1) | SB(-2, 0) | SB(-1, -2) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0),
-    SB(-2, 0) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, 0),
-    SB(-2, 0) | SB(-2, 1) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(-1, 2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, 0) | SB(1, 1),
-    SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, 0) | SB(1, 1),
-    SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(1, 2) | SB(2, 0) | SB(2, 1),
-    SB(-1, 0) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, 0)};
-static const uint32_t h_stamp2[9] = {
-    SB(-1, 0) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(2, 0),
-    SB(-1, -1) | SB(-1, 0) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -2) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(2, -1) | SB(2, 0),
-    SB(-1, -1) | SB(-1, 0) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0),
-    SB(-2, -1) | SB(-2, 0) | SB(-1, -2) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(0, -2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, -1) | SB(1, 0),
-    SB(-2, 0) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, 0),
-    SB(-2, 0) | SB(-2, 1) | SB(-1, -1) | SB(-1, 0) | SB(-1, 1) | SB(-1, 2) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, 0) | SB(1, 1),
-    SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, 0) | SB(1, 1),
-    SB(-1, 0) | SB(-1, 1) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(0, 2) | SB(1, -1) | SB(1, 0) | SB(1, 1) | SB(1, 2) | SB(2, 0) | SB(2, 1),
-    SB(-1, 0) | SB(0, -1) | SB(0, 0) | SB(0, 1) | SB(1, 0)};
-#undef SB
+// Stamps of cv2.line(img, p, p + D[d], colour, T) around p for T = 2 (5x5, bit (dy+2)*5 + dx+2) and T = 3 (7x7, bit
+// (dy+3)*7 + dx+3); entry 8: the single point (the disc drawn at every contour vertex).  Chain codes D: 0 E, 1 NE, 2 N,
+// 3 NW, 4 W, 5 SW, 6 S, 7 SE (y down).  Printed by tools/make_stamps.py; tests/test_host_logic.py compares them with the
+// installed OpenCV through ub_contour_stamp.
+#define UB_STAMPS2 {0x67980ull, 0x67bccull, 0x239c4ull, 0x33de6ull, 0x33cc0ull, 0x67bcc0ull, 0x473880ull, 0xcf7980ull, 0x23880ull}
+#define UB_STAMPS3 {0xc3cfcf0c00ull, 0x41c7df1c10ull, 0x41c7cf8e08ull, 0x41c7c7c704ull, 0x61e7e78600ull, 0x1071f7c70400ull, \
+                    0x20e3e7c70400ull, 0x41c7c7c70400ull, 0x41c7c70400ull}
+__constant__ unsigned long long c_stamp[2][9] = {UB_STAMPS2, UB_STAMPS3};
+static const unsigned long long h_stamp[2][9] = {UB_STAMPS2, UB_STAMPS3};
 
 // One thread per 32-pixel word of the mask: border pixels (foreground with an exterior orthogonal neighbour) are few, each
 // paints the stamps of its steps.  Three 34-bit windows (rows y-1, y, y+1; bit i+1 = pixel 32w + i) of the foreground and
 // of the exterior plane give every neighbour of every pixel of the word by shifts.  Outside the image: background, exterior.
+template <int T>       // thickness 2 or 3
 __global__ void __launch_bounds__(256) k_contour_paint(const uint8_t* __restrict__ mask, const uint32_t* __restrict__ ext, uint8_t* __restrict__ frames,
-                                                       int H, int W, int Wd, uchar3 colour) {
+                                                       int H, int W, int Wd, uchar3 colour, int* __restrict__ redo) {
+  constexpr int R = T, SIDE = 2 * T + 1;
   const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
   if (w >= Wd || y >= H) return;
   const uint8_t* img = mask + (size_t)blockIdx.z * H * W;
@@ -171,18 +159,19 @@ __global__ void __launch_bounds__(256) k_contour_paint(const uint8_t* __restrict
                         ((r2 & 1u) << 5) | (((r2 >> 1) & 1u) << 6) | (((r2 >> 2) & 1u) << 7);
     const uint32_t eo = ((uint32_t)(E[1] >> (i + 2)) & 1u) | (((uint32_t)(E[0] >> (i + 1)) & 1u) << 2) | (((uint32_t)(E[1] >> i) & 1u) << 4) |
                         (((uint32_t)(E[2] >> (i + 1)) & 1u) << 6);
-    uint32_t stamp = c_stamp2[8];
+    unsigned long long stamp = c_stamp[T - 2][8];
 #pragma unroll
     for (int d = 0; d < 8; d += 2)
       if ((eo >> d) & 1u) {
-        if ((nb >> (d + 1)) & 1u) stamp |= c_stamp2[d + 1];
-        else if ((nb >> ((d + 2) & 7)) & 1u) stamp |= c_stamp2[(d + 2) & 7];
+        if ((nb >> (d + 1)) & 1u) stamp |= c_stamp[T - 2][d + 1];
+        else if ((nb >> ((d + 2) & 7)) & 1u) stamp |= c_stamp[T - 2][(d + 2) & 7];
       }
     const int x = 32 * w + i;
+    if (T == 3 && redo && (x <= 1 || y <= 1 || x >= W - 2 || y >= H - 2)) redo[blockIdx.z] = 1;
     while (stamp) {
-      const int b = __ffs(stamp) - 1;
+      const int b = __ffsll((long long)stamp) - 1;
       stamp &= stamp - 1;
-      const int yy = y + b / 5 - 2, xx = x + b % 5 - 2;
+      const int yy = y + b / SIDE - R, xx = x + b % SIDE - R;
       if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
         uint8_t* p = frame + ((size_t)yy * W + xx) * 3;
         p[0] = colour.x; p[1] = colour.y; p[2] = colour.z;
@@ -205,7 +194,10 @@ __global__ void __launch_bounds__(256) k_paint_layer(uint8_t* __restrict__ frame
 
 }  // namespace ann
 
-int draw_contours_impl(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B, int H, int W, int b, int g, int r, cudaStream_t st) {
+int draw_contours_impl(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B, int H, int W, int b, int g, int r, int thickness,
+                       int* redo, cudaStream_t st) {
+  if (thickness != 2 && thickness != 3) return ub_fail(ctx, UB_ERR_ARG, "ub_draw_contours: thickness %d (2 or 3)", thickness);
+  if (thickness == 3 && !redo) return ub_fail(ctx, UB_ERR_ARG, "ub_draw_contours: thickness 3 needs the redo flags");
   const int Wd = (W + 31) / 32;
   const size_t smem = (size_t)2 * (H + 2) * (Wd + 2) * sizeof(uint32_t);
   if (smem > 200 * 1024) return ub_fail(ctx, UB_ERR_ARG, "ub_draw_contours: a %dx%d frame does not fit the per-frame flood (%zu B of shared memory)", H, W, smem);
@@ -220,8 +212,11 @@ int draw_contours_impl(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B,
   uint32_t* ext = reinterpret_cast<uint32_t*>(ctx->d_lab[1]);
   const int nthr = H * Wd >= 4096 ? 1024 : (H * Wd >= 1024 ? 512 : 128);
   ann::k_exterior_frame<<<B, nthr, smem, st>>>(mask, ext, H, W, Wd);
-  ann::k_contour_paint<<<dim3(cdiv(Wd, 32), cdiv(H, 8), B), dim3(32, 8), 0, st>>>(mask, ext, frames, H, W, Wd,
-                                                                                make_uchar3((unsigned char)b, (unsigned char)g, (unsigned char)r));
+  const uchar3 col = make_uchar3((unsigned char)b, (unsigned char)g, (unsigned char)r);
+  const dim3 grid(cdiv(Wd, 32), cdiv(H, 8), B), block(32, 8);
+  if (redo) UB_CUDA(ctx, cudaMemsetAsync(redo, 0, sizeof(int) * B, st));
+  if (thickness == 2) ann::k_contour_paint<2><<<grid, block, 0, st>>>(mask, ext, frames, H, W, Wd, col, redo);
+  else ann::k_contour_paint<3><<<grid, block, 0, st>>>(mask, ext, frames, H, W, Wd, col, redo);
   UB_CHECK_LAUNCH_N(ctx, 2);
   return UB_OK;
 }
@@ -235,6 +230,6 @@ int paint_layer_impl(ub_ctx* ctx, uint8_t* frames, const uint8_t* layer, int per
   return UB_OK;
 }
 
-uint32_t contour_stamp(int thickness, int code) {
-  return thickness == 2 && code >= 0 && code < 9 ? ann::h_stamp2[code] : 0u;
+unsigned long long contour_stamp(int thickness, int code) {
+  return (thickness == 2 || thickness == 3) && code >= 0 && code < 9 ? ann::h_stamp[thickness - 2][code] : 0ull;
 }

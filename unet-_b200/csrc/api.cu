@@ -46,9 +46,9 @@ int morph_op(ub_ctx*, int op, int k, const uint8_t* src, uint8_t* dst, uint8_t* 
 int gaussian5(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, cudaStream_t);
 int canny(ub_ctx*, const uint8_t*, uint8_t*, uint8_t*, int*, int, int, int, int, int, cudaStream_t);
 int blur_canny(ub_ctx*, const uint8_t*, uint8_t*, int, int, int, int, int, cudaStream_t, int phase = 0);
-int draw_contours_impl(ub_ctx*, uint8_t*, const uint8_t*, int, int, int, int, int, int, cudaStream_t);
+int draw_contours_impl(ub_ctx*, uint8_t*, const uint8_t*, int, int, int, int, int, int, int, int*, cudaStream_t);
 int paint_layer_impl(ub_ctx*, uint8_t*, const uint8_t*, int, int, int, int, const uint8_t*, cudaStream_t);
-uint32_t contour_stamp(int, int);
+unsigned long long contour_stamp(int, int);
 int diameter_metrics(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int analyze_defects(ub_ctx*, const uint8_t*, int, int, int, int, int, int, int32_t*, cudaStream_t);
 int width_profiles(ub_ctx*, const uint8_t*, int, int, int, int, int, float*, cudaStream_t);
@@ -136,8 +136,9 @@ int ub_create(ub_ctx** out, int device, int max_batch, int frame_h, int frame_w,
   c->device = device; c->sm_count = prop.multiProcessorCount;
   c->max_batch = max_batch; c->frame_h = frame_h; c->frame_w = frame_w; c->net_h = net_h; c->net_w = net_w;
   c->num_classes = num_classes;
-  const char* impl = getenv("UB_CONV_IMPL");
-  if (impl) c->conv_impl = atoi(impl);
+  if (const char* impl = getenv("UB_CONV_IMPL")) {        // 2 = the aligned-A variant of the tcgen05 kernel; the CUDA-core comparator (1) cannot
+    if (atoi(impl) == 2) c->conv_impl = 2;                 // be selected from the environment, only per context by ub_debug_set_conv_impl
+  }
   int r = UB_OK;
   auto fail = [&](int code) { ub_destroy(c); return code; };
   for (int i = 0; i < 22 && r == UB_OK; ++i) {
@@ -198,7 +199,7 @@ void ub_destroy(ub_ctx* c) {
   delete c;
 }
 
-int ub_set_conv_impl(ub_ctx* ctx, int impl) {
+int ub_debug_set_conv_impl(ub_ctx* ctx, int impl) {
   NEED_CTX(ctx);
   if (impl < 0 || impl > 2) return ub_fail(ctx, UB_ERR_ARG, "conv impl %d (0 tcgen05, 1 simt, 2 tcgen05 aligned-A)", impl);
   ctx->conv_impl = impl;
@@ -388,11 +389,12 @@ int ub_overlay(ub_ctx* ctx, const uint8_t* frames, const uint8_t* mc, const uint
   return overlay_impl(ctx, frames, mc, mt, mb, B, H, W, *roi, out, as_stream(stream));
 }
 
-int ub_draw_contours(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B, int H, int W, int b, int g, int r, void* stream) {
+int ub_draw_contours(ub_ctx* ctx, uint8_t* frames, const uint8_t* mask, int B, int H, int W, int b, int g, int r, int thickness,
+                     int32_t* redo, void* stream) {
   NEED_CTX(ctx);
   if (!frames || !mask) return ub_fail(ctx, UB_ERR_ARG, "ub_draw_contours: null pointer");
   RUN(check_frame_shape(ctx, B, H, W));
-  return draw_contours_impl(ctx, frames, mask, B, H, W, b, g, r, as_stream(stream));
+  return draw_contours_impl(ctx, frames, mask, B, H, W, b, g, r, thickness, redo, as_stream(stream));
 }
 
 int ub_paint_layer(ub_ctx* ctx, uint8_t* frames, const uint8_t* layer, int per_frame, int B, int H, int W, const uint8_t* bgr9, void* stream) {
@@ -402,7 +404,7 @@ int ub_paint_layer(ub_ctx* ctx, uint8_t* frames, const uint8_t* layer, int per_f
   return paint_layer_impl(ctx, frames, layer, per_frame, B, H, W, bgr9, as_stream(stream));
 }
 
-unsigned int ub_contour_stamp(int thickness, int code) { return contour_stamp(thickness, code); }
+unsigned long long ub_contour_stamp(int thickness, int code) { return contour_stamp(thickness, code); }
 
 int ub_diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int cable_cls, int tape_cls, int min_area,
                         int min_valid_rows, int32_t* out, void* stream) {

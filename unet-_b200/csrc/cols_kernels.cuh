@@ -370,12 +370,14 @@ __global__ void __launch_bounds__(256) k_burr_chain_cols(const uint8_t* __restri
     if (out) store_bits_as_bytes(out + fbase + (size_t)t * W + x, o, W - x, 1u);
     if (bits) {
       bits[((size_t)blockIdx.z * H + t) * Wd + wq] = o;
-      int* l = lab_all + fbase + (size_t)t * W + x;
-      uint32_t c = o;
-      while (c) {
-        int a, len;
-        c &= ~first_run(c, a, len);
-        l[a] = t * W + x + a;
+      if (lab_all) {                                            // union-find entries of the run starts (k_cclb_init's job)
+        int* l = lab_all + fbase + (size_t)t * W + x;
+        uint32_t c = o;
+        while (c) {
+          int a, len;
+          c &= ~first_run(c, a, len);
+          l[a] = t * W + x + a;
+        }
       }
     }
   }

@@ -1,6 +1,6 @@
 // conv_simt.cu -- plain CUDA-core 3x3 conv in the PP layout.  NOT the product path: it
 // exists so the tcgen05 kernel (conv_tc.cu) can be checked kernel-against-kernel on the
-// device, and is selected only through ub_set_conv_impl(ctx, 1).
+// device, and is selected only through ub_debug_set_conv_impl(ctx, 1) (a test hook; never a fallback).
 #include "common.cuh"
 
 namespace {

@@ -12,8 +12,7 @@ Same names, argument meaning and results as the reference functions:
   compute_thickness_profile src/utils/geometry_enhanced.py:190-228 (per-row delta-D profile)
   filter_cable_by_shape, constrain_tape_to_ring   src/refactor/postprocess.py:12-118 (shape constraints on the masks)
   analyze_defects         src/utils/geometry_enhanced.py:236-330 (coverage, components, hole ratio, defect areas)
-  visualize_two_stage     infer_two_stage_burr.py:130-170 (blend, ROI box + label and the thickness-2 contours on the device;
-                          the burr contours' thickness 3 by cv2 on the host)
+  visualize_two_stage     infer_two_stage_burr.py:130-170 (blend, ROI box + label and the three contour sets on the device)
 Each accepts what the reference accepts (one numpy frame on the host) and returns the same
 kind of object; it ALSO accepts a batched CUDA tensor ([B,...]) and then returns CUDA tensors
 without touching the host.  All arithmetic runs in the CUDA library; there is no CPU path.
@@ -312,23 +311,27 @@ def _roi_layer(h, w, roi):
     return _roi_layers[key]
 
 
-def annotate_on_device(c, f, mask_cable, mask_tape, roi, draw_roi_box=True):
-    """ROI box + label and the cable / tape contours (thickness 2) of visualize_two_stage (infer_two_stage_burr.py:156-163)
-    painted in place on the CUDA frames f u8 [B,H,W,3] through context c; masks u8 [B,H,W] on the same device.
-    Returns False (nothing drawn) when a frame is larger than the per-frame flood of ub_draw_contours holds."""
+def annotate_on_device(c, f, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
+    """The vector half of visualize_two_stage (infer_two_stage_burr.py:156-166) painted in place on the CUDA frames f u8
+    [B,H,W,3] through context c: ROI box + label (host-rasterised once per ROI, ub_paint_layer), then the cable, tape
+    (thickness 2) and burr (thickness 3) contours (ub_draw_contours); masks u8 [B,H,W] on the same device.
+    Returns the int32 [B] redo flags of the burr contours (frames where cv2 must redraw them on top, see
+    ub_draw_contours), or None -- nothing drawn -- when a frame is larger than the per-frame flood holds."""
     b, h, w, _ = f.shape
     if 2 * (h + 2) * ((w + 31) // 32 + 2) * 4 > 200 * 1024:
-        return False
+        return None
     if draw_roi_box:
         c.paint_layer(f, torch.from_numpy(_roi_layer(h, w, roi)).to(f.device), [(0, 255, 255)])
     c.draw_contours(f, mask_cable.contiguous(), (0, 255, 0))
     c.draw_contours(f, mask_tape.contiguous(), (255, 0, 0))
-    return True
+    _, redo = c.draw_contours(f, mask_burr.contiguous(), (255, 0, 255), thickness=3)
+    return redo
 
 
 def draw_host_contours(img, mask_burr, mask_cable=None, mask_tape=None, roi=None):
-    """What stays with cv2: the burr contours (thickness 3, infer_two_stage_burr.py:165-166) -- and, for frames the device
-    path does not take, the box and the other two contour sets before them.  img numpy [H,W,3], drawn in place."""
+    """cv2's share: the burr contours (thickness 3, infer_two_stage_burr.py:165-166) of a frame whose redo flag is set --
+    and, for frames the device path does not take, the box and the other two contour sets before them.
+    img numpy [H,W,3], drawn in place."""
     import cv2
     todo = []
     if mask_cable is not None:
@@ -344,25 +347,25 @@ def draw_host_contours(img, mask_burr, mask_cable=None, mask_tape=None, roi=None
 
 
 def draw_annotations(img, mask_cable, mask_tape, mask_burr, roi, draw_roi_box=True):
-    """The vector part of visualize_two_stage (infer_two_stage_burr.py:156-170) over the blended frame(s).
-    On the device: the ROI box and label (host-rasterised once per ROI, painted by ub_paint_layer) and the cable and tape
-    contours (ub_draw_contours: findContours(RETR_EXTERNAL) + drawContours(thickness 2), byte-identical to cv2).  The burr
-    contours (thickness 3, the last thing the reference draws) stay with cv2 on the host: OpenCV's odd-thickness rasteriser
-    is not translation invariant near the image border.  img: numpy or CUDA tensor, [H,W,3] / [B,H,W,3]; masks likewise
-    [H,W] / [B,H,W].  Returns numpy."""
+    """The vector part of visualize_two_stage (infer_two_stage_burr.py:156-170) over the blended frame(s), on the device
+    (annotate_on_device).  cv2 only redraws the burr contours of frames whose mask comes within a pixel of the image border
+    (OpenCV's odd-thickness rasteriser paints extra pixels there), and draws everything for frames too large for the
+    device path.  img: numpy or CUDA tensor, [H,W,3] / [B,H,W,3]; masks likewise [H,W] / [B,H,W].  Returns numpy."""
     f, _, single = _batched(img, 3)
-    mc, mt = (_batched(m, 2)[0].to(f.device) for m in (mask_cable, mask_tape))
+    mc, mt, mb = (_batched(m, 2)[0].to(f.device) for m in (mask_cable, mask_tape, mask_burr))
     b, h, w, _ = f.shape
     with torch.cuda.device(f.device):
-        on_device = annotate_on_device(_ctx(f.device, b, (h, w)), f, mc, mt, roi, draw_roi_box)
+        redo = annotate_on_device(_ctx(f.device, b, (h, w)), f, mc, mt, mb, roi, draw_roi_box)
         out = f.cpu().numpy()
-    host = [(m.cpu().numpy() if isinstance(m, torch.Tensor) else np.asarray(m)) for m in (mask_burr, mask_cable, mask_tape)]
-    host = [m[None] if m.ndim == 2 else m for m in host]
-    for i in range(b):
-        if on_device:
-            draw_host_contours(out[i], host[0][i])
-        else:
-            draw_host_contours(out[i], host[0][i], host[1][i], host[2][i], roi if draw_roi_box else None)
+        redo = redo.cpu().numpy() if redo is not None else None
+    if redo is None or redo.any():
+        host = [(m.cpu().numpy() if isinstance(m, torch.Tensor) else np.asarray(m)) for m in (mask_burr, mask_cable, mask_tape)]
+        host = [m[None] if m.ndim == 2 else m for m in host]
+        for i in range(b):
+            if redo is None:
+                draw_host_contours(out[i], host[0][i], host[1][i], host[2][i], roi if draw_roi_box else None)
+            elif redo[i]:
+                draw_host_contours(out[i], host[0][i])
     return out[0] if single else out
 
 
