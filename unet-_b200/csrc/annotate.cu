@@ -21,6 +21,7 @@
 // fewer): for a frame with a border pixel of the mask in that two-pixel band the kernel raises redo[frame], and the caller
 // redraws that frame's contours with cv2 over the device's (a superset in the same colour) -- exact in every case.
 #include "common.cuh"
+#include "flood.cuh"
 
 namespace ann {
 
@@ -44,23 +45,6 @@ __device__ __forceinline__ uint32_t pack32(const uint8_t* __restrict__ img, int 
   return word;
 }
 
-// Kogge-Stone fill: the runs of c that hold a bit of g
-__device__ __forceinline__ uint32_t fill_runs(uint32_t g, uint32_t c) {
-  uint32_t gl = g, pl = c;
-  gl |= pl & (gl << 1);  pl &= pl << 1;
-  gl |= pl & (gl << 2);  pl &= pl << 2;
-  gl |= pl & (gl << 4);  pl &= pl << 4;
-  gl |= pl & (gl << 8);  pl &= pl << 8;
-  gl |= pl & (gl << 16);
-  uint32_t gr = g, pr = c;
-  gr |= pr & (gr >> 1);  pr &= pr >> 1;
-  gr |= pr & (gr >> 2);  pr &= pr >> 2;
-  gr |= pr & (gr >> 4);  pr &= pr >> 4;
-  gr |= pr & (gr >> 8);  pr &= pr >> 8;
-  gr |= pr & (gr >> 16);
-  return gl | gr;
-}
-
 // Exterior background of one frame: flood of the background (4-connectivity) from the image frame, both bit planes of
 // the frame in shared memory with a border of one word / one row that is exterior by definition.  ext [B][H][Wd] words,
 // bit = 1: background pixel connected to the outside (bits beyond W in the last word are set).
@@ -81,31 +65,7 @@ __global__ void __launch_bounds__(1024) k_exterior_frame(const uint8_t* __restri
     S[idx] = outside;
   }
   __syncthreads();
-  int changed;
-  do {
-    changed = 0;
-#pragma unroll 1
-    for (int sweep = 0; sweep < 2; ++sweep) {
-      int r = tid / Wd, w = tid - r * Wd;
-      const int dr = nthr / Wd, dw = nthr - dr * Wd;
-      for (; r < H;) {
-        const int idx = (r + 1) * Wp + w + 1;
-        const uint32_t c = C[idx];
-        if (c) {
-          const uint32_t s = S[idx];
-          if (s != c) {
-            const uint32_t seeds = (S[idx - Wp] | S[idx + Wp] | s | (s << 1) | (s >> 1) | (S[idx - 1] >> 31) | (S[idx + 1] << 31)) & c;
-            if (seeds != s) {                  // s is a union of whole runs except before the word's first update
-              S[idx] = fill_runs(seeds, c);
-              changed = 1;
-            }
-          }
-        }
-        r += dr; w += dw;
-        if (w >= Wd) { w -= Wd; ++r; }
-      }
-    }
-  } while (__syncthreads_or(changed));
+  fl::flood<false>(C, S, H, Wd);
   uint32_t* out = ext + (size_t)blockIdx.x * H * Wd;
   for (int i = tid; i < H * Wd; i += nthr) {
     const int r = i / Wd, w = i - r * Wd;

@@ -10,6 +10,7 @@
 //                  u8 plane (infer_two_stage_burr.py:78-97; oracle/cvnp.py dilate / erode)
 // Included by stage2.cu after pack32 / inside32 / store_bits_as_bytes.
 #pragma once
+#include "flood.cuh"
 
 namespace s2 {
 
@@ -389,28 +390,11 @@ __global__ void __launch_bounds__(256) k_burr_chain_cols(const uint8_t* __restri
 // Canny hysteresis (second half of cv2.Canny; oracle/cvnp.py canny: "every candidate whose 8-connected component of
 // candidates holds a strong pixel") as a flood of the strong bits through the candidate bits, one CTA per frame with
 // both bit planes of the frame in shared memory (448 x 800: 2 x 48.6 KB, zero-padded by one word / one row all round).
-// A sweep visits every candidate word: the seeds are the word's own kept bits and the 3x3 dilation of the kept bits
-// around it; the whole runs of candidates that hold a seed are then filled in one go (Kogge-Stone fill in both
-// directions), so a sweep carries the flood along complete horizontal runs and one row up or down; words are updated in
-// place (monotone: races only make a sweep see more).  Sweeps repeat until none changes a word.  No labels, no atomics,
+// A visit of a candidate word seeds it with its own kept bits and the 3x3 dilation of the kept bits around it and fills the
+// whole runs of candidates that hold a seed (Kogge-Stone); a thread visits a segment of consecutive rows of one word
+// column in order, down then up, in place (flood.cuh).  Sweeps repeat until none changes a word.  No labels, no atomics,
 // no per-pixel scratch plane: 2 x P/8 bytes in, P bytes out.  Frames whose planes do not fit take the union-find path.
 // ------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t hf_fill(uint32_t g, uint32_t c) {            // runs of c that hold a bit of g (g within c)
-  uint32_t gl = g, pl = c;
-  gl |= pl & (gl << 1);  pl &= pl << 1;
-  gl |= pl & (gl << 2);  pl &= pl << 2;
-  gl |= pl & (gl << 4);  pl &= pl << 4;
-  gl |= pl & (gl << 8);  pl &= pl << 8;
-  gl |= pl & (gl << 16);
-  uint32_t gr = g, pr = c;
-  gr |= pr & (gr >> 1);  pr &= pr >> 1;
-  gr |= pr & (gr >> 2);  pr &= pr >> 2;
-  gr |= pr & (gr >> 4);  pr &= pr >> 4;
-  gr |= pr & (gr >> 8);  pr &= pr >> 8;
-  gr |= pr & (gr >> 16);
-  return gl | gr;
-}
-
 __global__ void __launch_bounds__(1024) k_hyst_frame(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ strong,
                                                      uint8_t* __restrict__ dst, int H, int W, int Wd) {
   extern __shared__ uint32_t hf_smem[];
@@ -427,34 +411,7 @@ __global__ void __launch_bounds__(1024) k_hyst_frame(const uint32_t* __restrict_
     S[idx] = strong[wb + i];
   }
   __syncthreads();
-  int changed;
-  do {
-    changed = 0;
-#pragma unroll 1
-    for (int sweep = 0; sweep < 2; ++sweep) {
-      int r = tid / Wd, w = tid - r * Wd;
-      const int dr = nthr / Wd, dw = nthr - dr * Wd;
-      for (; r < H; ) {
-        const int idx = (r + 1) * Wp + w + 1;
-        const uint32_t c = C[idx];
-        if (c) {
-          const uint32_t s = S[idx];
-          if (s != c) {
-            const uint32_t m = S[idx - Wp] | S[idx + Wp] | s;
-            const uint32_t l = (S[idx - Wp - 1] | S[idx - 1] | S[idx + Wp - 1]) >> 31;
-            const uint32_t q = (S[idx - Wp + 1] | S[idx + 1] | S[idx + Wp + 1]) << 31;
-            const uint32_t seeds = (m | (m << 1) | (m >> 1) | l | q) & c;
-            if (seeds != s) {
-              S[idx] = hf_fill(seeds, c);
-              changed = 1;
-            }
-          }
-        }
-        r += dr; w += dw;
-        if (w >= Wd) { w -= Wd; ++r; }
-      }
-    }
-  } while (__syncthreads_or(changed));
+  fl::flood<true>(C, S, H, Wd);
   uint8_t* out = dst + (size_t)blockIdx.x * H * W;
   for (int i = tid; i < H * Wd; i += nthr) {
     const int r = i / Wd, w = i - r * Wd;

@@ -1033,14 +1033,20 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
 // =====================================================================================================
 namespace s2 {
 
+__device__ __forceinline__ uint32_t eq_bytes01(uint32_t w, uint32_t cls4) {          // byte j = (byte j of w == cls) ? 1 : 0
+  const uint32_t v = w ^ cls4;                                                         // zero byte where equal
+  return ((((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v) & 0x80808080u) >> 7 ^ 0x01010101u;
+}
+// 16 pixels per thread (one 16-byte vector each way) when both planes are 16-byte aligned
 __global__ void k_class_mask(const uint8_t* __restrict__ pred, uint8_t* __restrict__ out, size_t n, int cls) {
-  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (i + 4 <= n && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out)) & 3) == 0) {
-    const uint32_t v = *reinterpret_cast<const uint32_t*>(pred + i) ^ (0x01010101u * (uint32_t)cls);   // zero byte where pred == cls
-    const uint32_t nz = (((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v) & 0x80808080u;                          // 0x80 where byte != 0
-    *reinterpret_cast<uint32_t*>(out + i) = (nz >> 7) ^ 0x01010101u;
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (i >= n) return;
+  const uint32_t c4 = 0x01010101u * (uint32_t)cls;
+  if (i + 16 <= n && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+    const uint4 v = *reinterpret_cast<const uint4*>(pred + i);
+    *reinterpret_cast<uint4*>(out + i) = make_uint4(eq_bytes01(v.x, c4), eq_bytes01(v.y, c4), eq_bytes01(v.z, c4), eq_bytes01(v.w, c4));
   } else {
-    for (size_t k = i; k < n && k < i + 4; ++k) out[k] = pred[k] == cls;
+    for (size_t k = i; k < n && k < i + 16; ++k) out[k] = pred[k] == cls;
   }
 }
 
@@ -1191,7 +1197,7 @@ int width_profiles(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int ca
   float* raw = reinterpret_cast<float*>(ctx->d_tmp[1]);              // [B][2][H]
   dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
   for (int k = 0; k < 2; ++k) {
-    k_class_mask<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
+    k_class_mask<<<(unsigned)((n / 16 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
     k_pack_rows<<<g, dim3(32, 8), 0, st>>>(m, bits, H, W, Wd);
     k_diam_rows<<<dim3(cdiv(H, 8), 1, B), 256, 0, st>>>(bits, nullptr, H, W, Wd, nullptr, 0, nullptr, raw + (size_t)k * H, 2 * H);
     UB_CHECK_LAUNCH_N(ctx, 3);
@@ -1218,7 +1224,7 @@ int diameter_metrics(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int 
   UB_CUDA(ctx, cudaMemsetAsync(best, 0, sizeof(unsigned long long) * 2 * B, st));
   dim3 g(cdiv(Wd, 32), cdiv(H, 8), B);
   for (int k = 0; k < 2; ++k) {
-    k_class_mask<<<(unsigned)((n / 4 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
+    k_class_mask<<<(unsigned)((n / 16 + 255) / 256 + 1), 256, 0, st>>>(pred, m, n, k ? tape_cls : cable_cls);
     RUN(cclb_label(ctx, m, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
     k_cclb_stats<true><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
     k_diam_select<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane, min_area, best + (size_t)k * B);
@@ -1266,15 +1272,43 @@ __global__ void __launch_bounds__(256) k_comp_summary(const uint32_t* __restrict
 // holes = closed & ~tape as bytes {0,1};  class histogram (ids 0..7) with one shared-memory histogram per block
 __global__ void __launch_bounds__(256) k_holes_hist(const uint8_t* __restrict__ pred, const uint8_t* __restrict__ closed, const uint8_t* __restrict__ tape,
                                                     uint8_t* __restrict__ holes, int HW, int* __restrict__ hist_all, int hist_stride) {
+  // 16 pixels per thread; the class histogram is counted in registers (byte-compare masks), reduced per warp, then per block
   __shared__ int s_h[8];
   if (threadIdx.x < 8) s_h[threadIdx.x] = 0;
   __syncthreads();
   const size_t base = (size_t)blockIdx.y * HW;
-  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int i = (blockIdx.x * 256 + threadIdx.x) * 16;
+  int cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (i < HW) {
-    holes[base + i] = (closed[base + i] != 0 && tape[base + i] == 0) ? 1 : 0;
-    const int c = pred[base + i];
-    if (c < 8) atomicAdd(&s_h[c], 1);
+    const uint8_t *pp = pred + base + i, *pc = closed + base + i, *pt = tape + base + i;
+    uint8_t* ph = holes + base + i;
+    if (i + 16 <= HW && ((reinterpret_cast<uintptr_t>(pp) | reinterpret_cast<uintptr_t>(pc) | reinterpret_cast<uintptr_t>(pt) |
+                          reinterpret_cast<uintptr_t>(ph)) & 15) == 0) {
+      const uint4 vp = *reinterpret_cast<const uint4*>(pp), vc = *reinterpret_cast<const uint4*>(pc), vt = *reinterpret_cast<const uint4*>(pt);
+      const uint32_t wp[4] = {vp.x, vp.y, vp.z, vp.w}, wc[4] = {vc.x, vc.y, vc.z, vc.w}, wt[4] = {vt.x, vt.y, vt.z, vt.w};
+      uint32_t h[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h[k] = (eq_bytes01(wc[k], 0u) ^ 0x01010101u) & eq_bytes01(wt[k], 0u);       // closed != 0 && tape == 0
+      *reinterpret_cast<uint4*>(ph) = make_uint4(h[0], h[1], h[2], h[3]);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t c4 = 0x01010101u * (uint32_t)c;
+        const uint32_t sum = eq_bytes01(wp[0], c4) + eq_bytes01(wp[1], c4) + eq_bytes01(wp[2], c4) + eq_bytes01(wp[3], c4);   // <= 4 per byte lane
+        cnt[c] = (int)((sum * 0x01010101u) >> 24);
+      }
+    } else {
+      for (int k = 0; k < 16 && i + k < HW; ++k) {
+        ph[k] = (pc[k] != 0 && pt[k] == 0) ? 1 : 0;
+        const int c = pp[k];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) cnt[q] += c == q;
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const int v = __reduce_add_sync(0xffffffffu, cnt[c]);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_h[c], v);
   }
   __syncthreads();
   if (threadIdx.x < 8 && s_h[threadIdx.x]) atomicAdd(hist_all + (size_t)blockIdx.y * hist_stride + threadIdx.x, s_h[threadIdx.x]);
@@ -1312,7 +1346,7 @@ int analyze_defects(ub_ctx* ctx, const uint8_t* pred, int B, int H, int W, int c
   k_comp_summary<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, 0, acc, 16);
   // holes = CLOSE(tape, 5x5) - tape, class histogram
   RUN(morph_op(ctx, 2, 5, tape, closed, tmp, B, H, W, 1, st));
-  k_holes_hist<<<dim3(cdiv(H * W, 256), B), 256, 0, st>>>(pred, closed, tape, other, H * W, out + 8, 16);
+  k_holes_hist<<<dim3(cdiv(H * W, 256 * 16), B), 256, 0, st>>>(pred, closed, tape, other, H * W, out + 8, 16);
   RUN(cclb_label(ctx, other, bits, nullptr, lab, B, H, W, ctx->d_comp, plane, st));
   k_cclb_stats<false><<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, plane);
   k_comp_summary<<<g, dim3(32, 8), 0, st>>>(bits, lab, H, W, Wd, ctx->d_comp, hole_min_size, acc + 5, 16);
