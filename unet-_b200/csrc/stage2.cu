@@ -21,10 +21,23 @@ __device__ __forceinline__ int uf_find(const int* lab, int x) {
     x = p;
   }
 }
+// find with path splitting: every node on the way is re-pointed to its grandparent.  Parents only ever decrease (atomicMin)
+// and a grandparent is an ancestor, so the forest stays valid under concurrent unions; on solid masks (every word of a row
+// chained to the word before it, every row to the one above) this keeps the chains short instead of hundreds of hops.
+__device__ __forceinline__ int uf_find_split(int* lab, int x) {
+  int p = __ldcg(lab + x);
+  while (p != x) {
+    const int g = __ldcg(lab + p);
+    if (g != p) atomicMin(lab + x, g);
+    x = p;
+    p = g;
+  }
+  return x;
+}
 __device__ __forceinline__ void uf_union(int* lab, int a, int b) {
   while (true) {
-    a = uf_find(lab, a);
-    b = uf_find(lab, b);
+    a = uf_find_split(lab, a);
+    b = uf_find_split(lab, b);
     if (a == b) return;
     if (a < b) { int t = a; a = b; b = t; }
     int old = atomicMin(lab + a, b);
@@ -492,35 +505,52 @@ __global__ void __launch_bounds__(256) k_cclb_relabel(const uint32_t* __restrict
                                                       const int* __restrict__ comp, size_t plane, const uint32_t* __restrict__ markbits,
                                                       const int* __restrict__ wordprefix, int KW, int* __restrict__ labels,
                                                       int* __restrict__ stats, int max_labels, const int* __restrict__ bgacc) {
+  // a thread resolves the labels of the 32 pixels of its word; the warp (32 words of one row) then stores them through
+  // shared memory so that every store instruction writes 512 contiguous bytes instead of 32 scattered words
+  __shared__ int s_lab[8][32 * 33];
   const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
-  if (w >= Wd || y >= H) return;
-  uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+  const bool act = w < Wd && y < H;
   const size_t base = (size_t)blockIdx.z * H * W;
-  int* out = labels ? labels + base + (size_t)y * W + 32 * w : nullptr;
-  const int nvalid = min(32, W - 32 * w);
-  int pos = 0;
-  while (c) {
-    int a, len;
-    c &= ~first_run(c, a, len);
-    const int p = y * W + 32 * w + a, r = lab_all[base + p];
-    const int key = comp[5 * plane + base + r];
-    const int lbl = wordprefix[(size_t)blockIdx.z * KW + (key >> 5)] +
-                    __popc(markbits[(size_t)blockIdx.z * KW + (key >> 5)] & ((1u << (key & 31)) - 1u)) + 1;
-    if (out) {
-      for (; pos < a; ++pos) out[pos] = 0;
-      for (; pos < a + len; ++pos) out[pos] = lbl;
+  int* srow = s_lab[threadIdx.y] + threadIdx.x * 33;
+  if (act) {
+    uint32_t c = bits[((size_t)blockIdx.z * H + y) * Wd + w];
+    int pos = 0;
+    while (c) {
+      int a, len;
+      c &= ~first_run(c, a, len);
+      const int p = y * W + 32 * w + a, r = lab_all[base + p];
+      const int key = comp[5 * plane + base + r];
+      const int lbl = wordprefix[(size_t)blockIdx.z * KW + (key >> 5)] +
+                      __popc(markbits[(size_t)blockIdx.z * KW + (key >> 5)] & ((1u << (key & 31)) - 1u)) + 1;
+      if (labels) {
+        for (; pos < a; ++pos) srow[pos] = 0;
+        for (; pos < a + len; ++pos) srow[pos] = lbl;
+      }
+      if (r == p && stats && lbl < max_labels) {
+        const int* k = comp + base + r;
+        int* s = stats + ((size_t)blockIdx.z * max_labels + lbl) * 5;
+        s[0] = k[plane]; s[1] = k[3 * plane]; s[2] = k[2 * plane] - k[plane] + 1; s[3] = k[4 * plane] - k[3 * plane] + 1; s[4] = k[0];
+      }
     }
-    if (r == p && stats && lbl < max_labels) {
-      const int* k = comp + base + r;
-      int* s = stats + ((size_t)blockIdx.z * max_labels + lbl) * 5;
-      s[0] = k[plane]; s[1] = k[3 * plane]; s[2] = k[2 * plane] - k[plane] + 1; s[3] = k[4 * plane] - k[3 * plane] + 1; s[4] = k[0];
+    if (labels) for (; pos < 32; ++pos) srow[pos] = 0;
+    if (w == 0 && y == 0 && stats && max_labels > 0) {
+      const int* a = bgacc + blockIdx.z * 8;
+      int* s = stats + (size_t)blockIdx.z * max_labels * 5;
+      s[0] = a[1]; s[1] = a[3]; s[2] = a[2] - a[1] + 1; s[3] = a[4] - a[3] + 1; s[4] = a[0];
     }
   }
-  if (out) for (; pos < nvalid; ++pos) out[pos] = 0;
-  if (w == 0 && y == 0 && stats && max_labels > 0) {
-    const int* a = bgacc + blockIdx.z * 8;
-    int* s = stats + (size_t)blockIdx.z * max_labels * 5;
-    s[0] = a[1]; s[1] = a[3]; s[2] = a[2] - a[1] + 1; s[3] = a[4] - a[3] + 1; s[4] = a[0];
+  if (!labels || y >= H) return;                              // uniform per warp (a warp is one row)
+  __syncwarp();
+  int* orow = labels + base + (size_t)y * W + (size_t)blockIdx.x * 1024;      // first pixel of this warp's 32 words
+  const int npx = min(1024, W - blockIdx.x * 1024);                           // pixels of the row this warp covers
+  const int* sw = s_lab[threadIdx.y];
+  if ((W & 3) == 0 && (reinterpret_cast<uintptr_t>(orow) & 15) == 0) {
+    for (int q = threadIdx.x * 4; q < npx; q += 128) {                        // q: pixel offset, 4 pixels per lane and step
+      const int* sp = sw + (q >> 5) * 33 + (q & 31);
+      *reinterpret_cast<int4*>(orow + q) = make_int4(sp[0], sp[1], sp[2], sp[3]);
+    }
+  } else {
+    for (int q = threadIdx.x; q < npx; q += 32) orow[q] = sw[(q >> 5) * 33 + (q & 31)];
   }
 }
 __global__ void k_bg_init(int* bgacc, int B) {
