@@ -29,7 +29,7 @@ FRAME_HW = (448, 800)
 NET_HW = (512, 512)
 GFLOP_PER_FRAME = 111.636          # 18 conv3x3 + final at 512x512, 2*MACs
 METRIC = "frames/sec (800x448 UNet++ + burr)"
-CONV_SOURCES = ("conv_rows.cu", "conv_tc.cu", "tc_ptx.cuh", "net_glue.cu", "common.cuh")
+CONV_SOURCES = ("conv_rows.cu", "conv_tc.cu", "conv_block.cu", "tc_ptx.cuh", "net_glue.cu", "common.cuh")
 
 
 def conv_source_hash():

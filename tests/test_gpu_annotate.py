@@ -147,3 +147,32 @@ def test_visualize_two_stage_vs_oracle(box):
         got = U.visualize_two_stage(fr[i], mc, mt, mb, roi, box)
         want = R.visualize_two_stage(fr[i], mc, mt, mb, roi, box)
         assert got.dtype == np.uint8 and np.array_equal(got, want), int((got != want).any(axis=2).sum())
+
+
+def test_cli_batch_overlay_path_equals_oracle():
+    """What the CLIs do for the result video (cli_common.py): ub_overlay + ops.annotate_on_device on the whole batch, one
+    download, then draw_overlay(redo=...) per frame -- the frames equal the oracle's visualize_two_stage."""
+    from oracle import ref_pipeline as R
+    from unet_b200 import _lib, cli_common, ops
+    h, w, n = 448, 800, 3
+    fr = S.frames_cable(n, h, w, seed=12)
+    roi = R.map_roi((w, h))
+    mc = np.stack([S.mask_cable_synth(h, w)] * n)
+    mt = np.stack([S.mask_blobs(h, w, seed=40 + i, fill=0.03) for i in range(n)])
+    mb = np.stack([S.mask_blobs(h, w, seed=50 + i, fill=0.004) for i in range(n)])
+    mb[1, -2:, 250:290] = 1                                   # frame 1: burr pixels on the bottom border -> redo
+    c = _lib.Context(0, max_batch=n, frame_hw=(h, w), net_hw=(16, 16))
+    try:
+        d, dmc, dmt, dmb = dev(fr), dev(mc), dev(mt), dev(mb)
+        blend = c.overlay(d, dmc, dmt, dmb, roi)
+        redo = ops.annotate_on_device(c, blend, dmc, dmt, dmb, roi).cpu().numpy()
+        assert redo[1] == 1
+        frames = blend.cpu().numpy()
+        for i in range(n):
+            got = cli_common.draw_overlay(frames[i], mc[i], mt[i], mb[i], roi, redo=int(redo[i]))
+            assert np.array_equal(got, R.visualize_two_stage(fr[i], mc[i], mt[i], mb[i], roi, True)), i
+        # frames too large for the device path: cv2 draws everything (redo=None)
+        got = cli_common.draw_overlay(c.overlay(d, dmc, dmt, dmb, roi).cpu().numpy()[0], mc[0], mt[0], mb[0], roi, redo=None)
+        assert np.array_equal(got, R.visualize_two_stage(fr[0], mc[0], mt[0], mb[0], roi, True))
+    finally:
+        c.close()
