@@ -176,3 +176,26 @@ def test_cli_batch_overlay_path_equals_oracle():
         assert np.array_equal(got, R.visualize_two_stage(fr[0], mc[0], mt[0], mb[0], roi, True))
     finally:
         c.close()
+
+
+def test_annotate_error_behaviour():
+    """Bad arguments to the annotation entry points come back as UbError (negative code + message); the context stays usable."""
+    import ctypes as C
+    from unet_b200 import _lib
+    h, w = 64, 96
+    c = _lib.Context(0, max_batch=2, frame_hw=(h, w), net_hw=(16, 16))
+    try:
+        fr = dev(np.zeros((2, h, w, 3), np.uint8))
+        m = dev(np.ones((2, h, w), np.uint8))
+        with pytest.raises(_lib.UbError, match="thickness"):
+            c.draw_contours(fr, m, (1, 2, 3), thickness=4)
+        with pytest.raises(_lib.UbError, match="redo"):                           # thickness 3 needs the flags
+            c._check(_lib.lib().ub_draw_contours(c._h, fr.data_ptr(), m.data_ptr(), 2, h, w, 1, 2, 3, 3, None, c.stream))
+        with pytest.raises(_lib.UbError, match="exceed the context"):
+            c.draw_contours(dev(np.zeros((3, h, w, 3), np.uint8)), dev(np.ones((3, h, w), np.uint8)), (1, 2, 3))
+        with pytest.raises(_lib.UbError, match="null"):
+            c._check(_lib.lib().ub_paint_layer(c._h, fr.data_ptr(), None, 0, 2, h, w, (C.c_uint8 * 9)(), c.stream))
+        out = c.draw_contours(fr, m, (9, 8, 7)).cpu().numpy()                       # a full mask: the frame's outline
+        assert (out[0, 0, 0] == (9, 8, 7)).all() and (out[0, h // 2, w // 2] == 0).all()
+    finally:
+        c.close()
