@@ -58,6 +58,7 @@ def measure(B=512, reps=10, log=None):
         ("ub_morph dilate 8x8 (k_morph_cols)", lambda: ctx.morph("dilate", 8, mask), 2 * P),
     ]
     out = {"frames": B, "hw": [H, W], "hbm_peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(pk) else "fallback",
+           "peak_note": "hbm_gbs is a measured COPY bandwidth (1 read : 1 write); a read-heavy kernel (BGR2GRAY: 3 : 1) can exceed it",
            "edge_fused": os.environ.get("UB_EDGE_FUSED", "1"),
            "env": {k: os.environ[k] for k in ("UB_BLUR_COLS", "UB_MORPH_WORDS", "UB_BURR_COLS", "UB_EDGE_COLS") if k in os.environ}, "ops": []}
     for name, fn, nbytes in rows:

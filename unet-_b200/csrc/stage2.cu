@@ -214,8 +214,8 @@ __global__ void __launch_bounds__(256) k_cclb_init(const uint8_t* __restrict__ s
   const int w = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
   if (w >= Wd || y >= H) return;
   const size_t fb = (size_t)blockIdx.z * H * W, wb = ((size_t)blockIdx.z * H + y) * Wd + w;
-  uint32_t c = src ? pack32(src + fb, H, W, y, 32 * w) : bits[wb];       // src == null: the plane is already packed in `bits`
-  if (src) bits[wb] = c;
+  uint32_t c = pack32(src + fb, H, W, y, 32 * w);
+  bits[wb] = c;
   if (strong) strong[wb] = c & ~pack32(src + fb, H, W, y, 32 * w, 0x02020202u);
   int* l = lab + fb + (size_t)y * W + 32 * w;
   while (c) {
@@ -713,7 +713,6 @@ static int ccl_label(ub_ctx* ctx, const uint8_t* src, int* lab, int B, int H, in
 }
 
 // run-based labelling of a u8 image on packed rows: bits (+ strong) planes and lab entries at run starts
-// (src == null: of the plane already packed in `bits`)
 static int cclb_label(ub_ctx* ctx, const uint8_t* src, uint32_t* bits, uint32_t* strong, int* lab, int B, int H, int W,
                       int* comp, size_t plane, cudaStream_t st) {
   const int Wd = (W + 31) / 32;
