@@ -984,9 +984,12 @@ int burr_finish(ub_ctx* ctx, const uint8_t* mask, int B, int H, int W, const ub_
       int RS = 4;
       while (RS < mc.band.top + mc.band.bottom + 1 || RS < mc.close.top + mc.close.bottom + 1 || RS < mc.open.top + mc.open.bottom + 1) RS *= 2;
       const int warps = (size_t)8 * 6 * RS * 128 <= 48 * 1024 ? 8 : ((size_t)4 * 6 * RS * 128 <= 48 * 1024 ? 4 : 2);
-      // rows per warp: about 40 warps per SM when the batch is small (the walk is a serial chain), 32..64 rows when it is large
-      long want = ((long)B * H * nstrips + (long)ctx->sm_count * 40 - 1) / ((long)ctx->sm_count * 40);
-      int R = want < 8 ? 8 : (want > 64 ? 64 : (int)want);
+      // rows per warp: every task also walks the 13 (standard) rows of reach above and below its rows, so few long tasks beat many
+      // short ones as long as every SM has a dozen warps (batch 64, ncu: 4 rows 67.5 us, 8: 54.7, 12: 51.4, 16: 50.5; profiles/r03b)
+      long want = ((long)B * H * nstrips + (long)ctx->sm_count * 16 - 1) / ((long)ctx->sm_count * 16);
+      int R = want < 12 ? 12 : (want > 64 ? 64 : (int)want);
+      static const int rows_env = getenv("UB_CHAIN_ROWS") ? atoi(getenv("UB_CHAIN_ROWS")) : 0;       // tuning override
+      if (rows_env > 0) R = rows_env;
       if (R > H) R = H;
       const int nblk = cdiv(H, R);
       static const int tab_env = getenv("UB_MORPH_TABLES") ? atoi(getenv("UB_MORPH_TABLES")) : 1;
