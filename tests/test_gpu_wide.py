@@ -130,3 +130,24 @@ def test_properties_at_full_batch():
         assert torch.equal(e_hi[:4], e_hi[4:8])                   # identical frames give identical maps at every batch position
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("hw", [(37, 53), (5, 7), (448, 800), (33, 65)])
+def test_gray_odd_sizes_and_unaligned_frames(hw):
+    """BGR2GRAY (16 pixels per thread with 16-byte vectors when aligned): pixel counts that are not multiples of 16, and a frame
+    pointer one byte off alignment (the scalar path), against cv2."""
+    from unet_b200 import _lib
+    h, w = hw
+    fr = S.frames_noise(3, h, w, seed=h * w)
+    c = _lib.Context(0, max_batch=3, frame_hw=hw, net_hw=(16, 16))
+    try:
+        _, g = c.preprocess(dev(fr), want_x=False, want_gray=True)
+        for i in range(3):
+            same(f"gray[{i}]", g[i], cv2.cvtColor(fr[i], cv2.COLOR_BGR2GRAY))
+        raw = torch.zeros(fr.size + 1, dtype=torch.uint8, device="cuda")
+        raw[1:] = dev(fr).reshape(-1)
+        _, g = c.preprocess(raw[1:].view(3, h, w, 3), want_x=False, want_gray=True)
+        for i in range(3):
+            same(f"gray unaligned[{i}]", g[i], cv2.cvtColor(fr[i], cv2.COLOR_BGR2GRAY))
+    finally:
+        c.close()
