@@ -208,7 +208,7 @@ __device__ __forceinline__ void mc_scatter(uint32_t w, int lane, const Footprint
 // warps x (OP >= 2 ? 2 : 1) rings x RS x 32 words, RS a power of two >= top + bottom + 1.
 // K: 0 = footprint given at run time, else one of the FpT sizes (then `fp` and RS are ignored)
 template <int OP, int K>
-__global__ void __launch_bounds__(256) k_morph_cols(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int H, int W,
+__global__ void __launch_bounds__(256, 5) k_morph_cols(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int H, int W,
                                                     const __grid_constant__ Footprint fp, uint32_t value, int nstrips, int nblk, int R, int RSr) {
   constexpr bool TWO = OP >= 2;
   constexpr bool DIL1 = OP == 0 || OP == 2, DIL2 = OP == 3;
