@@ -311,7 +311,7 @@ namespace {
 
 // ---- non-local means ------------------------------------------------------------------------
 // FastNlMeansDenoisingInvoker<uchar | Vec2b, int, unsigned, DistSquared, int>::operator().
-// CTA = 8 warps side by side; a warp owns NLM_WCOLS = 26 output columns x RT rows.  The source
+// CTA = 8 warps side by side; a warp owns NLM_WCOLS = 26 output columns x RT rows (RT = 20: see nlm()).  The source
 // patch (tile + 13-pixel REFLECT_101 border) sits in shared memory.  For each of the 441 search
 // offsets a lane walks DOWN its column keeping the vertical 7-sum of squared differences in
 // registers (ring of 7), the horizontal 7-sum is four shuffles (lanes 26..31 only feed their
@@ -486,8 +486,21 @@ int nlm(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, int 
   if (src == dst) return ub_fail(ctx, UB_ERR_ARG, "NLM cannot run in place");
   TimeScope ts(ctx, UB_T_ENHANCE, st);
   const EnhTables* T = reinterpret_cast<const EnhTables*>(ctx->d_enh);
-  return cn == 1 ? launch_nlm<1, 32>(ctx, src, dst, B, H, W, pstride, ch, T, st)
-                 : launch_nlm<2, 32>(ctx, src, dst, B, H, W, pstride, ch, T, st);
+  // rows per warp walk (RT): the accumulators of RT rows live in registers, so RT sets the register count and with it the warps per
+  // SM that hide the SHFL / LDS latency of the walk.  One channel: 98 registers / 16 warps per SM at RT = 32, 64 / 28 at RT = 20
+  // (ncu: issue slots 46 % -> 59 % busy, short-scoreboard stalls either way).  Two channels: 126 registers at RT = 32 AND at 24, yet
+  // 24 rows take half the time -- the walk is unrolled over RT + 6 steps inside the loop over the 441 offsets, and the 38-step body
+  // is what hurts there.  Per 800x448 frame, batch 16, L / ab channels (profiles/r03k_nlm_rows_sweep.log): 0.309 / 0.457 ms at
+  // RT = 32, 0.201 / 0.248 at 28, 0.211 / 0.232 at 24, 0.201 / 0.215 at 20 (the default), 0.204 / 0.250 at 16, 0.207 / 0.264 at 8.
+  static const int rt_env = getenv("UB_NLM_RT") ? atoi(getenv("UB_NLM_RT")) : 20;
+#define UB_NLM_CASE(R_)                                                                         \
+  if (rt_env == R_)                                                                             \
+    return cn == 1 ? launch_nlm<1, R_>(ctx, src, dst, B, H, W, pstride, ch, T, st)              \
+                   : launch_nlm<2, R_>(ctx, src, dst, B, H, W, pstride, ch, T, st);
+  UB_NLM_CASE(8) UB_NLM_CASE(16) UB_NLM_CASE(24) UB_NLM_CASE(28) UB_NLM_CASE(32)
+#undef UB_NLM_CASE
+  return cn == 1 ? launch_nlm<1, 20>(ctx, src, dst, B, H, W, pstride, ch, T, st)
+                 : launch_nlm<2, 20>(ctx, src, dst, B, H, W, pstride, ch, T, st);
 }
 
 int sharpen3(ub_ctx* ctx, const uint8_t* src, uint8_t* dst, int B, int H, int W, cudaStream_t st) {
