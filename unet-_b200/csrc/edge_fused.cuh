@@ -9,7 +9,7 @@
 // REFLECT_101, one rounding (acc + 2^15) >> 16; Sobel 3x3 on the blurred plane with
 // BORDER_REPLICATE, |gx|+|gy| (0 outside the image), fixed-point NMS with TG22 = 13573 (<<15).
 //
-// Tile: EF_TW x EF_TH outputs per CTA of 256 threads.  A "column word" cw covers the four pixels
+// Tile: EF_TW x EF_TH (160 x 24) outputs per CTA of 256 threads.  A "column word" cw covers the four pixels
 // x0 - 4 + 4cw .. +3, so every stage works on aligned 32-bit words:
 //   L  gray words with a 4-pixel halo                         g  [TH+8][42]   u8x4
 //   V  vertical 5-tap on (c0,c1),(c2,c3) u16x2 lanes           vv [TH+4][44]   2 x u16x2
@@ -23,7 +23,14 @@
 
 namespace s2 {
 
-constexpr int EF_TW = 160, EF_TH = 32;
+#ifndef UB_EF_TH
+#define UB_EF_TH 24
+#endif
+// tile height: (TH + 4) % 4 == 0 and TH even (the V / S stages walk rows in groups of 4 / 2).  24 rows = 37.6 KB of shared memory, six
+// CTAs per SM; 32 rows (48.5 KB, four CTAs) were 10 % slower, 28 / 20 / 16 rows in between (ub_blur_canny per 512 frames: 0.907 ms at
+// 32, 0.840 at 28, 0.810 at 24, 0.893 at 20, 0.898 at 16; profiles/r03n_edge_tile_height.log)
+constexpr int EF_TW = 160, EF_TH = UB_EF_TH;
+static_assert((EF_TH + 4) % 4 == 0 && EF_TH % 2 == 0, "tile height");
 constexpr int EF_CW = EF_TW / 4 + 2;            // 42 column words (one word of halo each side)
 constexpr int EF_TR = 256 / EF_CW;               // 6 row lanes
 constexpr int EF_CWP = EF_CW + 2;               // + one pad word each side (read by the neighbours' taps, never used)
